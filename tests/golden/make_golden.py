@@ -1,0 +1,116 @@
+"""Generates tests/golden/*.npz by executing the third-party libraries the reference calls
+(scipy.spatial.distance.cdist, cv2.BFMatcher, cv2.solvePnP / solvePnPRansac, cv2.SVDecomp) on
+small seeded inputs.  The reference itself (ROS + RTAB-Map + Python 2) cannot be imported
+here, and ships no golden vectors, so these library outputs at the
+reference's own call sites are the pin:  data_handler.py:170 (cdist),
+myRegistrationVis.cpp:580-581/739-740/852 (BFMatcher k=2), :1077 (solvePnPRansac).
+
+Run from the repo root:  python tests/golden/make_golden.py
+Versions used for the committed files: cv2 4.13.0, scipy 1.18.1, numpy 2.3.5.
+"""
+import os
+import sys
+
+import cv2
+import numpy as np
+from scipy.spatial.distance import cdist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from multi_robot_slam_separators_b200 import synth  # noqa: E402
+from oracle import matching, pnp  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def golden_svd():
+    rng = np.random.default_rng(101)
+    mats, ws, us, vts = [], [], [], []
+    for shape in [(12, 12), (12, 12), (3, 3), (3, 3), (6, 4), (6, 3), (6, 5)]:
+        A = rng.standard_normal(shape)
+        if shape == (12, 12) and len(mats) == 1:
+            M = rng.standard_normal((10, 12))
+            A = M.T @ M  # rank 10: the EPnP 5-point case
+        w, u, vt = cv2.SVDecomp(A)
+        mats.append(A); ws.append(w.ravel()); us.append(u); vts.append(vt)
+    np.savez(os.path.join(OUT, "svd.npz"), **{f"A{i}": m for i, m in enumerate(mats)},
+             **{f"w{i}": m for i, m in enumerate(ws)}, **{f"u{i}": m for i, m in enumerate(us)},
+             **{f"vt{i}": m for i, m in enumerate(vts)}, n=len(mats))
+
+
+def golden_hamming():
+    rng = np.random.default_rng(102)
+    q = rng.integers(0, 256, (96, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (120, 32), dtype=np.uint8)
+    # adversarial ties: duplicated train rows and queries equal to train rows
+    t[7] = t[3]; t[50] = t[3]; t[119] = t[0]
+    q[0] = t[3]; q[1] = t[0]
+    q[2] = t[10]; q[2, 0] ^= 1
+    # SURVEY 8c(i) known-answer: one byte descriptors are not valid here (32 B), mimic with padding
+    ka_t = np.zeros((6, 32), np.uint8); ka_t[:, 0] = [0x0f, 0x01, 0x03, 0x01, 0x03, 0x01]
+    ka_q = np.zeros((1, 32), np.uint8)
+    bf = cv2.BFMatcher(cv2.NORM_HAMMING)
+    ka = [(m.trainIdx, int(m.distance)) for m in bf.knnMatch(ka_q, ka_t, k=3)[0]]
+    idx, dist = matching.knn2(q, t)
+    pairs = np.array(matching.global_match(q, t, 0.8), dtype=np.int32).reshape(-1, 2)
+    pairs_strict = np.array(matching.global_match(q, t, 0.8, strict=True), dtype=np.int32).reshape(-1, 2)
+    np.savez(os.path.join(OUT, "hamming.npz"), q=q, t=t, idx=idx, dist=dist, pairs=pairs,
+             pairs_strict=pairs_strict, ka_q=ka_q, ka_t=ka_t, ka=np.array(ka, dtype=np.int32))
+
+
+def golden_netvlad():
+    rng = np.random.default_rng(103)
+    A, B = synth.make_robots(2, 48, n_feat=8, dim=128, seed=1030)
+    local, recv = A.netvlad, B.netvlad[:40]
+    d = cdist(local, recv)
+    local_used = np.array([3, 17], dtype=np.int32)
+    other_used = np.array([5], dtype=np.int32)
+    pairs_ignored = np.array([[0, int(np.argmin(d[0]))], [9, 2]], dtype=np.int32)
+    np.savez(os.path.join(OUT, "netvlad.npz"), local=local, recv=recv, d=d, local_used=local_used,
+             other_used=other_used, pairs_ignored=pairs_ignored)
+
+
+def golden_epnp():
+    rng = np.random.default_rng(104)
+    K = pnp.K_matrix(synth.FX, synth.FY, synth.CX, synth.CY)
+    objs, imgs, rvs, tvs = [], [], [], []
+    for t in range(24):
+        n = 5
+        rv = rng.standard_normal(3) * 0.3
+        tv = rng.standard_normal(3) * np.array([2, 1, 2])
+        R, _ = cv2.Rodrigues(rv)
+        Pc = np.stack([rng.uniform(-8, 8, n), rng.uniform(-3, 3, n), rng.uniform(4, 40, n)], 1)
+        Pw = (R.T @ (Pc - tv).T).T
+        uv = (K @ Pc.T).T
+        uv = uv[:, :2] / uv[:, 2:] + rng.standard_normal((n, 2)) * (0.5 if t % 3 else 25.0)
+        obj = Pw.astype(np.float32); img = uv.astype(np.float32)
+        ok, rvec, tvec = cv2.solvePnP(obj, img, K, None, flags=cv2.SOLVEPNP_EPNP)
+        objs.append(obj); imgs.append(img); rvs.append(rvec.ravel()); tvs.append(tvec.ravel())
+    np.savez(os.path.join(OUT, "epnp.npz"), obj=np.array(objs), img=np.array(imgs), rvec=np.array(rvs),
+             tvec=np.array(tvs), K=K)
+
+
+def golden_pnp_ransac():
+    A, B = synth.make_robots(2, 40, n_feat=1000, dim=128, seed=1050)
+    from oracle import find_matches as fm
+    ms = fm.find_matches(A.netvlad, B.netvlad, 0.13, 20)[:6]
+    K = pnp.K_matrix(synth.FX, synth.FY, synth.CX, synth.CY)
+    rv0, _ = cv2.Rodrigues(synth.R_LOCAL.T.copy())
+    rv0 = rv0.ravel(); tv0 = np.zeros(3)
+    out = dict(K=K, rv0=rv0, tv0=tv0, n=len(ms))
+    for i, (a, b) in enumerate(ms):
+        pairs = matching.global_match(B.desc[b], A.desc[a], 0.8)
+        obj, img, fi, ti = matching.pnp_correspondences(pairs, A.kp3d[a], B.kp2d[b])
+        iters = [300, 100, 1000][i % 3]
+        ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, K, rv0, tv0, iterations=iters)
+        out.update({f"desc_from{i}": A.desc[a], f"desc_to{i}": B.desc[b], f"kp3d_from{i}": A.kp3d[a],
+                    f"kp2d_to{i}": B.kp2d[b], f"pairs{i}": np.array(pairs, np.int32), f"obj{i}": obj,
+                    f"img{i}": img, f"iters{i}": iters, f"ok{i}": ok, f"rvec{i}": rv, f"tvec{i}": tv,
+                    f"inliers{i}": inl, f"samples{i}": pnp.sample_index_stream(len(obj), 5, iters)})
+    np.savez_compressed(os.path.join(OUT, "pnp_ransac.npz"), **out)
+
+
+if __name__ == "__main__":
+    golden_svd(); golden_hamming(); golden_netvlad(); golden_epnp(); golden_pnp_ransac()
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
