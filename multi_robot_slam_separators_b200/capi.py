@@ -1,0 +1,177 @@
+"""ctypes binding of include/sepb200.h (the C-ABI shared library libsepb200.so).
+
+The library is the product; this module only marshals numpy buffers.  There is no CPU
+fallback: if the library is missing or no sm_100 device is present, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsepb200.so")
+
+_lib = None
+
+
+class SepbError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SepbError(f"{LIB_PATH} not built: run `python -m multi_robot_slam_separators_b200.build` "
+                            "(there is no CPU fallback)")
+        _lib = C.CDLL(LIB_PATH)
+        _declare(_lib)
+    return _lib
+
+
+class MatchParams(C.Structure):
+    _fields_ = [("nndr", C.c_float), ("nndr_strict", C.c_int32)]
+
+
+def _declare(L):
+    vp, i32, i64 = C.c_void_p, C.c_int, C.c_int64
+    L.sepb_ctx_create.argtypes = [i32, C.POINTER(vp)]
+    L.sepb_ctx_create.restype = i32
+    L.sepb_ctx_destroy.argtypes = [vp]
+    L.sepb_ctx_destroy.restype = None
+    L.sepb_last_error.argtypes = [vp]
+    L.sepb_last_error.restype = C.c_char_p
+    L.sepb_ctx_stream.argtypes = [vp]
+    L.sepb_ctx_stream.restype = vp
+    L.sepb_ctx_sync.argtypes = [vp]
+    L.sepb_ctx_sync.restype = i32
+    L.sepb_ctx_launch_count.argtypes = [vp]
+    L.sepb_ctx_launch_count.restype = i64
+    L.sepb_frames_create.argtypes = [vp, i32, i32, C.POINTER(vp)]
+    L.sepb_frames_create.restype = i32
+    L.sepb_frames_destroy.argtypes = [vp]
+    L.sepb_frames_destroy.restype = None
+    L.sepb_frames_size.argtypes = [vp]
+    L.sepb_frames_size.restype = i32
+    L.sepb_frames_upload.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp]
+    L.sepb_frames_upload.restype = i32
+    L.sepb_measure_peak.argtypes = [vp, i32, i32, C.POINTER(C.c_double)]
+    L.sepb_measure_peak.restype = i32
+    for name in ("sepb_match_pairs", "sepb_match_pairs_dev"):
+        f = getattr(L, name)
+        f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), vp, vp, vp, vp, vp, vp]
+        f.restype = i32
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    assert a.flags["C_CONTIGUOUS"]
+    return C.c_void_p(a.ctypes.data)
+
+
+class Context:
+    def __init__(self, device: int = 0):
+        self._h = C.c_void_p()
+        rc = lib().sepb_ctx_create(device, C.byref(self._h))
+        if rc != 0:
+            raise SepbError(f"sepb_ctx_create(device={device}) failed with code {rc} (CUDA device required)")
+
+    def check(self, rc: int):
+        if rc != 0:
+            raise SepbError(f"sepb error {rc}: {lib().sepb_last_error(self._h).decode()}")
+
+    @property
+    def stream(self) -> int:
+        return lib().sepb_ctx_stream(self._h) or 0
+
+    def sync(self):
+        self.check(lib().sepb_ctx_sync(self._h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(lib().sepb_ctx_launch_count(self._h))
+
+    def measure_peak(self, kind: str, reps: int = 5) -> float:
+        """'popc' -> POPC/s, 'dfma' -> FP64 FMA/s (measured microbenchmarks)."""
+        v = C.c_double()
+        self.check(lib().sepb_measure_peak(self._h, {"popc": 0, "dfma": 1}[kind], reps, C.byref(v)))
+        return v.value
+
+    def close(self):
+        if self._h:
+            lib().sepb_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Frames:
+    """Device-resident feature store of one robot (sepb_frames)."""
+
+    def __init__(self, ctx: Context, capacity: int, max_feat: int):
+        self.ctx, self.capacity, self.max_feat = ctx, capacity, max_feat
+        self._h = C.c_void_p()
+        ctx.check(lib().sepb_frames_create(ctx._h, capacity, max_feat, C.byref(self._h)))
+
+    def upload(self, first, desc, kp2d, kp3d, count, octave=None):
+        desc = np.ascontiguousarray(desc, dtype=np.uint8)
+        n = desc.shape[0]
+        assert desc.shape == (n, self.max_feat, 32)
+        kp2d = np.ascontiguousarray(kp2d, dtype=np.float32).reshape(n, self.max_feat, 2)
+        kp3d = np.ascontiguousarray(kp3d, dtype=np.float32).reshape(n, self.max_feat, 3)
+        count = np.ascontiguousarray(count, dtype=np.int32).reshape(n)
+        if octave is not None:
+            octave = np.ascontiguousarray(octave, dtype=np.int32).reshape(n, self.max_feat)
+        self.ctx.check(lib().sepb_frames_upload(self.ctx._h, self._h, first, n, _ptr(desc), _ptr(kp2d), _ptr(kp3d),
+                                                _ptr(octave), _ptr(count)))
+
+    @property
+    def size(self):
+        return lib().sepb_frames_size(self._h)
+
+    def close(self):
+        if self._h:
+            lib().sepb_frames_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def frames_from_robot(ctx: Context, robot) -> Frames:
+    """Upload a synth.RobotFrames."""
+    n, F = robot.desc.shape[0], robot.desc.shape[1]
+    f = Frames(ctx, n, F)
+    f.upload(0, robot.desc, robot.kp2d, robot.kp3d, robot.count, robot.octave)
+    return f
+
+
+def match_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, nndr=0.8, strict=False, want_knn=True):
+    """Host-buffer K2 call.  pairs: [P,2] (from_frame, to_frame).  Returns dict of numpy arrays."""
+    pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+    P = pairs.shape[0]
+    Ft, Ff = frames_to.max_feat, frames_from.max_feat
+    knn_idx = np.full((P, Ft, 2), -1, np.int32) if want_knn else None
+    knn_dist = np.full((P, Ft, 2), -1, np.int32) if want_knn else None
+    n_matches = np.zeros(P, np.int32)
+    n_unique = np.zeros(P, np.int32)
+    mf = np.zeros((P, Ff), np.uint16)
+    mt = np.zeros((P, Ff), np.uint16)
+    prm = MatchParams(nndr, 1 if strict else 0)
+    ctx.check(lib().sepb_match_pairs(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(prm),
+                                     _ptr(knn_idx), _ptr(knn_dist), _ptr(n_matches), _ptr(mf), _ptr(mt),
+                                     _ptr(n_unique)))
+    return dict(knn_idx=knn_idx, knn_dist=knn_dist, n_matches=n_matches, match_from=mf, match_to=mt,
+                n_unique_to=n_unique)

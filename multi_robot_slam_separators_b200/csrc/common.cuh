@@ -1,0 +1,98 @@
+// Shared host-side plumbing for the C ABI (context, frame store, error capture).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+
+#include "../../include/sepb200.h"
+
+struct sepb_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  int64_t launches = 0;
+  std::mutex mu;
+  // grow-only device scratch (pairs, outputs of host-level calls)
+  void* scratch = nullptr;
+  size_t scratch_bytes = 0;
+  int sm_count = 148;
+};
+
+struct sepb_frames {
+  sepb_ctx* ctx = nullptr;
+  int capacity = 0;
+  int max_feat = 0;
+  int size = 0;  // highest uploaded slot + 1
+  uint8_t* desc = nullptr;   // [capacity][max_feat][32]
+  float* kp2d = nullptr;     // [capacity][max_feat][2]
+  float* kp3d = nullptr;     // [capacity][max_feat][3]
+  int32_t* octave = nullptr; // [capacity][max_feat]
+  int32_t* count = nullptr;  // [capacity]
+};
+
+// device view of a frame store passed by value to kernels
+struct FramesView {
+  const uint8_t* desc;
+  const float* kp2d;
+  const float* kp3d;
+  const int32_t* octave;
+  const int32_t* count;
+  int max_feat;
+  int size;
+};
+
+static inline FramesView view_of(const sepb_frames* f) {
+  return FramesView{f->desc, f->kp2d, f->kp3d, f->octave, f->count, f->max_feat, f->size};
+}
+
+static inline int sepb_fail(sepb_ctx* ctx, int code, const char* what, const char* file, int line) {
+  char buf[512];
+  if (code > 0)
+    snprintf(buf, sizeof buf, "%s: %s (%s:%d)", what, cudaGetErrorString((cudaError_t)code), file, line);
+  else
+    snprintf(buf, sizeof buf, "%s (%s:%d)", what, file, line);
+  if (ctx) ctx->err = buf;
+  return code;
+}
+
+#define SEPB_CUDA(ctx, expr)                                                     \
+  do {                                                                           \
+    cudaError_t _e = (expr);                                                     \
+    if (_e != cudaSuccess) return sepb_fail((ctx), (int)_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define SEPB_REQUIRE(ctx, cond, code)                                            \
+  do {                                                                           \
+    if (!(cond)) return sepb_fail((ctx), (code), "requirement failed: " #cond, __FILE__, __LINE__); \
+  } while (0)
+
+// grow-only scratch; returns nullptr on failure (error recorded)
+static inline void* sepb_scratch(sepb_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->scratch_bytes) return ctx->scratch;
+  if (ctx->scratch) {
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->scratch);
+    ctx->scratch = nullptr;
+    ctx->scratch_bytes = 0;
+  }
+  size_t want = bytes + bytes / 4 + 4096;
+  cudaError_t e = cudaMalloc(&ctx->scratch, want);
+  if (e != cudaSuccess) {
+    sepb_fail(ctx, (int)e, "cudaMalloc(scratch)", __FILE__, __LINE__);
+    return nullptr;
+  }
+  ctx->scratch_bytes = want;
+  return ctx->scratch;
+}
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// kernel launchers implemented in the .cu files
+int sepb_launch_hamming_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                              float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist,
+                              int32_t* d_n_matches, uint16_t* d_match_from, uint16_t* d_match_to,
+                              int32_t* d_n_unique_to);

@@ -1,0 +1,61 @@
+// Roofline denominators that MEASURED_PEAKS.json does not carry: POPC (K2) and FP64 FMA (K3)
+// issue-rate microbenchmarks.  Measurement support only; not on the data path.
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) popc_peak_kernel(uint32_t* out, int iters, uint32_t seed) {
+  uint32_t x0 = seed + threadIdx.x, x1 = x0 * 3u, x2 = x0 * 5u, x3 = x0 * 7u;
+  uint32_t x4 = x0 * 11u, x5 = x0 * 13u, x6 = x0 * 17u, x7 = x0 * 19u;
+  for (int i = 0; i < iters; ++i) {
+    // 8 independent dependent-chains of POPC: x = popc(x) ^ c keeps the pipe busy without folding
+    x0 = __popc(x0) ^ 0x9E3779B9u; x1 = __popc(x1) ^ 0x7F4A7C15u; x2 = __popc(x2) ^ 0xF39CC060u; x3 = __popc(x3) ^ 0x5CEDC834u;
+    x4 = __popc(x4) ^ 0x1082276Bu; x5 = __popc(x5) ^ 0xF3A5C9E1u; x6 = __popc(x6) ^ 0x3C6EF372u; x7 = __popc(x7) ^ 0xA54FF53Au;
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7;
+}
+
+__global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters, double seed) {
+  double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 0.999999, c = 1e-9;
+  for (int i = 0; i < iters; ++i) {
+    a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+    a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+}  // namespace
+
+extern "C" {
+
+// kind 0: POPC ops/s; kind 1: FP64 FMA/s (one FMA = 2 FLOP).  Best of `reps` launches.
+int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s) {
+  if (!ctx || !ops_per_s) return SEPB_E_INVALID;
+  SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int blocks = ctx->sm_count * 8, threads = 256, iters = kind == 0 ? 4096 : 2048;
+  void* buf = sepb_scratch(ctx, (size_t)blocks * threads * 8);
+  if (!buf) return (int)cudaErrorMemoryAllocation;
+  cudaEvent_t e0, e1;
+  SEPB_CUDA(ctx, cudaEventCreate(&e0));
+  SEPB_CUDA(ctx, cudaEventCreate(&e1));
+  double best = 0;
+  for (int r = 0; r < reps + 1; ++r) {
+    SEPB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+    if (kind == 0) popc_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((uint32_t*)buf, iters, 12345u + r);
+    else dfma_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((double*)buf, iters, 1.0 + r);
+    ctx->launches++;
+    SEPB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+    SEPB_CUDA(ctx, cudaEventSynchronize(e1));
+    float ms = 0;
+    SEPB_CUDA(ctx, cudaEventElapsedTime(&ms, e0, e1));
+    const double ops = (double)blocks * threads * iters * 8.0 / (ms * 1e-3);
+    if (r > 0 && ops > best) best = ops;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *ops_per_s = best;
+  return SEPB_OK;
+}
+
+}  // extern "C"
