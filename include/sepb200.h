@@ -87,6 +87,76 @@ SEPB_API int sepb_match_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const 
                          int32_t* d_n_matches, uint16_t* d_match_from, uint16_t* d_match_to,
                          int32_t* d_n_unique_to);
 
+/* ---- K3: batched PnP-RANSAC + refit ------------------------------------------------------
+ * Replaces the PnP block R/src/myRegistrationVis.cpp:1055-1112: RTAB-Map
+ * util3d::estimateMotion3DTo2D -> cv::solvePnPRansac(useExtrinsicGuess=true, iterations,
+ * reprojError, confidence 0.99, flags=ITERATIVE => 5-point EPnP minimal sets) -> final
+ * ITERATIVE refit on the inliers seeded by the caller's guess, then T = (local * pnp)^-1.
+ * Correspondences come from K2's match lists (ascending From index).  Rectified cameras only
+ * (zero distortion), like the stereo model the reference builds (stereoCamGeometricTools.cpp:77). */
+typedef struct sepb_pnp_params {
+  double fx, fy, cx, cy;  /* intrinsics of the To camera, cam_.left() (stereoCamGeometricTools.cpp:142-143) */
+  int32_t iterations;     /* Vis/Iterations, RTAB-Map default 300 */
+  int32_t min_inliers;    /* Vis/MinInliers = separators_min_inliers (launch default 5); must be >= 5 */
+  double reproj_error;    /* Vis/PnPReprojError, default 2.0 px */
+  double confidence;      /* 0.99, hard-coded in util3d::solvePnPRansac */
+  double guess_rvec[3];   /* (guess * localTransform)^-1 as Rodrigues vector ... */
+  double guess_tvec[3];   /* ... and translation; sepb_pnp_params_init sets the identity guess of pass 1 */
+  double local_R[9];      /* camera localTransform rotation (optical -> base), row-major */
+  double local_t[3];
+} sepb_pnp_params;
+
+/* defaults above + optical->base localTransform + identity guess (stereoCamGeometricTools.cpp:126) */
+SEPB_API void sepb_pnp_params_init(sepb_pnp_params* p, double fx, double fy, double cx, double cy);
+/* set guess_rvec/guess_tvec from a 3x4 row-major transform `guess` (From-base <- To-base), like
+ * estimateMotion3DTo2D: guessCameraFrame = (guess * localTransform)^-1 */
+SEPB_API void sepb_pnp_set_guess(sepb_pnp_params* p, const double* guess3x4);
+
+/* status per pair */
+#define SEPB_PNP_TOO_FEW 0     /* fewer than min_inliers correspondences: null transform, no RANSAC */
+#define SEPB_PNP_OK 1          /* transform valid (success=true in EstTransform.srv) */
+#define SEPB_PNP_NO_MODEL 2    /* RANSAC found no hypothesis with > 4 inliers */
+#define SEPB_PNP_FEW_INLIERS 3 /* inliers < min_inliers */
+
+/* Outputs (device or host according to the entry point):
+ *   status[P] i32, n_inliers[P] i32, pose[P][6] f64 (rvec, tvec of the To camera w.r.t. From base),
+ *   transform[P][12] f32 (3x4 row-major T, From-base <- To-base; zeros when not SEPB_PNP_OK, like
+ *   MsgConversion.cpp:77-80), inlier_mask[P][mask_words] u32 over match-list positions (optional),
+ *   best_hyp[P], iters_run[P] i32 (optional; index of the winning hypothesis, iterations executed).
+ * custom_samples: optional i32 [P][custom_h][5] minimal-sample indices (into the match list)
+ *   replacing the built-in replay of cv::RNG(-1) -- "feed the reference's own indices". */
+SEPB_API int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                                 int n_pairs, const int32_t* d_n_matches, const uint16_t* d_match_from,
+                                 const uint16_t* d_match_to, const int32_t* d_n_unique_to, const sepb_pnp_params* prm,
+                                 const int32_t* d_custom_samples, int custom_h, const double* d_guess,
+                                 int32_t* d_status, int32_t* d_n_inliers, double* d_pose, float* d_transform,
+                                 uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp, int32_t* d_iters_run);
+
+/* ---- fused verification: K2 -> K3 on the device, nothing but ids and results cross PCIe ----
+ * The batch form of StereoCamGeometricTools::estimateTransformation pass 1
+ * (R/src/stereoCamGeometricTools.cpp:122-152): pairs[p] = (from_frame, to_frame).
+ * Host pointers; any output except status may be NULL. */
+typedef struct sepb_verify_out {
+  int32_t* status;       /* [P] */
+  int32_t* n_matches;    /* [P] */
+  int32_t* n_inliers;    /* [P] */
+  double* pose;          /* [P][6] */
+  float* transform;      /* [P][12] */
+  uint16_t* match_from;  /* [P][max_feat] */
+  uint16_t* match_to;    /* [P][max_feat] */
+  uint32_t* inlier_mask; /* [P][(max_feat+31)/32] */
+  int32_t* best_hyp;     /* [P] */
+  int32_t* iters_run;    /* [P] */
+} sepb_verify_out;
+
+SEPB_API int sepb_verify_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                               int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                               const int32_t* custom_samples, int custom_h, sepb_verify_out* out);
+/* same, everything (pairs and the arrays inside `out`) in device memory, asynchronous on the ctx stream */
+SEPB_API int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                                   int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                                   const int32_t* d_custom_samples, int custom_h, const sepb_verify_out* d_out);
+
 /* ---- measurement support (roofline denominators not in MEASURED_PEAKS.json) ----------------
  * kind 0: POPC instructions/s (K2's bounding pipe), kind 1: FP64 FMA/s (K3's).  Best of reps. */
 SEPB_API int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s);

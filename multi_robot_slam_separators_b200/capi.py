@@ -35,6 +35,28 @@ class MatchParams(C.Structure):
     _fields_ = [("nndr", C.c_float), ("nndr_strict", C.c_int32)]
 
 
+class PnpParams(C.Structure):
+    _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double),
+                ("iterations", C.c_int32), ("min_inliers", C.c_int32), ("reproj_error", C.c_double),
+                ("confidence", C.c_double), ("guess_rvec", C.c_double * 3), ("guess_tvec", C.c_double * 3),
+                ("local_R", C.c_double * 9), ("local_t", C.c_double * 3)]
+
+
+class VerifyOut(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("status", "n_matches", "n_inliers", "pose", "transform", "match_from",
+                                          "match_to", "inlier_mask", "best_hyp", "iters_run")]
+
+
+def pnp_params(fx, fy, cx, cy, iterations=300, min_inliers=5, reproj_error=2.0, confidence=0.99, guess=None):
+    p = PnpParams()
+    lib().sepb_pnp_params_init(C.byref(p), fx, fy, cx, cy)
+    p.iterations, p.min_inliers, p.reproj_error, p.confidence = iterations, min_inliers, reproj_error, confidence
+    if guess is not None:
+        g = np.ascontiguousarray(np.asarray(guess, dtype=np.float64)[:3, :4])
+        lib().sepb_pnp_set_guess(C.byref(p), _ptr(g))
+    return p
+
+
 def _declare(L):
     vp, i32, i64 = C.c_void_p, C.c_int, C.c_int64
     L.sepb_ctx_create.argtypes = [i32, C.POINTER(vp)]
@@ -59,6 +81,18 @@ def _declare(L):
     L.sepb_frames_upload.restype = i32
     L.sepb_measure_peak.argtypes = [vp, i32, i32, C.POINTER(C.c_double)]
     L.sepb_measure_peak.restype = i32
+    L.sepb_pnp_params_init.argtypes = [C.POINTER(PnpParams), C.c_double, C.c_double, C.c_double, C.c_double]
+    L.sepb_pnp_params_init.restype = None
+    L.sepb_pnp_set_guess.argtypes = [C.POINTER(PnpParams), vp]
+    L.sepb_pnp_set_guess.restype = None
+    L.sepb_pnp_ransac_dev.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, vp, C.POINTER(PnpParams), vp, i32, vp,
+                                      vp, vp, vp, vp, vp, i32, vp, vp]
+    L.sepb_pnp_ransac_dev.restype = i32
+    for name in ("sepb_verify_pairs", "sepb_verify_pairs_dev"):
+        f = getattr(L, name)
+        f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), C.POINTER(PnpParams), vp, i32,
+                      C.POINTER(VerifyOut)]
+        f.restype = i32
     for name in ("sepb_match_pairs", "sepb_match_pairs_dev"):
         f = getattr(L, name)
         f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), vp, vp, vp, vp, vp, vp]
@@ -175,3 +209,31 @@ def match_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, nnd
                                      _ptr(n_unique)))
     return dict(knn_idx=knn_idx, knn_dist=knn_dist, n_matches=n_matches, match_from=mf, match_to=mt,
                 n_unique_to=n_unique)
+
+
+def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pnp: PnpParams, nndr=0.8, strict=False,
+                 custom_samples=None):
+    """Host-buffer fused K2 -> K3 call (estimate_transformation pass 1 for a batch of pairs)."""
+    pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+    P, F = pairs.shape[0], frames_from.max_feat
+    res = dict(status=np.zeros(P, np.int32), n_matches=np.zeros(P, np.int32), n_inliers=np.zeros(P, np.int32),
+               pose=np.zeros((P, 6), np.float64), transform=np.zeros((P, 12), np.float32),
+               match_from=np.zeros((P, F), np.uint16), match_to=np.zeros((P, F), np.uint16),
+               inlier_mask=np.zeros((P, (F + 31) // 32), np.uint32), best_hyp=np.zeros(P, np.int32),
+               iters_run=np.zeros(P, np.int32))
+    out = VerifyOut(**{k: v.ctypes.data for k, v in res.items()})
+    cs, ch = None, 0
+    if custom_samples is not None:
+        cs = np.ascontiguousarray(custom_samples, dtype=np.int32)
+        assert cs.ndim == 3 and cs.shape[0] == P and cs.shape[2] == 5
+        ch = cs.shape[1]
+    mp = MatchParams(nndr, 1 if strict else 0)
+    ctx.check(lib().sepb_verify_pairs(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(mp), C.byref(pnp),
+                                      _ptr(cs), ch, C.byref(out)))
+    return res
+
+
+def inlier_indices(mask_row, n_matches):
+    """bitmask over match-list positions -> ascending index array"""
+    bits = np.unpackbits(mask_row.view(np.uint8), bitorder="little")[:n_matches]
+    return np.nonzero(bits)[0].astype(np.int32)

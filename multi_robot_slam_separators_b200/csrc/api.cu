@@ -36,6 +36,7 @@ void sepb_ctx_destroy(sepb_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   if (ctx->scratch) cudaFree(ctx->scratch);
+  if (ctx->table) cudaFree(ctx->table);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

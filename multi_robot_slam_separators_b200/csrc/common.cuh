@@ -20,6 +20,9 @@ struct sepb_ctx {
   void* scratch = nullptr;
   size_t scratch_bytes = 0;
   int sm_count = 148;
+  // cv::RNG(-1) minimal-sample index table [count][table_h][5] (K3)
+  uint16_t* table = nullptr;
+  int table_m = -1, table_h = 0;
 };
 
 struct sepb_frames {
@@ -96,3 +99,12 @@ int sepb_launch_hamming_match(sepb_ctx* ctx, FramesView from, FramesView to, con
                               float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist,
                               int32_t* d_n_matches, uint16_t* d_match_from, uint16_t* d_match_to,
                               int32_t* d_n_unique_to);
+
+int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H);
+int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                           const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,
+                           const int32_t* d_n_unique_to, const uint16_t* d_table, int table_h,
+                           const int32_t* d_custom_samples, int custom_h, const double* d_guess,
+                           const sepb_pnp_params* p, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
+                           float* d_transform, uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp,
+                           int32_t* d_iters_run);

@@ -1,0 +1,199 @@
+// Double-precision small-matrix routines that replay, operation for operation, the arithmetic
+// cv::solvePnPRansac executes per minimal sample (OpenCV 4.x calib3d / core, reached from
+// R/src/myRegistrationVis.cpp:1077 through RTAB-Map's util3d::estimateMotion3DTo2D):
+//   * cv::SVD for matrices with < 25 rows  -> OpenCV's own one-sided Jacobi (JacobiSVDImpl_)
+//   * cv::solve / cv::invert with DECOMP_SVD -> the same SVD + SVBkSb back-substitution
+//   * epnp::compute_pose (control points, barycentric alphas, M^T M null space, 3 beta
+//     initialisations + Gauss-Newton, Procrustes R|t), cv::Rodrigues, cv::projectPoints.
+// The ORDER of every +,-,*,/,sqrt matters: for 5 points M^T M has an exactly 2-dimensional null space
+// whose basis is decided by rounding noise, and EPnP's linearisation depends on that basis
+// (measured: re-orienting it moves ~15 % of hypothesis poses by > 1e-4).  The translation unit that
+// includes this header is compiled with -fmad=false so that no multiply-add is contracted, matching
+// the x86-64 SSE2 build of cv2.  Written __host__ __device__ so the same text can be checked against
+// cv2 on the CPU by tests/host_harness (test-only build; the product path is the CUDA kernel).
+//
+// Storage: `Heap` is a strided view of per-thread scratch (stride 32 doubles in shared memory so
+// that the 32 lanes of a warp hit 32 different banks; stride 1 on the host).
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define CVM_HD __host__ __device__
+#define CVM_NOINLINE __noinline__
+#else
+#define CVM_HD
+#define CVM_NOINLINE __attribute__((noinline))
+#endif
+
+namespace cvm {
+
+constexpr double kDblEps = 2.220446049250313e-16;
+constexpr double kDblMin = 2.2250738585072014e-308;
+
+struct Intrinsics {
+  double fx, fy, cx, cy;
+};
+
+struct Heap {
+  double* p;
+  int stride;
+  CVM_HD double& operator[](int i) const { return p[(size_t)i * stride]; }
+  CVM_HD Heap at(int off) const { return Heap{p + (size_t)off * stride, stride}; }
+};
+
+// cv::RNG (multiply-with-carry)
+struct Rng {
+  uint64_t state;
+  CVM_HD explicit Rng(uint64_t s) : state(s) {}
+  CVM_HD uint32_t next() {
+    state = (uint64_t)(uint32_t)state * 4164903690ULL + (state >> 32);
+    return (uint32_t)state;
+  }
+};
+
+// file-local hypot of OpenCV's lapack.cpp (not libm's)
+CVM_HD inline double cv_hypot(double a, double b) {
+  a = fabs(a);
+  b = fabs(b);
+  if (a > b) {
+    b /= a;
+    return a * sqrt(1 + b * b);
+  }
+  if (b > 0) {
+    a /= b;
+    return b * sqrt(1 + a * a);
+  }
+  return 0;
+}
+
+// JacobiSVDImpl_<double>: At is n rows of length m (row r at At[r*m + k]); on return rows of At are the
+// unit left singular vectors of A = At^T, W descending, Vt (n x n, optional) the right vectors.
+// n1 = number of rows to normalise / complete (== n at every call site on this path).
+CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt, bool want_v, int m, int n) {
+  const double eps = kDblEps * 10;
+  for (int i = 0; i < n; ++i) {
+    double sd = 0;
+    for (int k = 0; k < m; ++k) {
+      const double t = At[i * m + k];
+      sd += t * t;
+    }
+    W[i] = sd;
+    if (want_v) {
+      for (int k = 0; k < n; ++k) Vt[i * n + k] = 0;
+      Vt[i * n + i] = 1;
+    }
+  }
+  const int max_iter = m > 30 ? m : 30;
+  for (int iter = 0; iter < max_iter; ++iter) {
+    bool changed = false;
+    for (int i = 0; i < n - 1; ++i)
+      for (int j = i + 1; j < n; ++j) {
+        const Heap Ai = At.at(i * m), Aj = At.at(j * m);
+        double a = W[i], p = 0, b = W[j];
+        for (int k = 0; k < m; ++k) p += Ai[k] * Aj[k];
+        if (fabs(p) <= eps * sqrt(a * b)) continue;
+        p *= 2;
+        const double beta = a - b, gamma = cv_hypot(p, beta);
+        double c, s;
+        if (beta < 0) {
+          const double delta = (gamma - beta) * 0.5;
+          s = sqrt(delta / gamma);
+          c = p / (gamma * s * 2);
+        } else {
+          c = sqrt((gamma + beta) / (gamma * 2));
+          s = p / (gamma * c * 2);
+        }
+        a = b = 0;
+        for (int k = 0; k < m; ++k) {
+          const double x = Ai[k], y = Aj[k];
+          const double t0 = c * x + s * y;
+          const double t1 = -s * x + c * y;
+          Ai[k] = t0;
+          Aj[k] = t1;
+          a += t0 * t0;
+          b += t1 * t1;
+        }
+        W[i] = a;
+        W[j] = b;
+        changed = true;
+        if (want_v) {
+          const Heap Vi = Vt.at(i * n), Vj = Vt.at(j * n);
+          for (int k = 0; k < n; ++k) {
+            const double x = Vi[k], y = Vj[k];
+            Vi[k] = c * x + s * y;
+            Vj[k] = -s * x + c * y;
+          }
+        }
+      }
+    if (!changed) break;
+  }
+  for (int i = 0; i < n; ++i) {
+    double sd = 0;
+    for (int k = 0; k < m; ++k) {
+      const double t = At[i * m + k];
+      sd += t * t;
+    }
+    W[i] = sqrt(sd);
+  }
+  for (int i = 0; i < n - 1; ++i) {
+    int j = i;
+    for (int k = i + 1; k < n; ++k)
+      if (W[j] < W[k]) j = k;
+    if (i != j) {
+      double t = W[i]; W[i] = W[j]; W[j] = t;
+      for (int k = 0; k < m; ++k) { t = At[i * m + k]; At[i * m + k] = At[j * m + k]; At[j * m + k] = t; }
+      if (want_v)
+        for (int k = 0; k < n; ++k) { t = Vt[i * n + k]; Vt[i * n + k] = Vt[j * n + k]; Vt[j * n + k] = t; }
+    }
+  }
+  Rng rng(0x12345678);
+  for (int i = 0; i < n; ++i) {
+    double sd = W[i];
+    for (int ii = 0; ii < 100 && sd <= kDblMin; ++ii) {
+      // zero singular value: random +-1/m vector, orthogonalised against the previous rows
+      const double val0 = 1. / m;
+      for (int k = 0; k < m; ++k) At[i * m + k] = (rng.next() & 256) != 0 ? val0 : -val0;
+      for (int it = 0; it < 2; ++it)
+        for (int j = 0; j < i; ++j) {
+          sd = 0;
+          for (int k = 0; k < m; ++k) sd += At[i * m + k] * At[j * m + k];
+          double asum = 0;
+          for (int k = 0; k < m; ++k) {
+            const double t = At[i * m + k] - sd * At[j * m + k];
+            At[i * m + k] = t;
+            asum += fabs(t);
+          }
+          asum = asum > eps * 100 ? 1 / asum : 0;
+          for (int k = 0; k < m; ++k) At[i * m + k] *= asum;
+        }
+      sd = 0;
+      for (int k = 0; k < m; ++k) {
+        const double t = At[i * m + k];
+        sd += t * t;
+      }
+      sd = sqrt(sd);
+    }
+    const double s = sd > kDblMin ? 1 / sd : 0.;
+    for (int k = 0; k < m; ++k) At[i * m + k] *= s;
+  }
+}
+
+// SVBkSb, one right-hand side: x[n] = V diag(1/w) U^T b, with U^T = rows of At (n x m), Vt n x n.
+CVM_HD inline void svd_backsubst(Heap At, Heap W, Heap Vt, int m, int n, const double* b, double* x) {
+  double threshold = 0;
+  for (int i = 0; i < n; ++i) threshold += W[i];
+  threshold *= kDblEps * 2;
+  for (int k = 0; k < n; ++k) x[k] = 0;
+  for (int i = 0; i < n; ++i) {
+    double wi = W[i];
+    if (fabs(wi) <= threshold) continue;
+    wi = 1 / wi;
+    double s = 0;
+    for (int k = 0; k < m; ++k) s += At[i * m + k] * b[k];
+    s *= wi;
+    for (int k = 0; k < n; ++k) x[k] = x[k] + s * Vt[i * n + k];
+  }
+}
+
+}  // namespace cvm

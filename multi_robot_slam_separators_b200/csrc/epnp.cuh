@@ -1,0 +1,377 @@
+// 5-point EPnP minimal solver: operation-for-operation replay of cv::solvePnP(SOLVEPNP_EPNP) as
+// PnPRansacCallback::runKernel reaches it (undistortPoints -> epnp::compute_pose), see cvmath.cuh.
+// Per-thread scratch lives in a `cvm::Heap` of kEpnpHeap doubles:
+//   [0,144)   12x12 M^T M / its Jacobi sweep; afterwards rows 8..11 ([96,144)) are the null-space
+//             vectors, [0,60) holds L_6x10 and [60,96) is small-SVD scratch
+//   [144,164) barycentric alphas (5x4)      [164,176) control points cws (4x3)
+//   [176,208) W of the big SVD, afterwards W / Vt of the small SVDs
+#pragma once
+#include "cvmath.cuh"
+
+namespace cvm {
+
+constexpr int kEpnpHeap = 208;
+constexpr int kN = 5;  // model points
+
+namespace detail {
+constexpr int H_AT = 0, H_L = 0, H_SAT = 60, H_UT = 96, H_ALPHA = 144, H_CWS = 164, H_W = 176, H_SW = 176,
+              H_SVT = 181;
+
+CVM_HD inline double dot3(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+// cvSolve(A[6 x NC], rho, x, CV_SVD) with A's columns picked from L_6x10
+template <int NC>
+CVM_HD inline void solve_cols(Heap h, const int (&cols)[NC], const double* rho, double* x) {
+  Heap At = h.at(H_SAT), W = h.at(H_SW), Vt = h.at(H_SVT);
+  for (int c = 0; c < NC; ++c)
+    for (int r = 0; r < 6; ++r) At[c * 6 + r] = h[H_L + r * 10 + cols[c]];
+  jacobi_svd(At, W, Vt, true, 6, NC);
+  svd_backsubst(At, W, Vt, 6, NC, rho, x);
+}
+
+// epnp::qr_solve for the 6x4 Gauss-Newton system (A row-major 6x4, b[6]) -> X[4]; false if singular
+CVM_HD inline bool qr_solve_6x4(double* A, double* b, double* X) {
+  const int nr = 6, nc = 4;
+  double A1[4], A2[4];
+  for (int k = 0; k < nc; ++k) {
+    const int kk = k * nc + k;
+    int p = kk;
+    double eta = fabs(A[p]);
+    for (int i = k + 1; i < nr; ++i) {  // (sic) scans rows k..nr-2
+      const double elt = fabs(A[p]);
+      if (eta < elt) eta = elt;
+      p += nc;
+    }
+    if (eta == 0) return false;
+    const double inv_eta = 1. / eta;
+    double sum2 = 0;
+    p = kk;
+    for (int i = k; i < nr; ++i) {
+      A[p] *= inv_eta;
+      sum2 += A[p] * A[p];
+      p += nc;
+    }
+    double sigma = sqrt(sum2);
+    if (A[kk] < 0) sigma = -sigma;
+    A[kk] += sigma;
+    A1[k] = sigma * A[kk];
+    A2[k] = -eta * sigma;
+    for (int j = k + 1; j < nc; ++j) {
+      double sum = 0;
+      p = kk;
+      for (int i = k; i < nr; ++i) {
+        sum += A[p] * A[p + j - k];
+        p += nc;
+      }
+      const double tau = sum / A1[k];
+      p = kk;
+      for (int i = k; i < nr; ++i) {
+        A[p + j - k] -= tau * A[p];
+        p += nc;
+      }
+    }
+  }
+  for (int j = 0; j < nc; ++j) {
+    const int jj = j * nc + j;
+    double tau = 0;
+    int p = jj;
+    for (int i = j; i < nr; ++i) {
+      tau += A[p] * b[i];
+      p += nc;
+    }
+    tau /= A1[j];
+    p = jj;
+    for (int i = j; i < nr; ++i) {
+      b[i] -= tau * A[p];
+      p += nc;
+    }
+  }
+  X[nc - 1] = b[nc - 1] / A2[nc - 1];
+  for (int i = nc - 2; i >= 0; --i) {
+    double sum = 0;
+    int p = i * nc + (i + 1);
+    for (int j = i + 1; j < nc; ++j) {
+      sum += A[p] * X[j];
+      ++p;
+    }
+    X[i] = (b[i] - sum) / A2[i];
+  }
+  return true;
+}
+
+CVM_HD inline void gauss_newton(Heap h, const double* rho, double* betas) {
+  double x_stale[4] = {0, 0, 0, 0};  // epnp::gauss_newton's local x[4] = {}
+  for (int it = 0; it < 5; ++it) {
+    double A[24], b[6];
+    for (int i = 0; i < 6; ++i) {
+      double r[10];
+      for (int c = 0; c < 10; ++c) r[c] = h[H_L + i * 10 + c];
+      A[i * 4 + 0] = 2 * r[0] * betas[0] + r[1] * betas[1] + r[3] * betas[2] + r[6] * betas[3];
+      A[i * 4 + 1] = r[1] * betas[0] + 2 * r[2] * betas[1] + r[4] * betas[2] + r[7] * betas[3];
+      A[i * 4 + 2] = r[3] * betas[0] + r[4] * betas[1] + 2 * r[5] * betas[2] + r[8] * betas[3];
+      A[i * 4 + 3] = r[6] * betas[0] + r[7] * betas[1] + r[8] * betas[2] + 2 * r[9] * betas[3];
+      b[i] = rho[i] - (r[0] * betas[0] * betas[0] + r[1] * betas[0] * betas[1] + r[2] * betas[1] * betas[1] +
+                       r[3] * betas[0] * betas[2] + r[4] * betas[1] * betas[2] + r[5] * betas[2] * betas[2] +
+                       r[6] * betas[0] * betas[3] + r[7] * betas[1] * betas[3] + r[8] * betas[2] * betas[3] +
+                       r[9] * betas[3] * betas[3]);
+    }
+    double x[4];
+    if (qr_solve_6x4(A, b, x)) {
+      for (int i = 0; i < 4; ++i) x_stale[i] = x[i];
+    }  // singular: qr_solve returns early and X keeps its previous content
+    for (int i = 0; i < 4; ++i) betas[i] += x_stale[i];
+  }
+}
+
+// compute_ccs / compute_pcs / solve_for_sign / estimate_R_and_t / reprojection_error
+CVM_HD inline double compute_R_and_t(Heap h, const float* o, const double* us, const Intrinsics& K, const double* betas,
+                                     double* R, double* t) {
+  double ccs[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+  for (int i = 0; i < 4; ++i) {
+    const int row = H_UT + (3 - i) * 12;  // ut row 11 - i
+    for (int j = 0; j < 4; ++j)
+      for (int k = 0; k < 3; ++k) ccs[j][k] += betas[i] * h[row + 3 * j + k];
+  }
+  double pcs[kN][3];
+  for (int i = 0; i < kN; ++i) {
+    const double a0 = h[H_ALPHA + 4 * i], a1 = h[H_ALPHA + 4 * i + 1], a2 = h[H_ALPHA + 4 * i + 2],
+                 a3 = h[H_ALPHA + 4 * i + 3];
+    for (int j = 0; j < 3; ++j) pcs[i][j] = a0 * ccs[0][j] + a1 * ccs[1][j] + a2 * ccs[2][j] + a3 * ccs[3][j];
+  }
+  if (pcs[0][2] < 0.0) {
+    for (int i = 0; i < kN; ++i)
+      for (int j = 0; j < 3; ++j) pcs[i][j] = -pcs[i][j];
+  }
+  double pc0[3] = {0, 0, 0}, pw0[3] = {0, 0, 0};
+  for (int i = 0; i < kN; ++i)
+    for (int j = 0; j < 3; ++j) {
+      pc0[j] += pcs[i][j];
+      pw0[j] += (double)o[3 * i + j];
+    }
+  for (int j = 0; j < 3; ++j) {
+    pc0[j] /= kN;
+    pw0[j] /= kN;
+  }
+  double abt[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < kN; ++i)
+    for (int j = 0; j < 3; ++j) {
+      abt[3 * j] += (pcs[i][j] - pc0[j]) * ((double)o[3 * i] - pw0[0]);
+      abt[3 * j + 1] += (pcs[i][j] - pc0[j]) * ((double)o[3 * i + 1] - pw0[1]);
+      abt[3 * j + 2] += (pcs[i][j] - pc0[j]) * ((double)o[3 * i + 2] - pw0[2]);
+    }
+  // cvSVD(ABt, D, U, V, MODIFY_A): Jacobi on rows of ABt^T; U(i,c) = At[c][i], V(j,c) = Vt[c][j]
+  Heap At = h.at(H_SAT), W = h.at(H_SW), Vt = h.at(H_SVT);
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) At[c * 3 + r] = abt[3 * r + c];
+  jacobi_svd(At, W, Vt, true, 3, 3);
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j)
+      R[3 * i + j] = At[0 * 3 + i] * Vt[0 * 3 + j] + At[1 * 3 + i] * Vt[1 * 3 + j] + At[2 * 3 + i] * Vt[2 * 3 + j];
+  const double det = R[0] * R[4] * R[8] + R[1] * R[5] * R[6] + R[2] * R[3] * R[7] - R[2] * R[4] * R[6] -
+                     R[1] * R[3] * R[8] - R[0] * R[5] * R[7];
+  if (det < 0) {
+    R[6] = -R[6];
+    R[7] = -R[7];
+    R[8] = -R[8];
+  }
+  t[0] = pc0[0] - dot3(R, pw0);
+  t[1] = pc0[1] - dot3(R + 3, pw0);
+  t[2] = pc0[2] - dot3(R + 6, pw0);
+  double sum2 = 0;
+  for (int i = 0; i < kN; ++i) {
+    const double pw[3] = {(double)o[3 * i], (double)o[3 * i + 1], (double)o[3 * i + 2]};
+    const double Xc = dot3(R, pw) + t[0];
+    const double Yc = dot3(R + 3, pw) + t[1];
+    const double inv_Zc = 1.0 / (dot3(R + 6, pw) + t[2]);
+    const double ue = K.cx + K.fx * Xc * inv_Zc;
+    const double ve = K.cy + K.fy * Yc * inv_Zc;
+    const double u = us[2 * i], v = us[2 * i + 1];
+    sum2 += sqrt((u - ue) * (u - ue) + (v - ve) * (v - ve));
+  }
+  return sum2 / kN;
+}
+}  // namespace detail
+
+// o: 5 object points (f32 xyz), im: 5 image points (f32 pixel uv).  Outputs R (row-major), t.
+CVM_HD inline void epnp5(Heap h, const float* o, const float* im, const Intrinsics& K, double* R, double* t) {
+  using namespace detail;
+  // undistortPoints (no distortion): double math, stored as f32; epnp::init_points rescales in double
+  const double ifx = 1. / K.fx, ify = 1. / K.fy;
+  double us[2 * kN];
+  for (int i = 0; i < kN; ++i) {
+    const float xn = (float)(((double)im[2 * i] - K.cx) * ifx);
+    const float yn = (float)(((double)im[2 * i + 1] - K.cy) * ify);
+    us[2 * i] = (double)xn * K.fx + K.cx;
+    us[2 * i + 1] = (double)yn * K.fy + K.cy;
+  }
+  // ---- choose_control_points
+  double c0[3] = {0, 0, 0};
+  for (int i = 0; i < kN; ++i)
+    for (int j = 0; j < 3; ++j) c0[j] += (double)o[3 * i + j];
+  for (int j = 0; j < 3; ++j) c0[j] /= kN;
+  {
+    // PW0^T PW0 (mulTransposed: upper triangle, sequential over points) then symmetric completion
+    double ptp[9];
+    for (int a = 0; a < 3; ++a)
+      for (int b = a; b < 3; ++b) {
+        double s = 0;
+        for (int k = 0; k < kN; ++k) s += ((double)o[3 * k + a] - c0[a]) * ((double)o[3 * k + b] - c0[b]);
+        ptp[3 * a + b] = s;
+      }
+    ptp[3] = ptp[1]; ptp[6] = ptp[2]; ptp[7] = ptp[5];
+    Heap At = h.at(0), W = h.at(9), Vt = h.at(12);
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) At[c * 3 + r] = ptp[3 * r + c];
+    jacobi_svd(At, W, Vt, true, 3, 3);
+    for (int j = 0; j < 3; ++j) h[H_CWS + j] = c0[j];
+    for (int i = 1; i < 4; ++i) {
+      const double k = sqrt(W[i - 1] / kN);
+      for (int j = 0; j < 3; ++j) h[H_CWS + 3 * i + j] = c0[j] + k * At[(i - 1) * 3 + j];
+    }
+  }
+  // ---- compute_barycentric_coordinates: cvInvert(CC, CV_SVD)
+  {
+    Heap At = h.at(0), W = h.at(9), Vt = h.at(12);
+    // CC[i][j-1] = cws[j][i] - cws[0][i]; Jacobi runs on rows of CC^T: At[c][r] = CC[r][c]
+    for (int i = 0; i < 3; ++i)
+      for (int j = 1; j < 4; ++j) At[(j - 1) * 3 + i] = h[H_CWS + 3 * j + i] - h[H_CWS + i];
+    jacobi_svd(At, W, Vt, true, 3, 3);
+    double ci[9];
+    for (int c = 0; c < 3; ++c) {
+      const double e[3] = {c == 0 ? 1. : 0., c == 1 ? 1. : 0., c == 2 ? 1. : 0.};
+      double x[3];
+      svd_backsubst(At, W, Vt, 3, 3, e, x);
+      ci[c] = x[0]; ci[3 + c] = x[1]; ci[6 + c] = x[2];
+    }
+    for (int i = 0; i < kN; ++i) {
+      const double px = (double)o[3 * i], py = (double)o[3 * i + 1], pz = (double)o[3 * i + 2];
+      double a[4];
+      for (int j = 0; j < 3; ++j)
+        a[1 + j] = ci[3 * j] * (px - h[H_CWS]) + ci[3 * j + 1] * (py - h[H_CWS + 1]) + ci[3 * j + 2] * (pz - h[H_CWS + 2]);
+      a[0] = 1.0 - a[1] - a[2] - a[3];
+      for (int j = 0; j < 4; ++j) h[H_ALPHA + 4 * i + j] = a[j];
+    }
+  }
+  // ---- M^T M (mulTransposed over the 10 x 12 M of fill_M, rows in order u0,v0,u1,v1,...)
+  {
+    Heap At = h.at(H_AT);
+    for (int a = 0; a < 12; ++a)
+      for (int b = a; b < 12; ++b) {
+        double s = 0;
+        const int ka = a / 3, ca = a % 3, kb = b / 3, cb = b % 3;
+        for (int i = 0; i < kN; ++i) {
+          const double aa = h[H_ALPHA + 4 * i + ka], ab = h[H_ALPHA + 4 * i + kb];
+          const double u = us[2 * i], v = us[2 * i + 1];
+          // row 2i: [a*fu, 0, a*(uc-u)], row 2i+1: [0, a*fv, a*(vc-v)]
+          const double m1a = ca == 0 ? aa * K.fx : (ca == 1 ? 0.0 : aa * (K.cx - u));
+          const double m1b = cb == 0 ? ab * K.fx : (cb == 1 ? 0.0 : ab * (K.cx - u));
+          const double m2a = ca == 0 ? 0.0 : (ca == 1 ? aa * K.fy : aa * (K.cy - v));
+          const double m2b = cb == 0 ? 0.0 : (cb == 1 ? ab * K.fy : ab * (K.cy - v));
+          s += m1a * m1b;
+          s += m2a * m2b;
+        }
+        At[a * 12 + b] = s;  // symmetric: row a of MtM^T == row a of MtM
+        At[b * 12 + a] = s;
+      }
+    jacobi_svd(At, h.at(H_W), h.at(H_W), false, 12, 12);
+  }
+  // ---- L_6x10 and rho
+  {
+    double L[60];
+    for (int i = 0; i < 6; ++i) {
+      // pairs (a,b): (0,1),(0,2),(0,3),(1,2),(1,3),(2,3)
+      const int a = i < 3 ? 0 : (i < 5 ? 1 : 2);
+      const int b = i < 3 ? i + 1 : (i < 5 ? i - 1 : 3);
+      double dv[4][3];
+      for (int v = 0; v < 4; ++v) {
+        const int row = H_UT + (3 - v) * 12;
+        for (int c = 0; c < 3; ++c) dv[v][c] = h[row + 3 * a + c] - h[row + 3 * b + c];
+      }
+      L[i * 10 + 0] = dot3(dv[0], dv[0]);
+      L[i * 10 + 1] = 2.0 * dot3(dv[0], dv[1]);
+      L[i * 10 + 2] = dot3(dv[1], dv[1]);
+      L[i * 10 + 3] = 2.0 * dot3(dv[0], dv[2]);
+      L[i * 10 + 4] = 2.0 * dot3(dv[1], dv[2]);
+      L[i * 10 + 5] = dot3(dv[2], dv[2]);
+      L[i * 10 + 6] = 2.0 * dot3(dv[0], dv[3]);
+      L[i * 10 + 7] = 2.0 * dot3(dv[1], dv[3]);
+      L[i * 10 + 8] = 2.0 * dot3(dv[2], dv[3]);
+      L[i * 10 + 9] = dot3(dv[3], dv[3]);
+    }
+    for (int i = 0; i < 60; ++i) h[H_L + i] = L[i];  // rows 0..4 of the swept matrix are dead by now
+  }
+  double rho[6];
+  {
+    double c[4][3];
+    for (int i = 0; i < 4; ++i)
+      for (int j = 0; j < 3; ++j) c[i][j] = h[H_CWS + 3 * i + j];
+    const int pa[6] = {0, 0, 0, 1, 1, 2}, pb[6] = {1, 2, 3, 2, 3, 3};
+    for (int i = 0; i < 6; ++i) {
+      const double d0 = c[pa[i]][0] - c[pb[i]][0], d1 = c[pa[i]][1] - c[pb[i]][1], d2 = c[pa[i]][2] - c[pb[i]][2];
+      rho[i] = d0 * d0 + d1 * d1 + d2 * d2;
+    }
+  }
+  double Rs[3][9], ts[3][3], errs[3];
+  // ---- approx 1: [B11 B12 B13 B14]
+  {
+    const int cols[4] = {0, 1, 3, 6};
+    double b4[4], betas[4];
+    solve_cols<4>(h, cols, rho, b4);
+    if (b4[0] < 0) {
+      betas[0] = sqrt(-b4[0]);
+      betas[1] = -b4[1] / betas[0];
+      betas[2] = -b4[2] / betas[0];
+      betas[3] = -b4[3] / betas[0];
+    } else {
+      betas[0] = sqrt(b4[0]);
+      betas[1] = b4[1] / betas[0];
+      betas[2] = b4[2] / betas[0];
+      betas[3] = b4[3] / betas[0];
+    }
+    gauss_newton(h, rho, betas);
+    errs[0] = compute_R_and_t(h, o, us, K, betas, Rs[0], ts[0]);
+  }
+  // ---- approx 2: [B11 B12 B22]
+  {
+    const int cols[3] = {0, 1, 2};
+    double b3[3], betas[4];
+    solve_cols<3>(h, cols, rho, b3);
+    if (b3[0] < 0) {
+      betas[0] = sqrt(-b3[0]);
+      betas[1] = (b3[2] < 0) ? sqrt(-b3[2]) : 0.0;
+    } else {
+      betas[0] = sqrt(b3[0]);
+      betas[1] = (b3[2] > 0) ? sqrt(b3[2]) : 0.0;
+    }
+    if (b3[1] < 0) betas[0] = -betas[0];
+    betas[2] = 0.0;
+    betas[3] = 0.0;
+    gauss_newton(h, rho, betas);
+    errs[1] = compute_R_and_t(h, o, us, K, betas, Rs[1], ts[1]);
+  }
+  // ---- approx 3: [B11 B12 B22 B13 B23]
+  {
+    const int cols[5] = {0, 1, 2, 3, 4};
+    double b5[5], betas[4];
+    solve_cols<5>(h, cols, rho, b5);
+    if (b5[0] < 0) {
+      betas[0] = sqrt(-b5[0]);
+      betas[1] = (b5[2] < 0) ? sqrt(-b5[2]) : 0.0;
+    } else {
+      betas[0] = sqrt(b5[0]);
+      betas[1] = (b5[2] > 0) ? sqrt(b5[2]) : 0.0;
+    }
+    if (b5[1] < 0) betas[0] = -betas[0];
+    betas[2] = b5[3] / betas[0];
+    betas[3] = 0.0;
+    gauss_newton(h, rho, betas);
+    errs[2] = compute_R_and_t(h, o, us, K, betas, Rs[2], ts[2]);
+  }
+  int N = 0;
+  if (errs[1] < errs[0]) N = 1;
+  if (errs[2] < errs[N]) N = 2;
+  for (int i = 0; i < 9; ++i) R[i] = Rs[N][i];
+  for (int i = 0; i < 3; ++i) t[i] = ts[N][i];
+}
+
+}  // namespace cvm

@@ -1,0 +1,370 @@
+// K3: batched PnP-RANSAC + ITERATIVE refit, one keyframe pair per CTA (one warp).
+//
+// Replaces util3d::estimateMotion3DTo2D -> cv::solvePnPRansac (useExtrinsicGuess, 5-point EPnP
+// minimal sets, confidence 0.99) called at R/src/myRegistrationVis.cpp:1077-1090.
+//
+// cv::solvePnPRansac is a sequential loop, but its hypotheses do not depend on loop state: the
+// RNG stream is consumed unconditionally, so hypothesis h is a pure function of (match count, h).
+// A warp therefore SOLVES 32 consecutive hypotheses at once (one lane each; EPnP's summation order
+// must be replayed serially, see cvmath.cuh, so a hypothesis cannot be split across lanes), then
+// SCORES them one after the other with all 32 lanes striding over the correspondences (warp per
+// hypothesis), applying OpenCV's `goodCount > max(best, 4)` rule and RANSACUpdateNumIters after each
+// one, which reproduces the sequential result exactly and keeps most of its early exit.
+// Compiled with -fmad=false (see build.py): no multiply-add contraction, like the cv2 build.
+#include "common.cuh"
+#include "epnp.cuh"
+#include "pnp_geom.cuh"
+
+namespace {
+
+constexpr int kWarp = 32;
+constexpr int kMaskWords = SEPB_MAX_FEATURES / 32;
+
+struct PnpKernelParams {
+  cvm::Intrinsics K;
+  int iterations;
+  float thr2;          // (float)(reprojError^2)
+  double confidence;
+  int min_inliers;
+  double rvec0[3], tvec0[3];   // guess, camera frame (== (guess * local)^-1)
+  double local_R[9], local_t[3];
+  int table_h;                 // hypotheses per row of the sample table
+};
+
+// getSubset index stream: table[count][h][5]; thread per count value
+__global__ void sample_table_kernel(uint16_t* table, int max_count, int H) {
+  const int count = blockIdx.x * blockDim.x + threadIdx.x;
+  if (count > max_count) return;
+  uint16_t* row = table + (size_t)count * H * 5;
+  if (count < 5) {
+    for (int i = 0; i < H * 5; ++i) row[i] = 0;
+    return;
+  }
+  cvm::Rng rng(0xFFFFFFFFFFFFFFFFULL);
+  for (int h = 0; h < H; ++h) {
+    int idx[5];
+    for (int i = 0; i < 5; ++i) {
+      int v;
+      bool dup;
+      do {
+        v = (int)(rng.next() % (unsigned)count);
+        dup = false;
+        for (int j = 0; j < i; ++j) dup |= idx[j] == v;
+      } while (dup);
+      idx[i] = v;
+      row[h * 5 + i] = (uint16_t)v;
+    }
+  }
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+  return v;
+}
+
+struct Corr {  // correspondence accessor of one pair
+  const float* kp3d;   // From frame 3-D points
+  const float* kp2d;   // To frame pixels
+  const uint16_t* mf;
+  const uint16_t* mt;
+  __device__ __forceinline__ void load(int m, float* o3, float* i2) const {
+    const int f = mf[m], t = mt[m];
+    o3[0] = kp3d[3 * f]; o3[1] = kp3d[3 * f + 1]; o3[2] = kp3d[3 * f + 2];
+    i2[0] = kp2d[2 * t]; i2[1] = kp2d[2 * t + 1];
+  }
+};
+
+// residuals / normal equations of the ITERATIVE refit over the inlier set, warp-cooperative
+__device__ void lm_accumulate(const Corr& cr, const uint32_t* mask, int M, const cvm::Intrinsics& K, const double* param,
+                              bool want_jac, double* JtJ /*21 upper*/, double* JtE /*6*/, double& err2) {
+  const int lane = threadIdx.x & 31;
+  double R[9], dRdr[27];
+  cvm::rodrigues_vec_to_mat(param, R, want_jac ? dRdr : nullptr);
+  double aJ[21], aE[6], e2 = 0;
+#pragma unroll
+  for (int i = 0; i < 21; ++i) aJ[i] = 0;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) aE[i] = 0;
+  for (int base = 0; base < M; base += 32) {
+    const int m = base + lane;
+    if (m >= M || !((mask[base >> 5] >> lane) & 1u)) continue;
+    float o3[3], i2[2];
+    cr.load(m, o3, i2);
+    const double X = o3[0], Y = o3[1], Z = o3[2];
+    double x = R[0] * X + R[1] * Y + R[2] * Z + param[3];
+    double y = R[3] * X + R[4] * Y + R[5] * Z + param[4];
+    double z = R[6] * X + R[7] * Y + R[8] * Z + param[5];
+    z = z ? 1. / z : 1;
+    x *= z;
+    y *= z;
+    const double ex = (x * K.fx + K.cx) - (double)i2[0], ey = (y * K.fy + K.cy) - (double)i2[1];
+    e2 += ex * ex + ey * ey;
+    if (want_jac) {
+      double jx[6], jy[6];
+      jx[3] = K.fx * z; jx[4] = 0; jx[5] = K.fx * (-x * z);
+      jy[3] = 0; jy[4] = K.fy * z; jy[5] = K.fy * (-y * z);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const double* d = dRdr + 9 * j;
+        const double dx0 = X * d[0] + Y * d[1] + Z * d[2];
+        const double dy0 = X * d[3] + Y * d[4] + Z * d[5];
+        const double dz0 = X * d[6] + Y * d[7] + Z * d[8];
+        jx[j] = K.fx * (z * (dx0 - x * dz0));
+        jy[j] = K.fy * (z * (dy0 - y * dz0));
+      }
+      int k = 0;
+#pragma unroll
+      for (int a = 0; a < 6; ++a) {
+        aE[a] += jx[a] * ex + jy[a] * ey;
+#pragma unroll
+        for (int b = a; b < 6; ++b) aJ[k++] += jx[a] * jx[b] + jy[a] * jy[b];
+      }
+    }
+  }
+  err2 = warp_sum(e2);
+  if (want_jac) {
+#pragma unroll
+    for (int i = 0; i < 21; ++i) JtJ[i] = warp_sum(aJ[i]);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) JtE[i] = warp_sum(aE[i]);
+  }
+}
+
+// CvLevMarq::step(): (JtJ with diag *= 1 + lambda) x = JtErr by SVD; param = prev - x
+__device__ void lm_step(cvm::Heap h, const double* JtJ, const double* JtE, int lambda_lg10, const double* prev,
+                        double* param) {
+  const double lambda = exp(lambda_lg10 * log(10.));
+  cvm::Heap At = h.at(0), W = h.at(36), Vt = h.at(42);
+  int k = 0;
+  for (int a = 0; a < 6; ++a)
+    for (int b = a; b < 6; ++b) {
+      const double v = JtJ[k++];
+      At[a * 6 + b] = v;
+      At[b * 6 + a] = v;
+    }
+  for (int a = 0; a < 6; ++a) At[a * 6 + a] = At[a * 6 + a] * (1. + lambda);
+  cvm::jacobi_svd(At, W, Vt, true, 6, 6);
+  double x[6];
+  cvm::svd_backsubst(At, W, Vt, 6, 6, JtE, x);
+  for (int i = 0; i < 6; ++i) param[i] = prev[i] - x[i];
+}
+
+__global__ void __launch_bounds__(kWarp)
+pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs,
+                  const int32_t* __restrict__ n_matches, const uint16_t* __restrict__ match_from,
+                  const uint16_t* __restrict__ match_to, const int32_t* __restrict__ n_unique_to,
+                  const uint16_t* __restrict__ table, const int32_t* __restrict__ custom_samples, int custom_h,
+                  const double* __restrict__ guess /*[P][6] or null*/, PnpKernelParams prm,
+                  int32_t* __restrict__ status, int32_t* __restrict__ n_inliers, double* __restrict__ pose /*[P][6]*/,
+                  float* __restrict__ transform /*[P][12]*/, uint32_t* __restrict__ inlier_mask, int mask_words,
+                  int32_t* __restrict__ best_hyp, int32_t* __restrict__ iters_run) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  double* heap_base = reinterpret_cast<double*>(smem_raw);
+  uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)cvm::kEpnpHeap * 32 * 8);  // 2 * kMaskWords
+  const int lane = threadIdx.x;
+  const int pair = blockIdx.x;
+  if (pair >= n_pairs) return;
+  const cvm::Heap heap{heap_base + lane, 32};
+  const int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
+  const int M = n_matches[pair];
+  const int nf = from.count[fi];
+  const int nu = n_unique_to ? n_unique_to[pair] : M;
+  Corr cr{from.kp3d + (size_t)fi * from.max_feat * 3, to.kp2d + (size_t)ti * to.max_feat * 2,
+          match_from + (size_t)pair * from.max_feat, match_to + (size_t)pair * from.max_feat};
+  double g[6];
+  for (int i = 0; i < 3; ++i) {
+    g[i] = guess ? guess[6 * pair + i] : prm.rvec0[i];
+    g[3 + i] = guess ? guess[6 * pair + 3 + i] : prm.tvec0[i];
+  }
+  uint32_t* out_mask = inlier_mask ? inlier_mask + (size_t)pair * mask_words : nullptr;
+  if (out_mask)
+    for (int w = lane; w < mask_words; w += 32) out_mask[w] = 0;
+
+  auto finish = [&](int st, int ninl, const double* p6, int bh, int it) {
+    if (lane == 0) {
+      status[pair] = st;
+      n_inliers[pair] = ninl;
+      if (best_hyp) best_hyp[pair] = bh;
+      if (iters_run) iters_run[pair] = it;
+      for (int i = 0; i < 6; ++i) pose[6 * pair + i] = p6[i];
+      float* T = transform + 12 * (size_t)pair;
+      if (st == 1) {
+        // T = (local * [R|t])^-1  (maps To-base coordinates into the From base frame)
+        double R[9], RP[9], tP[3];
+        cvm::rodrigues_vec_to_mat(p6, R, nullptr);
+        for (int i = 0; i < 3; ++i) {
+          for (int j = 0; j < 3; ++j)
+            RP[3 * i + j] = prm.local_R[3 * i] * R[j] + prm.local_R[3 * i + 1] * R[3 + j] + prm.local_R[3 * i + 2] * R[6 + j];
+          tP[i] = prm.local_R[3 * i] * p6[3] + prm.local_R[3 * i + 1] * p6[4] + prm.local_R[3 * i + 2] * p6[5] + prm.local_t[i];
+        }
+        for (int i = 0; i < 3; ++i) {
+          for (int j = 0; j < 3; ++j) T[4 * i + j] = (float)RP[3 * j + i];
+          T[4 * i + 3] = (float)(-(RP[i] * tP[0] + RP[3 + i] * tP[1] + RP[6 + i] * tP[2]));
+        }
+      } else {
+        for (int i = 0; i < 12; ++i) T[i] = 0.f;  // null transform (Transform::isNull())
+      }
+    }
+  };
+
+  // myRegistrationVis.cpp:1069-1070 and estimateMotion3DTo2D: need >= minInliers on every side
+  if (M < prm.min_inliers || nf < prm.min_inliers || nu < prm.min_inliers || M < 5) {
+    finish(0, 0, g, -1, 0);
+    return;
+  }
+
+  if (M == 5) {  // count == modelPoints: one EPnP over all five, no refit, all inliers
+    float o[15], im[10];
+    for (int i = 0; i < 5; ++i) cr.load(i, o + 3 * i, im + 2 * i);
+    double R[9], p6[6];
+    cvm::epnp5(heap, o, im, prm.K, R, p6 + 3);
+    cvm::rodrigues_mat_to_vec(heap, R, p6);
+    if (out_mask && lane == 0) out_mask[0] = 0x1Fu;
+    finish(5 >= prm.min_inliers ? 1 : 3, 5, p6, 0, 1);
+    return;
+  }
+
+  int niters = prm.iterations > 1 ? prm.iterations : 1;
+  int best_good = 0, best_h = -1, cur = 0, hk = 0;
+  for (int chunk = 0; chunk < niters; chunk += 32) {
+    // ---- solve: lane <-> hypothesis
+    int h = chunk + lane;
+    if (h >= niters) h = niters - 1;
+    float o[15], im[10];
+    for (int i = 0; i < 5; ++i) {
+      const int s = custom_samples ? custom_samples[((size_t)pair * custom_h + h) * 5 + i]
+                                   : table[((size_t)M * prm.table_h + h) * 5 + i];
+      cr.load(min(max(s, 0), M - 1), o + 3 * i, im + 2 * i);
+    }
+    double Rh[9], th[3];
+    {
+      double R0[9], rv[3];
+      cvm::epnp5(heap, o, im, prm.K, R0, th);
+      cvm::rodrigues_mat_to_vec(heap, R0, rv);   // runKernel hands the model on as rvec
+      cvm::rodrigues_vec_to_mat(rv, Rh, nullptr);  // projectPoints turns it back into a matrix
+    }
+    __syncwarp();
+    // ---- score: warp <-> hypothesis, in RANSAC order
+    for (int k = 0; k < 32; ++k) {
+      hk = chunk + k;
+      if (hk >= niters) break;
+      double R[9], t[3];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) R[i] = __shfl_sync(0xFFFFFFFFu, Rh[i], k);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) t[i] = __shfl_sync(0xFFFFFFFFu, th[i], k);
+      uint32_t* cand = s_mask + (cur ^ 1) * kMaskWords;
+      int good = 0;
+      for (int base = 0; base < M; base += 32) {
+        const int m = base + lane;
+        bool inl = false;
+        if (m < M) {
+          float o3[3], i2[2];
+          cr.load(m, o3, i2);
+          inl = cvm::reproj_err_f32(R, t, prm.K, o3, i2) <= prm.thr2;
+        }
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, inl);
+        if (lane == 0) cand[base >> 5] = b;
+        good += __popc(b);
+      }
+      if (good > max(best_good, 4)) {
+        cur ^= 1;
+        best_good = good;
+        best_h = hk;
+        niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, 5, niters);
+      }
+      hk = hk + 1;
+    }
+  }
+  __syncwarp();
+  if (best_h < 0) {
+    finish(2, 0, g, -1, hk);
+    return;
+  }
+  const uint32_t* best = s_mask + cur * kMaskWords;
+  if (out_mask)
+    for (int w = lane; w < (M + 31) / 32; w += 32) out_mask[w] = best[w];
+
+  // ---- refit: solvePnP(inliers, ITERATIVE, useExtrinsicGuess) == CvLevMarq from the caller's guess
+  double param[6], prev[6], JtJ[21], JtE[6];
+  for (int i = 0; i < 6; ++i) param[i] = prev[i] = g[i];
+  int lambda_lg10 = -3, iters = 0;
+  double err2 = 0, prev_err_norm = 0;
+  const int max_iter = 20;
+  const double eps = 1.1920928955078125e-07;  // FLT_EPSILON
+  lm_accumulate(cr, best, M, prm.K, param, true, JtJ, JtE, err2);  // STARTED -> CALC_J
+  for (;;) {
+    // CALC_J
+    for (int i = 0; i < 6; ++i) prev[i] = param[i];
+    lm_step(heap, JtJ, JtE, lambda_lg10, prev, param);
+    if (iters == 0) prev_err_norm = sqrt(err2);
+    double dJ[21], dE[6];
+    lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
+    // CHECK_ERR
+    double err_norm = sqrt(err2);
+    while (err_norm > prev_err_norm && ++lambda_lg10 <= 16) {
+      lm_step(heap, JtJ, JtE, lambda_lg10, prev, param);
+      lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
+      err_norm = sqrt(err2);
+    }
+    lambda_lg10 = max(lambda_lg10 - 1, -16);
+    double dn = 0, pn = 0;
+    for (int i = 0; i < 6; ++i) {
+      dn += (param[i] - prev[i]) * (param[i] - prev[i]);
+      pn += prev[i] * prev[i];
+    }
+    if (++iters >= max_iter || sqrt(dn) / (sqrt(pn) + cvm::kDblEps) < eps) break;
+    prev_err_norm = err_norm;
+    lm_accumulate(cr, best, M, prm.K, param, true, JtJ, JtE, err2);
+  }
+  finish(best_good >= prm.min_inliers ? 1 : 3, best_good, param, best_h, hk);
+}
+
+}  // namespace
+
+struct PnpLaunchArgs;  // (reserved)
+
+int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H) {
+  const int threads = 128;
+  sample_table_kernel<<<(max_count + 1 + threads - 1) / threads, threads, 0, ctx->stream>>>(d_table, max_count, H);
+  ctx->launches++;
+  SEPB_CUDA(ctx, cudaGetLastError());
+  return SEPB_OK;
+}
+
+int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                           const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,
+                           const int32_t* d_n_unique_to, const uint16_t* d_table, int table_h,
+                           const int32_t* d_custom_samples, int custom_h, const double* d_guess,
+                           const sepb_pnp_params* p, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
+                           float* d_transform, uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp,
+                           int32_t* d_iters_run) {
+  if (n_pairs == 0) return SEPB_OK;
+  PnpKernelParams k;
+  k.K = cvm::Intrinsics{p->fx, p->fy, p->cx, p->cy};
+  k.iterations = p->iterations;
+  k.thr2 = (float)(p->reproj_error * p->reproj_error);
+  k.confidence = p->confidence;
+  k.min_inliers = p->min_inliers;
+  for (int i = 0; i < 3; ++i) {
+    k.rvec0[i] = p->guess_rvec[i];
+    k.tvec0[i] = p->guess_tvec[i];
+    k.local_t[i] = p->local_t[i];
+  }
+  for (int i = 0; i < 9; ++i) k.local_R[i] = p->local_R[i];
+  k.table_h = table_h;
+  const size_t smem = (size_t)cvm::kEpnpHeap * 32 * 8 + 2 * kMaskWords * 4;
+  static bool configured = false;
+  if (!configured) {
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  pnp_ransac_kernel<<<n_pairs, kWarp, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, d_n_matches, d_match_from,
+                                                          d_match_to, d_n_unique_to, d_table, d_custom_samples, custom_h,
+                                                          d_guess, k, d_status, d_n_inliers, d_pose, d_transform,
+                                                          d_inlier_mask, mask_words, d_best_hyp, d_iters_run);
+  ctx->launches++;
+  SEPB_CUDA(ctx, cudaGetLastError());
+  return SEPB_OK;
+}

@@ -275,6 +275,7 @@ class EPnP:
     @staticmethod
     def gauss_newton(L, rho, betas):
         betas = list(betas)
+        stale = [0.0] * 4
         for _ in range(5):
             A = []
             b = []
@@ -299,9 +300,9 @@ class EPnP:
                     r[9] * betas[3] * betas[3]))
             x = _qr_solve(A, b, 6, 4)
             if x is None:
-                # qr_solve returns early leaving X untouched (zeros on first use / stale later)
-                x = getattr(EPnP, "_stale_x", [0.0] * 4)
-            EPnP._stale_x = x
+                # qr_solve returns early leaving the caller's x[4] (zero-initialised per call) untouched
+                x = stale
+            stale = x
             for i in range(4):
                 betas[i] += x[i]
         return betas
