@@ -87,6 +87,46 @@ SEPB_API int sepb_match_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const 
                          int32_t* d_n_matches, uint16_t* d_match_from, uint16_t* d_match_to,
                          int32_t* d_n_unique_to);
 
+/* ---- K1: NetVLAD nearest-neighbour search against the peer database --------------------------
+ * Replaces DataHandler.find_matches (R/scripts/data_handler.py:166-209): `cdist(local, received)`
+ * (f64 Euclidean, :170), masks to +inf for local_kf_already_used rows (:178-179),
+ * other_kf_already_used columns (:180-181) and frames_kept_pairs_ignored cells (:183-184), per-row
+ * argmin (:187) -- extended to the k smallest per row -- and the greedy selection loop (:191-205).
+ * Rows of the distance matrix = `queries`, columns = database rows.  Distances are bit-identical to
+ * scipy's cdist (sequential f64 summation, sqrt); ties resolve to the lowest index (np.argmin).
+ * The database is append-only like received_descriptors (:300-301) and takes the float64[] wire
+ * payload of FindMatches.srv:1 as is. */
+SEPB_API int sepb_db_create(sepb_ctx* ctx, int dim, int capacity, sepb_db** out);
+SEPB_API void sepb_db_destroy(sepb_db* db);
+SEPB_API int sepb_db_size(const sepb_db* db);
+SEPB_API int sepb_db_append(sepb_ctx* ctx, sepb_db* db, const double* rows, int n);  /* host rows [n][dim] */
+/* row-sharded databases: global index of this shard's row 0 (indices returned are global) */
+SEPB_API int sepb_db_set_base(sepb_db* db, int64_t base);
+/* other_kf_already_used as a byte mask over the database rows [size]; NULL clears */
+SEPB_API int sepb_db_set_col_mask(sepb_ctx* ctx, sepb_db* db, const uint8_t* mask);
+
+/* k <= 16.  row_mask: [nq] bytes or NULL; ignored: [n_ignored][2] (query row, GLOBAL db row) or NULL.
+ * out_idx [nq][k] i32 (-1 = none / masked), out_dist [nq][k] f64 (+inf = none), ascending (dist, idx).
+ * mode: SEPB_NN_EXACT = fp64 scan (K1b) ; SEPB_NN_TENSOR = tcgen05 split-bf16 filter (K1) + exact
+ * fp64 re-rank of the surviving candidates, with per-row fallback to the exact scan whenever the
+ * filter's error bound cannot prove the candidate set complete.  Results are identical in both. */
+#define SEPB_NN_EXACT 0
+#define SEPB_NN_TENSOR 1
+SEPB_API int sepb_netvlad_topk(sepb_ctx* ctx, const sepb_db* db, const double* queries, int nq, int k, int mode,
+                               const uint8_t* row_mask, const int32_t* ignored, int n_ignored, int32_t* out_idx,
+                               double* out_dist);
+/* device form: d_queries [nq][dim] f64; d_ign_start [nq+1] / d_ign_col CSR of ignored cells (or NULL) */
+SEPB_API int sepb_netvlad_topk_dev(sepb_ctx* ctx, const sepb_db* db, const double* d_queries, int nq, int k, int mode,
+                                   const uint8_t* d_row_mask, const int32_t* d_ign_start, const int32_t* d_ign_col,
+                                   int32_t* d_out_idx, double* d_out_dist);
+/* merge `lists` per-shard results (layout [lists][nq][k], e.g. after an all-gather) -> [nq][k] */
+SEPB_API int sepb_topk_merge_dev(sepb_ctx* ctx, const int32_t* d_in_idx, const double* d_in_dist, int lists, int nq,
+                                 int k, int32_t* d_out_idx, double* d_out_dist);
+/* the selection loop of data_handler.py:191-205 over per-row minima (host, O(nq log nq)):
+ * writes up to max_matches_nb (query_row, db_row) pairs, returns their number (or <0). */
+SEPB_API int sepb_select_matches(const int32_t* row_min_idx, const double* row_min_dist, int nq,
+                                 double netvlad_distance, int max_matches_nb, int32_t* out_pairs);
+
 /* ---- K3: batched PnP-RANSAC + refit ------------------------------------------------------
  * Replaces the PnP block R/src/myRegistrationVis.cpp:1055-1112: RTAB-Map
  * util3d::estimateMotion3DTo2D -> cv::solvePnPRansac(useExtrinsicGuess=true, iterations,

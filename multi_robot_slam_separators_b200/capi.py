@@ -88,6 +88,26 @@ def _declare(L):
     L.sepb_pnp_ransac_dev.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, vp, C.POINTER(PnpParams), vp, i32, vp,
                                       vp, vp, vp, vp, vp, i32, vp, vp]
     L.sepb_pnp_ransac_dev.restype = i32
+    L.sepb_db_create.argtypes = [vp, i32, i32, C.POINTER(vp)]
+    L.sepb_db_create.restype = i32
+    L.sepb_db_destroy.argtypes = [vp]
+    L.sepb_db_destroy.restype = None
+    L.sepb_db_size.argtypes = [vp]
+    L.sepb_db_size.restype = i32
+    L.sepb_db_append.argtypes = [vp, vp, vp, i32]
+    L.sepb_db_append.restype = i32
+    L.sepb_db_set_base.argtypes = [vp, i64]
+    L.sepb_db_set_base.restype = i32
+    L.sepb_db_set_col_mask.argtypes = [vp, vp, vp]
+    L.sepb_db_set_col_mask.restype = i32
+    L.sepb_netvlad_topk.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp, i32, vp, vp]
+    L.sepb_netvlad_topk.restype = i32
+    L.sepb_netvlad_topk_dev.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp, vp]
+    L.sepb_netvlad_topk_dev.restype = i32
+    L.sepb_topk_merge_dev.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+    L.sepb_topk_merge_dev.restype = i32
+    L.sepb_select_matches.argtypes = [vp, vp, i32, C.c_double, i32, vp]
+    L.sepb_select_matches.restype = i32
     for name in ("sepb_verify_pairs", "sepb_verify_pairs_dev"):
         f = getattr(L, name)
         f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), C.POINTER(PnpParams), vp, i32,
@@ -237,3 +257,70 @@ def inlier_indices(mask_row, n_matches):
     """bitmask over match-list positions -> ascending index array"""
     bits = np.unpackbits(mask_row.view(np.uint8), bitorder="little")[:n_matches]
     return np.nonzero(bits)[0].astype(np.int32)
+
+
+NN_EXACT, NN_TENSOR = 0, 1
+
+
+class NetvladDB:
+    """Device-resident, append-only NetVLAD descriptor database (received_descriptors, data_handler.py:300-301)."""
+
+    def __init__(self, ctx: Context, dim: int, capacity: int, base: int = 0):
+        self.ctx, self.dim, self.capacity = ctx, dim, capacity
+        self._h = C.c_void_p()
+        ctx.check(lib().sepb_db_create(ctx._h, dim, capacity, C.byref(self._h)))
+        if base:
+            ctx.check(lib().sepb_db_set_base(self._h, base))
+
+    def append(self, rows):
+        rows = np.ascontiguousarray(rows, dtype=np.float64).reshape(-1, self.dim)
+        self.ctx.check(lib().sepb_db_append(self.ctx._h, self._h, _ptr(rows), rows.shape[0]))
+
+    @property
+    def size(self):
+        return lib().sepb_db_size(self._h)
+
+    def set_col_mask(self, used_indices):
+        """other_kf_already_used (list of database row indices) -> byte mask."""
+        if used_indices is None or len(used_indices) == 0:
+            self.ctx.check(lib().sepb_db_set_col_mask(self.ctx._h, self._h, None))
+            return
+        m = np.zeros(self.size, np.uint8)
+        m[np.asarray(used_indices, dtype=np.int64)] = 1
+        self.ctx.check(lib().sepb_db_set_col_mask(self.ctx._h, self._h, _ptr(m)))
+
+    def topk(self, queries, k=1, mode=NN_EXACT, local_used=(), pairs_ignored=()):
+        q = np.ascontiguousarray(queries, dtype=np.float64).reshape(-1, self.dim)
+        nq = q.shape[0]
+        rm = None
+        if len(local_used):
+            rm = np.zeros(nq, np.uint8)
+            rm[np.asarray(local_used, dtype=np.int64)] = 1
+        ign = np.ascontiguousarray(pairs_ignored, dtype=np.int32).reshape(-1, 2) if len(pairs_ignored) else None
+        idx = np.full((nq, k), -1, np.int32)
+        dist = np.full((nq, k), np.inf, np.float64)
+        self.ctx.check(lib().sepb_netvlad_topk(self.ctx._h, self._h, _ptr(q), nq, k, mode, _ptr(rm), _ptr(ign),
+                                               0 if ign is None else ign.shape[0], _ptr(idx), _ptr(dist)))
+        return idx, dist
+
+    def close(self):
+        if self._h:
+            lib().sepb_db_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def select_matches(row_min_idx, row_min_dist, netvlad_distance=0.13, max_matches_nb=20):
+    """data_handler.py:191-205 (host helper inside the C ABI)."""
+    i = np.ascontiguousarray(row_min_idx, dtype=np.int32).ravel()
+    d = np.ascontiguousarray(row_min_dist, dtype=np.float64).ravel()
+    out = np.zeros((max(max_matches_nb, 1), 2), np.int32)
+    n = lib().sepb_select_matches(_ptr(i), _ptr(d), len(i), float(netvlad_distance), int(max_matches_nb), _ptr(out))
+    if n < 0:
+        raise SepbError(f"sepb_select_matches failed: {n}")
+    return [(int(a), int(b)) for a, b in out[:n]]

@@ -23,6 +23,22 @@ struct sepb_ctx {
   // cv::RNG(-1) minimal-sample index table [count][table_h][5] (K3)
   uint16_t* table = nullptr;
   int table_m = -1, table_h = 0;
+  // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
+  size_t cfg_hamming_smem = 0;
+  bool cfg_pnp = false, cfg_exact = false, cfg_gemm = false;
+};
+
+struct sepb_db {
+  sepb_ctx* ctx = nullptr;
+  int dim = 0, capacity = 0, size = 0;
+  int64_t base = 0;            // global index of row 0 (row-sharded databases)
+  double* rows = nullptr;      // [capacity][dim] exact copy of the float64[] wire data
+  uint8_t* col_mask = nullptr; // [capacity] other_kf_already_used
+  bool has_mask = false;
+  // tensor-core filter operands (K1): split-bf16 rows [capacity][3*dim_pad] and squared norms, filled lazily
+  uint16_t* split = nullptr;
+  float* norm2 = nullptr;
+  int split_rows = 0;          // rows [0, split_rows) are converted
 };
 
 struct sepb_frames {
@@ -108,3 +124,10 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
                            const sepb_pnp_params* p, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
                            float* d_transform, uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp,
                            int32_t* d_iters_run);
+
+int sepb_launch_netvlad_exact(sepb_ctx* ctx, const double* d_q, int nq, const double* d_db, int n, int D, int k,
+                              int64_t base, const uint8_t* d_row_mask, const uint8_t* d_col_mask,
+                              const int32_t* d_ign_start, const int32_t* d_ign_col, int splits, int32_t* d_part_idx,
+                              double* d_part_dist, int32_t* d_out_idx, double* d_out_dist);
+int sepb_launch_topk_merge(sepb_ctx* ctx, const int32_t* d_in_idx, const double* d_in_dist, int lists, int nq, int k,
+                           int32_t* d_out_idx, double* d_out_dist);

@@ -184,7 +184,7 @@ int sepb_launch_hamming_match(sepb_ctx* ctx, FramesView from, FramesView to, con
   if (n_pairs == 0) return SEPB_OK;
   const size_t smem = (size_t)kTTile * 32 + (size_t)to.max_feat * 4 + (size_t)from.max_feat * 4 +
                       align_up((size_t)from.max_feat * 2, 16);
-  static size_t configured = 0;
+  size_t& configured = ctx->cfg_hamming_smem;
   if (smem > configured) {
     SEPB_CUDA(ctx, cudaFuncSetAttribute(hamming_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;

@@ -1,0 +1,198 @@
+// K1b: exact fp64 NetVLAD distances in scipy.cdist's summation order + masks + per-row top-k.
+//
+// Replaces `cdist` + row/column/cell masks + `argsort(axis=1)[:,0]` of DataHandler.find_matches
+// (R/scripts/data_handler.py:170-188), extended to top-k per row (BASELINE.json configs[1]: k=5).
+// cdist(euclidean) is s = 0; for j: d = u[j]-v[j]; s += d*d; return sqrt(s)  -- sequential, no FMA
+// (verified bit-for-bit against scipy 1.18 for D = 77, 128, 4096), so each (query,row) distance is
+// one serial chain; the parallelism is across pairs.  A thread owns one query and 32 database rows
+// at a time (32 independent chains), database chunks are read as 128-bit shared-memory broadcasts,
+// query chunks through an XOR-swizzled tile.  Two uses: (a) full scan of a database slice
+// (exact path; also the fallback of the tensor-core filter), (b) re-ranking candidate lists.
+// Output order per row: ascending (distance, index) -- ties to the lowest index like np.argmin.
+#include "common.cuh"
+
+namespace {
+
+constexpr int QB = 128;   // queries per CTA == threads
+constexpr int NB = 32;    // database rows per tile
+constexpr int DC = 64;    // descriptor elements per staged chunk
+constexpr int KMAX = 16;  // max k
+
+struct ExactParams {
+  const double* q;        // [nq][D]
+  const double* db;       // [n][D]
+  int nq, n, D;
+  int k;
+  int64_t base;           // global index of db row 0 (sharded databases)
+  const uint8_t* row_mask;   // [nq] 1 = row ignored (local_kf_already_used)
+  const uint8_t* col_mask;   // [n]  1 = column ignored (other_kf_already_used)
+  const int32_t* ign_start;  // [nq+1] CSR over ignored cells (frames_kept_pairs_ignored), may be null
+  const int32_t* ign_col;    // global column ids
+  int splits;             // database split count (grid.y)
+  int32_t* out_idx;       // [splits][nq][k]
+  double* out_dist;       // [splits][nq][k]
+};
+
+__device__ __forceinline__ bool better(double d, int64_t i, double d2, int64_t i2) {
+  return d < d2 || (d == d2 && i < i2);
+}
+
+__global__ void __launch_bounds__(QB) netvlad_exact_kernel(ExactParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  double* q_s = reinterpret_cast<double*>(smem);                 // [QB][DC] swizzled in 16 B units
+  double* db_s = q_s + QB * DC;                                  // [NB][DC]
+  double* top_d = db_s + NB * DC;                                // [KMAX][QB]
+  int32_t* top_i = reinterpret_cast<int32_t*>(top_d + KMAX * QB);  // [KMAX][QB]
+  const int tid = threadIdx.x;
+  const int q0 = blockIdx.x * QB;
+  const int qi = q0 + tid;
+  const int k = p.k;
+  // database slice of this split, in whole tiles
+  const int tiles = (p.n + NB - 1) / NB;
+  const int t_lo = (int)((int64_t)tiles * blockIdx.y / p.splits), t_hi = (int)((int64_t)tiles * (blockIdx.y + 1) / p.splits);
+  for (int j = 0; j < k; ++j) {
+    top_d[j * QB + tid] = INFINITY;
+    top_i[j * QB + tid] = -1;
+  }
+  double worst = INFINITY;   // k-th best distance so far
+  const bool row_dead = qi >= p.nq || (p.row_mask && p.row_mask[qi]);
+  const int ig0 = (p.ign_start && qi < p.nq) ? p.ign_start[qi] : 0, ig1 = (p.ign_start && qi < p.nq) ? p.ign_start[qi + 1] : 0;
+
+  for (int t = t_lo; t < t_hi; ++t) {
+    const int n0 = t * NB;
+    double acc[NB];
+#pragma unroll
+    for (int j = 0; j < NB; ++j) acc[j] = 0.0;
+    for (int kc = 0; kc < p.D; kc += DC) {
+      __syncthreads();
+      // stage query chunk (swizzled) and database chunk; zero fill outside (0-0)^2 adds exactly 0
+      for (int e = tid; e < QB * DC; e += QB) {
+        const int r = e / DC, c = e % DC;
+        double v = 0.0;
+        if (q0 + r < p.nq && kc + c < p.D) v = p.q[(size_t)(q0 + r) * p.D + kc + c];
+        q_s[r * DC + ((((c >> 1) ^ (r & 31)) << 1) | (c & 1))] = v;
+      }
+      for (int e = tid; e < NB * DC; e += QB) {
+        const int r = e / DC, c = e % DC;
+        double v = 0.0;
+        if (n0 + r < p.n && kc + c < p.D) v = p.db[(size_t)(n0 + r) * p.D + kc + c];
+        db_s[e] = v;
+      }
+      __syncthreads();
+      const double2* qrow = reinterpret_cast<const double2*>(q_s + tid * DC);
+      const double2* dbt = reinterpret_cast<const double2*>(db_s);
+#pragma unroll 2
+      for (int c2 = 0; c2 < DC / 2; ++c2) {
+        const double2 a = qrow[c2 ^ (tid & 31)];
+#pragma unroll
+        for (int j = 0; j < NB; ++j) {
+          const double2 b = dbt[j * (DC / 2) + c2];
+          const double d0 = __dsub_rn(a.x, b.x);
+          acc[j] = __dadd_rn(acc[j], __dmul_rn(d0, d0));
+          const double d1 = __dsub_rn(a.y, b.y);
+          acc[j] = __dadd_rn(acc[j], __dmul_rn(d1, d1));
+        }
+      }
+    }
+    if (row_dead) continue;
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+      const int n = n0 + j;
+      if (n >= p.n) continue;
+      const double d = __dsqrt_rn(acc[j]);
+      if (!(d <= worst)) continue;        // also rejects NaN
+      if (p.col_mask && p.col_mask[n]) continue;
+      const int64_t gi = p.base + n;
+      bool ign = false;
+      for (int g = ig0; g < ig1; ++g) ign |= p.ign_col[g] == (int32_t)gi;
+      if (ign || isinf(d)) continue;
+      // sorted insert by (d, idx); lists are short
+      int pos = k - 1;
+      if (!better(d, gi, top_d[pos * QB + tid], top_i[pos * QB + tid] < 0 ? INT64_MAX : (int64_t)top_i[pos * QB + tid])) continue;
+      while (pos > 0) {
+        const double pd = top_d[(pos - 1) * QB + tid];
+        const int32_t pi = top_i[(pos - 1) * QB + tid];
+        if (!better(d, gi, pd, pi < 0 ? INT64_MAX : (int64_t)pi)) break;
+        top_d[pos * QB + tid] = pd;
+        top_i[pos * QB + tid] = pi;
+        --pos;
+      }
+      top_d[pos * QB + tid] = d;
+      top_i[pos * QB + tid] = (int32_t)gi;
+      worst = top_d[(k - 1) * QB + tid];
+    }
+  }
+  if (qi < p.nq) {
+    const size_t o = ((size_t)blockIdx.y * p.nq + qi) * k;
+    for (int j = 0; j < k; ++j) {
+      p.out_idx[o + j] = top_i[j * QB + tid];
+      p.out_dist[o + j] = top_d[j * QB + tid];
+    }
+  }
+}
+
+// merge `lists` sorted top-k lists per row (layout [lists][nq][k]) into one; thread per row
+__global__ void topk_merge_kernel(const int32_t* __restrict__ in_idx, const double* __restrict__ in_dist, int lists,
+                                  int nq, int k, int32_t* __restrict__ out_idx, double* __restrict__ out_dist) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  int head[64];
+  for (int l = 0; l < lists; ++l) head[l] = 0;
+  for (int j = 0; j < k; ++j) {
+    int bl = -1;
+    double bd = INFINITY;
+    int32_t bi = -1;
+    for (int l = 0; l < lists; ++l) {
+      if (head[l] >= k) continue;
+      const size_t o = ((size_t)l * nq + q) * k + head[l];
+      const int32_t i = in_idx[o];
+      if (i < 0) continue;
+      const double d = in_dist[o];
+      if (bl < 0 || d < bd || (d == bd && i < bi)) {
+        bl = l;
+        bd = d;
+        bi = i;
+      }
+    }
+    out_idx[(size_t)q * k + j] = bi;
+    out_dist[(size_t)q * k + j] = bl < 0 ? INFINITY : bd;
+    if (bl >= 0) head[bl]++;
+  }
+}
+
+}  // namespace
+
+int sepb_launch_netvlad_exact(sepb_ctx* ctx, const double* d_q, int nq, const double* d_db, int n, int D, int k,
+                              int64_t base, const uint8_t* d_row_mask, const uint8_t* d_col_mask,
+                              const int32_t* d_ign_start, const int32_t* d_ign_col, int splits, int32_t* d_part_idx,
+                              double* d_part_dist, int32_t* d_out_idx, double* d_out_dist) {
+  if (nq == 0) return SEPB_OK;
+  ExactParams p{d_q, d_db, nq, n, D, k, base, d_row_mask, d_col_mask, d_ign_start, d_ign_col, splits,
+                splits > 1 ? d_part_idx : d_out_idx, splits > 1 ? d_part_dist : d_out_dist};
+  const size_t smem = (size_t)(QB * DC + NB * DC + KMAX * QB) * 8 + (size_t)KMAX * QB * 4;
+  bool& configured = ctx->cfg_exact;
+  if (!configured) {
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(netvlad_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  dim3 grid((nq + QB - 1) / QB, splits);
+  netvlad_exact_kernel<<<grid, QB, smem, ctx->stream>>>(p);
+  ctx->launches++;
+  SEPB_CUDA(ctx, cudaGetLastError());
+  if (splits > 1) {
+    topk_merge_kernel<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(d_part_idx, d_part_dist, splits, nq, k, d_out_idx, d_out_dist);
+    ctx->launches++;
+    SEPB_CUDA(ctx, cudaGetLastError());
+  }
+  return SEPB_OK;
+}
+
+int sepb_launch_topk_merge(sepb_ctx* ctx, const int32_t* d_in_idx, const double* d_in_dist, int lists, int nq, int k,
+                           int32_t* d_out_idx, double* d_out_dist) {
+  if (nq == 0) return SEPB_OK;
+  if (lists > 64) return sepb_fail(ctx, SEPB_E_SHAPE, "topk_merge: more than 64 lists", __FILE__, __LINE__);
+  topk_merge_kernel<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(d_in_idx, d_in_dist, lists, nq, k, d_out_idx, d_out_dist);
+  ctx->launches++;
+  SEPB_CUDA(ctx, cudaGetLastError());
+  return SEPB_OK;
+}

@@ -355,7 +355,7 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   for (int i = 0; i < 9; ++i) k.local_R[i] = p->local_R[i];
   k.table_h = table_h;
   const size_t smem = (size_t)cvm::kEpnpHeap * 32 * 8 + 2 * kMaskWords * 4;
-  static bool configured = false;
+  bool& configured = ctx->cfg_pnp;
   if (!configured) {
     SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
