@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py -- verified keyframe pairs/s (Hamming match + PnP-RANSAC) on BASELINE.json configs[1]:
+2 robots x 10k synthetic stereo keyframes (1000 256-bit features + 128-d NetVLAD each), all-pairs
+NetVLAD NN, top-5 candidates per query verified.  One process per GPU; at N > 1 every rank owns an
+independent robot pair (candidate pairs partition with no data-path collective: weak scaling).
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA, libsepb200.so)
+  python bench.py --impl reference ...                      the reference's CPU library calls (oracle/)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "verified keyframe pairs/sec (match+PnP-RANSAC)"
+UNIT = "pairs/s"
+
+
+def env_int(name, default):
+    return int(os.environ.get(name, default))
+
+
+def workload_config(args):
+    return {"workload": "configs[1]: 2 robots x %d keyframes, %d ORB-like 256-bit features + %d-d NetVLAD per frame, "
+                        "all-pairs NetVLAD NN + top-%d Hamming/PnP-RANSAC verification" % (args.frames, args.feat, args.dim, args.topk),
+            "keyframes_per_robot": args.frames, "features_per_frame": args.feat, "netvlad_dim": args.dim,
+            "top_k": args.topk, "pairs_per_step_per_gpu": args.frames * args.topk, "ransac_iterations": 300,
+            "nndr": 0.8, "netvlad_distance": "inf (every top-k candidate is verified)",
+            "l2_policy": "inputs larger than L2 (feature stores 1.1 GB per GPU, 126 MB L2)",
+            "partition": "independent robot pair per rank, no collective on the data path"}
+
+
+# ---------------------------------------------------------------------------------------------
+def clocks_sampler_start(gpu_index):
+    f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+    q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    try:
+        p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                              "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+    except Exception:
+        return None, f.name
+    return p, f.name
+
+
+def clocks_sampler_stop(p, path):
+    out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+    if p is not None:
+        p.terminate()
+        try:
+            p.wait(timeout=5)
+        except Exception:
+            p.kill()
+    try:
+        rows = [l.strip().split(", ") for l in open(path) if l.strip()]
+        sm = [float(r[0]) for r in rows if len(r) >= 7]
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = float(rows[0][1])
+            out["samples"] = len(sm)
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            out["reasons"] = [n for i, n in enumerate(names) if any(r[3 + i].strip() == "Active" for r in rows if len(r) >= 7)]
+    except Exception:
+        pass
+    finally:
+        try:
+            os.unlink(path)
+        except OSError:
+            pass
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+def cpu_reference_step(sample, threads):
+    """The reference's own library calls on a bounded sample of the workload: scipy cdist + top-k,
+    then per pair cv2.BFMatcher(HAMMING).knnMatch(k=2)+NNDR+uniqueness and cv2.solvePnPRansac.
+    Returns (pairs_done, seconds, nn_queries, nn_seconds)."""
+    from oracle import find_matches as fm
+    t0 = time.perf_counter()
+    idx, dist = fm.topk(sample["q"], sample["db"], sample["k"])
+    t_nn = time.perf_counter() - t0
+    pairs = [(int(idx[r, j]), r) for r in range(idx.shape[0]) for j in range(idx.shape[1]) if idx[r, j] >= 0]
+    t1 = time.perf_counter()
+    if threads > 1:
+        import multiprocessing as mp
+        with mp.get_context("fork").Pool(threads, initializer=_cpu_worker_init, initargs=(sample,)) as pool:
+            res = pool.map(_cpu_verify_pair, pairs, chunksize=max(1, len(pairs) // (threads * 8)))
+    else:
+        _cpu_worker_init(sample)
+        res = [_cpu_verify_pair(p) for p in pairs]
+    t_ver = time.perf_counter() - t1
+    return len(pairs), t_nn + t_ver, idx.shape[0], t_nn, int(sum(res))
+
+
+_S = None
+
+
+def _cpu_worker_init(sample):
+    global _S
+    import cv2
+    cv2.setNumThreads(1)
+    _S = sample
+
+
+def _cpu_verify_pair(p):
+    import cv2
+    from oracle import matching, pnp
+    f, t = p
+    S = _S
+    A, B = S["A"], S["B"]
+    fa, tb = S["a_slot"][f], S["b_slot"][t]
+    pairs = matching.global_match(B.desc[tb], A.desc[fa], 0.8)
+    obj, img, _, _ = matching.pnp_correspondences(pairs, A.kp3d[fa], B.kp2d[tb])
+    if len(obj) < 5:
+        return 0
+    ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, S["K"], S["rv0"], S["tv0"], iterations=300)
+    return int(ok and len(inl) >= 5)
+
+
+def make_cpu_sample(args, seed, n_queries):
+    """NetVLAD for the full config (cheap) + features only for the frames the sampled queries touch."""
+    import cv2
+    from multi_robot_slam_separators_b200 import synth
+    from oracle import find_matches as fm, pnp
+    rng = np.random.default_rng([seed, 1])
+    places = synth.place_assignment(2, args.frames, 0.3, rng)
+    nv_a = synth.make_netvlad(places[0], args.dim, seed)
+    nv_b = synth.make_netvlad(places[1], args.dim, seed)
+    rows = np.arange(n_queries)                      # first rows of robot B (the computing robot)
+    idx, _ = fm.topk(nv_b[rows], nv_a, args.topk)
+    need_a = np.unique(idx[idx >= 0])
+    A = synth.make_frames(places[0][need_a], 0, seed, n_feat=args.feat, dim=8)
+    B = synth.make_frames(places[1][rows], 1, seed, n_feat=args.feat, dim=8)
+    K = pnp.K_matrix(synth.FX, synth.FY, synth.CX, synth.CY)
+    rv0, _ = cv2.Rodrigues(synth.R_LOCAL.T.copy())
+    return dict(q=nv_b[rows], db=nv_a, k=args.topk, A=A, B=B, a_slot={int(f): i for i, f in enumerate(need_a)},
+                b_slot={int(r): i for i, r in enumerate(rows)}, K=K, rv0=rv0.ravel(), tv0=np.zeros(3))
+
+
+def run_reference(args):
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = make_cpu_sample(args, 2000, args.cpu_queries)
+    times = []
+    done = 0
+    for s in range(args.warmup + args.steps):
+        n, sec, nq, t_nn, n_ok = cpu_reference_step(sample, threads)
+        if s >= args.warmup:
+            times.append(sec)
+            done += n
+    total = sum(times)
+    val = done / total
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u32+f64", "data": "synthetic", "config": workload_config(args),
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": "%d query rows x %d-row database NN (scipy cdist) + their top-%d = %d pairs through "
+                                       "cv2.BFMatcher/solvePnPRansac per step, process pool" % (args.cpu_queries, args.frames, args.topk, n)},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from multi_robot_slam_separators_b200 import capi, synth
+    from multi_robot_slam_separators_b200.engine import Camera, SeparatorEngine
+
+    rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: CUDA device required (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    # ---- synthetic robots of this rank (seed = 1000*config + rank)
+    t0 = time.time()
+    A, B = synth.make_robots(2, args.frames, n_feat=args.feat, dim=args.dim, seed=2000 + rank)
+    t_gen = time.time() - t0
+    eng = SeparatorEngine(Camera(synth.FX, synth.FY, synth.CX, synth.CY), args.feat, args.dim, args.frames, args.frames,
+                          device=local_rank)
+    P = args.frames * args.topk
+
+    def pin(a):
+        return torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+
+    hostA = dict(desc=pin(A.desc), kp2d=pin(A.kp2d), kp3d=pin(A.kp3d), octave=pin(A.octave), count=pin(A.count))
+    hostB = dict(desc=pin(B.desc), kp2d=pin(B.kp2d), kp3d=pin(B.kp3d), octave=pin(B.octave), count=pin(B.count))
+    nvA, nvB = pin(A.netvlad), pin(B.netvlad)
+    h2d_bytes = sum(v.nbytes for v in hostA.values()) + sum(v.nbytes for v in hostB.values()) + nvA.nbytes + nvB.nbytes + P * 8
+
+    def upload():
+        eng.add_peer_keyframes(hostA["desc"], hostA["kp2d"], hostA["kp3d"], hostA["count"], hostA["octave"])
+        eng.add_local_keyframes(hostB["desc"], hostB["kp2d"], hostB["kp3d"], hostB["count"], hostB["octave"])
+        eng.receive_descriptors(nvA)
+
+    upload()
+    d_q = torch.from_numpy(B.netvlad).to(dev)
+    mode = capi.NN_TENSOR if args.nn == "tensor" else capi.NN_EXACT
+    stream = eng.stream
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing -------------------------------------------------------------
+    for _ in range(args.warmup):
+        eng.step_dev(d_q, args.topk, mode)
+    eng.sync()
+    launches0 = eng.ctx.launch_count
+    sampler, spath = clocks_sampler_start(local_rank)
+    barrier()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    with torch.cuda.stream(stream):
+        ev[0].record(stream)
+        for _ in range(args.steps):
+            res = eng.step_dev(d_q, args.topk, mode)
+        ev[1].record(stream)
+    ev[1].synchronize()
+    barrier()
+    clocks = clocks_sampler_stop(sampler, spath)
+    ms_total = ev[0].elapsed_time(ev[1])
+    launches = eng.ctx.launch_count - launches0
+    n_ok = int((res["status"] == 1).sum().item())
+    n_ransac = int((res["n_matches"] >= 5).sum().item())
+    iters_mean = float(res["iters_run"][res["n_matches"] >= 5].float().mean().item()) if n_ransac else 0.0
+
+    # ---- per-kernel durations (CUDA events on the launching stream) ---------------------------
+    def timed(fn, reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            fn()
+            e0.record(stream)
+            for _ in range(reps):
+                fn()
+            e1.record(stream)
+        e1.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    idx, _ = eng.candidates_dev(d_q, args.topk, mode)
+    pairs = eng.pairs_from_candidates(idx)
+    ms_k1 = timed(lambda: eng.candidates_dev(d_q, args.topk, mode), 3)
+    import ctypes as C
+    L = capi.lib()
+    nm = torch.zeros(P, dtype=torch.int32, device=dev)
+    nu = torch.zeros(P, dtype=torch.int32, device=dev)
+    mf = torch.zeros((P, args.feat), dtype=torch.int16, device=dev)
+    mt = torch.zeros((P, args.feat), dtype=torch.int16, device=dev)
+
+    def k2():
+        eng.ctx.check(L.sepb_match_pairs_dev(eng.ctx._h, eng.peer._h, eng.local._h, C.c_void_p(pairs.data_ptr()), P,
+                                             C.byref(eng.mp), None, None, C.c_void_p(nm.data_ptr()),
+                                             C.c_void_p(mf.data_ptr()), C.c_void_p(mt.data_ptr()), C.c_void_p(nu.data_ptr())))
+    ms_k2 = timed(k2, 3)
+    ms_verify = timed(lambda: eng.verify_dev(pairs), 3)
+    ms_k3 = max(ms_verify - ms_k2, 0.0)
+
+    # ---- end to end through the host-buffer C ABI -------------------------------------------
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    out_idx = np.empty((args.frames, args.topk), np.int32)
+
+    def e2e_step():
+        eng.reset()
+        upload()                                                     # H2D of both robots' keyframes + descriptors
+        i5, d5 = eng.db.topk(nvB, args.topk, mode)                   # queries H2D, candidates D2H
+        pr = np.stack([i5.reshape(-1), np.repeat(np.arange(args.frames, dtype=np.int32), args.topk)], 1).astype(np.int32)
+        r = capi.verify_pairs_light(eng.ctx, eng.peer, eng.local, pr, eng.pnp)   # pairs H2D, results D2H
+        return r
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        r_e2e = e2e_step()
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    d2h_bytes = P * (4 + 4 + 4 + 48 + 48) + P * 12
+    assert int((r_e2e["status"] == 1).sum()) == n_ok, "e2e and resident paths disagree"
+
+    # ---- aggregate over ranks -----------------------------------------------------------------
+    t = torch.tensor([ms_total, t_e2e * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total_max, ms_e2e_max = t.tolist()
+    value = world * P * args.steps / (ms_total_max * 1e-3)
+    e2e_value = world * P * e2e_steps / (ms_e2e_max * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        popc_peak = eng.ctx.measure_peak("popc")
+        dfma_peak = eng.ctx.measure_peak("dfma")
+        k2_bytes = P * ((args.feat + args.feat) * 32 + args.feat * 12)        # algorithmic bytes per launch
+        k2_gbs = k2_bytes / (ms_k2 * 1e-3) / 1e9
+        k2_popc = P * 8.0 * args.feat * args.feat / (ms_k2 * 1e-3)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_total_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u32+f64", "data": "synthetic", "config": workload_config(args), "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
+                        "steps": e2e_steps},
+                "gpu_launches": int(launches),
+                "roofline": {"kernel": "hamming_match_kernel (K2)", "bound": "hbm", "achieved": k2_gbs, "peak": hbm_peak,
+                             "unit": "GB/s", "frac": k2_gbs / hbm_peak, "traffic": None,
+                             "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                             "note": "K2 is POPC-issue bound, not HBM bound: see roofline_int"},
+                "roofline_int": {"kernel": "hamming_match_kernel (K2)", "bound": "int (POPC pipe)", "achieved": k2_popc,
+                                 "peak": popc_peak, "unit": "popc32/s", "frac": k2_popc / popc_peak,
+                                 "peak_source": "sepb_measure_peak microbenchmark, same run"},
+                "kernels_ms": {"K1_netvlad_topk": ms_k1, "K2_hamming_match": ms_k2, "K3_pnp_ransac": ms_k3,
+                               "step_share_K2": ms_k2 / (ms_total / args.steps)},
+                "fp64_fma_peak_per_s": dfma_peak,
+                "nn_queries_per_s": args.frames / (ms_k1 * 1e-3), "nn_mode": args.nn,
+                "verified_ok_per_step": n_ok, "pairs_with_ransac_per_step": n_ransac, "ransac_iters_mean": iters_mean,
+                "synth_seconds": t_gen}
+        if not args.no_cpu_baseline and world == 1:
+            sample = make_cpu_sample(args, 2000, args.cpu_queries)
+            n, sec, nq, t_nn, _ = cpu_reference_step(sample, 1)
+            line["cpu_baseline"] = {"value": n / sec, "unit": UNIT, "cores": 1, "kind": "port",
+                                    "sample": "%d query rows NN (scipy cdist vs %d rows) + their top-%d = %d pairs through "
+                                              "cv2.BFMatcher(k=2)+NNDR+uniqueness and cv2.solvePnPRansac, single thread"
+                                              % (args.cpu_queries, args.frames, args.topk, n)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=10000)
+    ap.add_argument("--feat", type=int, default=1000)
+    ap.add_argument("--dim", type=int, default=128)
+    ap.add_argument("--topk", type=int, default=5)
+    ap.add_argument("--nn", default="exact", choices=["exact", "tensor"])
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--cpu-queries", type=int, default=200)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -99,6 +99,7 @@ SEPB_API int sepb_match_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const 
 SEPB_API int sepb_db_create(sepb_ctx* ctx, int dim, int capacity, sepb_db** out);
 SEPB_API void sepb_db_destroy(sepb_db* db);
 SEPB_API int sepb_db_size(const sepb_db* db);
+SEPB_API int sepb_db_clear(sepb_db* db);   /* forget all rows (node restart); capacity is kept */
 SEPB_API int sepb_db_append(sepb_ctx* ctx, sepb_db* db, const double* rows, int n);  /* host rows [n][dim] */
 /* row-sharded databases: global index of this shard's row 0 (indices returned are global) */
 SEPB_API int sepb_db_set_base(sepb_db* db, int64_t base);

@@ -94,6 +94,8 @@ def _declare(L):
     L.sepb_db_destroy.restype = None
     L.sepb_db_size.argtypes = [vp]
     L.sepb_db_size.restype = i32
+    L.sepb_db_clear.argtypes = [vp]
+    L.sepb_db_clear.restype = i32
     L.sepb_db_append.argtypes = [vp, vp, vp, i32]
     L.sepb_db_append.restype = i32
     L.sepb_db_set_base.argtypes = [vp, i64]
@@ -232,15 +234,17 @@ def match_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, nnd
 
 
 def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pnp: PnpParams, nndr=0.8, strict=False,
-                 custom_samples=None):
-    """Host-buffer fused K2 -> K3 call (estimate_transformation pass 1 for a batch of pairs)."""
+                 custom_samples=None, want_lists=True):
+    """Host-buffer fused K2 -> K3 call (estimate_transformation pass 1 for a batch of pairs).
+    want_lists=False skips the D2H of match lists / inlier masks (only what EstTransform.srv returns)."""
     pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
     P, F = pairs.shape[0], frames_from.max_feat
     res = dict(status=np.zeros(P, np.int32), n_matches=np.zeros(P, np.int32), n_inliers=np.zeros(P, np.int32),
                pose=np.zeros((P, 6), np.float64), transform=np.zeros((P, 12), np.float32),
-               match_from=np.zeros((P, F), np.uint16), match_to=np.zeros((P, F), np.uint16),
-               inlier_mask=np.zeros((P, (F + 31) // 32), np.uint32), best_hyp=np.zeros(P, np.int32),
-               iters_run=np.zeros(P, np.int32))
+               best_hyp=np.zeros(P, np.int32), iters_run=np.zeros(P, np.int32))
+    if want_lists:
+        res.update(match_from=np.zeros((P, F), np.uint16), match_to=np.zeros((P, F), np.uint16),
+                   inlier_mask=np.zeros((P, (F + 31) // 32), np.uint32))
     out = VerifyOut(**{k: v.ctypes.data for k, v in res.items()})
     cs, ch = None, 0
     if custom_samples is not None:
@@ -251,6 +255,10 @@ def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pn
     ctx.check(lib().sepb_verify_pairs(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(mp), C.byref(pnp),
                                       _ptr(cs), ch, C.byref(out)))
     return res
+
+
+def verify_pairs_light(ctx, frames_from, frames_to, pairs, pnp, nndr=0.8):
+    return verify_pairs(ctx, frames_from, frames_to, pairs, pnp, nndr, want_lists=False)
 
 
 def inlier_indices(mask_row, n_matches):
@@ -279,6 +287,9 @@ class NetvladDB:
     @property
     def size(self):
         return lib().sepb_db_size(self._h)
+
+    def clear(self):
+        self.ctx.check(lib().sepb_db_clear(self._h))
 
     def set_col_mask(self, used_indices):
         """other_kf_already_used (list of database row indices) -> byte mask."""

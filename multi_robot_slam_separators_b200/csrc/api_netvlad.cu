@@ -58,6 +58,14 @@ void sepb_db_destroy(sepb_db* db) {
 
 int sepb_db_size(const sepb_db* db) { return db ? db->size : 0; }
 
+int sepb_db_clear(sepb_db* db) {
+  if (!db) return SEPB_E_INVALID;
+  db->size = 0;
+  db->split_rows = 0;
+  db->has_mask = false;
+  return SEPB_OK;
+}
+
 int sepb_db_set_base(sepb_db* db, int64_t base) {
   if (!db || base < 0) return SEPB_E_INVALID;
   db->base = base;

@@ -166,9 +166,11 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
   const int pair = blockIdx.x;
   if (pair >= n_pairs) return;
   const cvm::Heap heap{heap_base + lane, 32};
-  const int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
-  const int M = n_matches[pair];
-  const int nf = from.count[fi];
+  int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
+  const bool valid_pair = fi >= 0 && fi < from.size && ti >= 0 && ti < to.size;
+  if (!valid_pair) fi = ti = 0;
+  const int M = valid_pair ? n_matches[pair] : 0;
+  const int nf = valid_pair ? from.count[fi] : 0;
   const int nu = n_unique_to ? n_unique_to[pair] : M;
   Corr cr{from.kp3d + (size_t)fi * from.max_feat * 3, to.kp2d + (size_t)ti * to.max_feat * 2,
           match_from + (size_t)pair * from.max_feat, match_to + (size_t)pair * from.max_feat};
