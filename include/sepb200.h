@@ -50,6 +50,17 @@ SEPB_API int sepb_ctx_sync(sepb_ctx* ctx);
 /* number of kernels this library launched on ctx since creation (bench.py "gpu_launches") */
 SEPB_API int64_t sepb_ctx_launch_count(const sepb_ctx* ctx);
 
+/* options (sepb_ctx_set_option): which kernel runs the Hamming matcher.  Both produce identical results.
+ *   SEPB_MATCH_POPC   hamming_knn.cu  -- INT/XU-pipe kernel (__popc, 128-bit shared-memory broadcasts)
+ *   SEPB_MATCH_TENSOR hamming_mma.cu  -- the same distances as an exact int8 tcgen05 GEMM
+ *   SEPB_MATCH_AUTO   tensor kernel whenever the frame sizes fit its shared-memory budget (default) */
+#define SEPB_OPT_MATCH_KERNEL 1
+#define SEPB_MATCH_AUTO (-1)
+#define SEPB_MATCH_POPC 0
+#define SEPB_MATCH_TENSOR 1
+SEPB_API int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value);
+SEPB_API int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value);
+
 /* ---- keyframe feature store ------------------------------------------------------------
  * Mirrors what GetFeatsAndDesc / FindMatches carry per keyframe (R/srv/GetFeatsAndDesc.srv:4-6,
  * R/msg/Descriptors.msg, R/msg/KeyPointVec.msg, R/msg/KeyPoint3DVec.msg): descriptors rows x 32

@@ -71,6 +71,10 @@ def _declare(L):
     L.sepb_ctx_sync.restype = i32
     L.sepb_ctx_launch_count.argtypes = [vp]
     L.sepb_ctx_launch_count.restype = i64
+    L.sepb_ctx_set_option.argtypes = [vp, i32, i32]
+    L.sepb_ctx_set_option.restype = i32
+    L.sepb_ctx_get_option.argtypes = [vp, i32, C.POINTER(C.c_int)]
+    L.sepb_ctx_get_option.restype = i32
     L.sepb_frames_create.argtypes = [vp, i32, i32, C.POINTER(vp)]
     L.sepb_frames_create.restype = i32
     L.sepb_frames_destroy.argtypes = [vp]
@@ -130,6 +134,9 @@ def _ptr(a):
     return C.c_void_p(a.ctypes.data)
 
 
+OPT_MATCH_KERNEL = 1
+
+
 class Context:
     def __init__(self, device: int = 0):
         self._h = C.c_void_p()
@@ -157,6 +164,10 @@ class Context:
         v = C.c_double()
         self.check(lib().sepb_measure_peak(self._h, {"popc": 0, "dfma": 1}[kind], reps, C.byref(v)))
         return v.value
+
+    def set_match_kernel(self, which: str):
+        """'auto' | 'popc' (INT-pipe kernel) | 'tensor' (tcgen05 int8 GEMM kernel); identical results."""
+        self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_KERNEL, {"auto": -1, "popc": 0, "tensor": 1}[which]))
 
     def close(self):
         if self._h:

@@ -3,6 +3,16 @@
 
 #include <new>
 
+int sepb_launch_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs, float nndr,
+                      int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
+                      uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to) {
+  const int opt = ctx->opt_match_kernel;
+  const bool tensor = opt == SEPB_MATCH_TENSOR || (opt == SEPB_MATCH_AUTO && sepb_hamming_mma_supported(from, to));
+  return (tensor ? sepb_launch_hamming_mma : sepb_launch_hamming_match)(ctx, from, to, d_pairs, n_pairs, nndr, strict,
+                                                                      d_knn_idx, d_knn_dist, d_n_matches, d_match_from,
+                                                                      d_match_to, d_n_unique_to);
+}
+
 extern "C" {
 
 int sepb_ctx_create(int device, sepb_ctx** out) {
@@ -49,6 +59,25 @@ int sepb_ctx_sync(sepb_ctx* ctx) {
   if (!ctx) return SEPB_E_INVALID;
   SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SEPB_OK;
+}
+
+int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value) {
+  if (!ctx) return SEPB_E_INVALID;
+  if (option == SEPB_OPT_MATCH_KERNEL) {
+    SEPB_REQUIRE(ctx, value == SEPB_MATCH_AUTO || value == SEPB_MATCH_POPC || value == SEPB_MATCH_TENSOR, SEPB_E_INVALID);
+    ctx->opt_match_kernel = value;
+    return SEPB_OK;
+  }
+  return sepb_fail(ctx, SEPB_E_INVALID, "unknown option", __FILE__, __LINE__);
+}
+
+int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value) {
+  if (!ctx || !value) return SEPB_E_INVALID;
+  if (option == SEPB_OPT_MATCH_KERNEL) {
+    *value = ctx->opt_match_kernel;
+    return SEPB_OK;
+  }
+  return SEPB_E_INVALID;
 }
 
 // ---- frame store ---------------------------------------------------------------------------
@@ -123,7 +152,7 @@ int sepb_match_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_fram
   if (n_pairs == 0) return SEPB_OK;
   SEPB_REQUIRE(ctx, d_pairs && d_n_matches, SEPB_E_INVALID);
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
-  return sepb_launch_hamming_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, prm->nndr, prm->nndr_strict,
+  return sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, prm->nndr, prm->nndr_strict,
                                    d_knn_idx, d_knn_dist, d_n_matches, d_match_from, d_match_to, d_n_unique_to);
 }
 
@@ -155,7 +184,7 @@ int sepb_match_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* 
   SEPB_CUDA(ctx, cudaMemcpyAsync(d_pairs, pairs, P * 8, cudaMemcpyHostToDevice, ctx->stream));
   if (d_ki) SEPB_CUDA(ctx, cudaMemsetAsync(d_ki, 0xFF, P * to->max_feat * 8, ctx->stream));
   if (d_kd) SEPB_CUDA(ctx, cudaMemsetAsync(d_kd, 0xFF, P * to->max_feat * 8, ctx->stream));
-  int rc = sepb_launch_hamming_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, prm->nndr, prm->nndr_strict,
+  int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, prm->nndr, prm->nndr_strict,
                                      d_ki, d_kd, d_nm, d_mf, d_mt, d_nu);
   if (rc) return rc;
   if (knn_idx) SEPB_CUDA(ctx, cudaMemcpyAsync(knn_idx, d_ki, P * to->max_feat * 8, cudaMemcpyDeviceToHost, ctx->stream));

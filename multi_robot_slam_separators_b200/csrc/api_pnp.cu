@@ -106,7 +106,7 @@ int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_fra
   // n_unique_to lives in a small grow-only scratch slice owned by the context
   int32_t* d_nu = (int32_t*)sepb_scratch(ctx, align_up((size_t)n_pairs * 4, 256));
   if (!d_nu) return (int)cudaErrorMemoryAllocation;
-  int rc = sepb_launch_hamming_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, mprm->nndr, mprm->nndr_strict,
+  int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, mprm->nndr, mprm->nndr_strict,
                                      nullptr, nullptr, o->n_matches, o->match_from, o->match_to, d_nu);
   if (rc) return rc;
   return sepb_pnp_ransac_dev(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm,

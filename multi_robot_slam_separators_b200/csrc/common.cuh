@@ -24,7 +24,9 @@ struct sepb_ctx {
   uint16_t* table = nullptr;
   int table_m = -1, table_h = 0;
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
-  size_t cfg_hamming_smem = 0;
+  size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0;
+  int opt_match_kernel = SEPB_MATCH_AUTO;
+  int opt_nn_mode = -1;  // reserved
   bool cfg_pnp = false, cfg_exact = false, cfg_gemm = false;
 };
 
@@ -115,6 +117,16 @@ int sepb_launch_hamming_match(sepb_ctx* ctx, FramesView from, FramesView to, con
                               float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist,
                               int32_t* d_n_matches, uint16_t* d_match_from, uint16_t* d_match_to,
                               int32_t* d_n_unique_to);
+
+// tensor-core variant (hamming_mma.cu); same contract, bit-identical outputs
+bool sepb_hamming_mma_supported(const FramesView& from, const FramesView& to);
+int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                            float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
+                            uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to);
+// dispatch on ctx->opt_match_kernel
+int sepb_launch_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs, float nndr,
+                      int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
+                      uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to);
 
 int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H);
 int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,

@@ -13,6 +13,7 @@
 // Roofline: 8 POPC per distance (16 lanes/clk/SM) -> INT/XU-pipe bound; algorithmic HBM bytes per
 // pair = (F_to + F_from) * 32 + F_from * 12 (descriptors once, From 3-D points once).
 #include "common.cuh"
+#include "match_tail.cuh"
 
 namespace {
 
@@ -106,73 +107,14 @@ hamming_match_kernel(FramesView from, FramesView to, const int32_t* __restrict__
         knn_dist[o] = d1;
         knn_dist[o + 1] = d2;
       }
-      // NNDR in f32 like RTAB-Map (needs two neighbours)
-      int a = -1;
-      if (i2 >= 0) {
-        const float lhs = (float)d1, rhs = __fmul_rn(nndr, (float)d2);
-        if (strict ? (lhs < rhs) : (lhs <= rhs)) a = i1;
-      }
+      const int a = mtail::nndr_assign(i1, d1, i2, d2, nndr, strict);
       s_assigned[qi] = a;
     }
   }
   __syncthreads();
-  // uniqueness filter (myRegistrationVis.cpp:882-894): To ids used more than once are dropped
-  for (int qi = tid; qi < nt; qi += kThreads) {
-    const int a = s_assigned[qi];
-    if (a >= 0) {
-      atomicAdd(&s_count[a], 1u);
-      s_owner[a] = (uint16_t)qi;  // only read back where count == 1 (single writer)
-    }
-  }
-  __syncthreads();
-  // ascending From index, drop non-finite From 3-D (util3d::isFinite) -> compact list
-  const int chunk = (nf + kThreads - 1) / kThreads;
-  const int lo = min(nf, tid * chunk), hi = min(nf, lo + chunk);
   const float* p3 = from.kp3d + (size_t)(valid_pair ? fi : 0) * from.max_feat * 3;
-  int local = 0, dropped = 0;
-  uint32_t keep_mask = 0;  // chunk <= 16 for max_feat <= 4096
-  for (int i = lo; i < hi; ++i) {
-    const uint32_t c = s_count[i];
-    if (c >= 2) dropped += (int)c;
-    if (c == 1) {
-      const float x = p3[3 * i], y = p3[3 * i + 1], z = p3[3 * i + 2];
-      if (isfinite(x) && isfinite(y) && isfinite(z)) {
-        keep_mask |= 1u << (i - lo);
-        ++local;
-      }
-    }
-  }
-  if (dropped) atomicAdd(&s_dropped, dropped);
-  // block exclusive scan of `local`
-  const int lane = tid & 31, warp = tid >> 5;
-  int incl = local;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-    if (lane >= o) incl += v;
-  }
-  if (lane == 31) s_scan[warp] = incl;
-  __syncthreads();
-  int base = 0, total = 0;
-#pragma unroll
-  for (int w = 0; w < kThreads / 32; ++w) {
-    const int v = s_scan[w];
-    if (w < warp) base += v;
-    total += v;
-  }
-  int pos = base + incl - local;
-  const size_t obase = (size_t)pair * from.max_feat;
-  for (int i = lo; i < hi; ++i) {
-    if (keep_mask & (1u << (i - lo))) {
-      if (match_from) match_from[obase + pos] = (uint16_t)i;
-      if (match_to) match_to[obase + pos] = s_owner[i];
-      ++pos;
-    }
-  }
-  if (tid == 0) {
-    n_matches[pair] = total;
-    if (n_unique_to) n_unique_to[pair] = nt - s_dropped;
-  }
+  mtail::unique_and_compact<kThreads>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
+                                      (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to, n_unique_to);
 }
 
 }  // namespace

@@ -1,0 +1,381 @@
+// K2T: brute-force 256-bit Hamming 2-NN on the 5th-generation tensor cores (tcgen05, kind::i8).
+//
+// Same contract and bit-identical results as hamming_knn.cu (the POPC-pipe kernel), which replaces
+// cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) + NNDR + uniqueness at R/src/myRegistrationVis.cpp:839-894.
+// The POPC pipe (16 lanes/clk/SM) caps that kernel at ~0.56 M pairs/s per GPU; here the 10^6 distances
+// of a pair become an exact integer GEMM whose accumulators ARE the sort keys:
+//
+//   every descriptor bit b becomes the int8 value +11 (b = 0) or -11 (b = 1), so for a To row q and a
+//   From row t   sum_k q_k t_k = 121 * (256 - 2 * hamming(q, t));
+//   one extra K-block of 32 int8 carries the From row's column inside its 224-column accumulator tile:
+//   A_x = (-64, -1, -128, -128, 0...), B_x(col) = (col >> 6, col & 63, pad, pad, 0...) contributing -col
+//   (and -32512 for the padding rows of a partial tile, pad = 127).  The s32 accumulator is
+//       acc = 30976 - (242 * hamming + col)           in [-31199, 30976]: it fits 16 bits,
+//   its maximum over a row is BFMatcher's best match (smallest distance, ties to the lowest train index)
+//   and the runner-up its second neighbour.  The epilogue reads TMEM with .pack::16b (two columns per
+//   register) and keeps the running top-2 with packed VIMNMX(3).S16x2: 1.25 instructions per distance,
+//   no key building, no masking, and everything stays exact.
+//
+// One CTA per keyframe pair, warp-specialised:
+//   warps 0-7   epilogue: TMEM -> registers (tcgen05.ld), running top-2 per To row; warps 0-3 own
+//               accumulator buffer 0, warps 4-7 buffer 1 (TMEM lane quarter = warp & 3)
+//   warp  8     MMA issuer (one lane): per (To tile, From tile) 8 SWIZZLE_128B K-steps + 1 index K-step
+//   warps 9-12  producers: expand descriptor bits into the +-11 operand tiles in shared memory
+// A resident chunk of 448 From rows (two 224-column accumulator tiles = double-buffered TMEM) is
+// expanded once; the 128-row To tiles stream through a 2-deep ring against it.
+#include <limits.h>
+
+#include "common.cuh"
+#include "match_tail.cuh"
+#include "umma.cuh"
+
+namespace {
+
+constexpr int kEpiWarps = 8;
+constexpr int kMmaWarp = 8;
+constexpr int kProdWarp0 = 9;
+constexpr int kProdWarps = 4;
+constexpr int kProdThreads = kProdWarps * 32;
+constexpr int kThreadsT = (kEpiWarps + 1 + kProdWarps) * 32;  // 416
+constexpr int TM = 128;             // To rows per A tile (= TMEM lanes)
+constexpr int TN = 224;             // From rows per accumulator tile
+constexpr int CH = 2 * TN;          // From rows per resident chunk
+constexpr int kTmemBuf = 256;       // TMEM column stride between the two accumulator buffers
+constexpr int kBBytes = CH * 256;   // main K-blocks of the resident chunk
+constexpr int kABytes = TM * 256;
+constexpr int kBxBytes = CH * 32;   // index K-block (interleaved layout)
+constexpr int kAxBytes = TM * 32;
+constexpr uint32_t kNoneKey = 0xFFFFFFFFu;
+
+constexpr int kScale = 121;           // product of the two operand magnitudes (11 * 11)
+constexpr int kStep = 2 * kScale;     // accumulator decrease per unit of Hamming distance (242 > TN - 1)
+constexpr int32_t kNoneV = -32000;    // accumulators at or below this are padding / "no neighbour"
+constexpr uint32_t kNone2 = 0x80008000u;
+
+// expand one 256-bit descriptor into 256 int8 (+11 / -11) at row r of a SWIZZLE_128B tile of `rows` rows
+// (shared-memory address `tile`).  Output word t of input word w holds bits {t, t+8, t+16, t+24} of w --
+// any fixed permutation of the 256 positions is fine as long as both operands use the same one.
+__device__ __forceinline__ void expand_row(uint32_t tile, int rows, int r, const uint4* __restrict__ g) {
+  const uint4 a = __ldg(g), b = __ldg(g + 1);
+  const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+  for (int wi = 0; wi < 8; ++wi) {
+    uint32_t o[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) o[t] = ((w[wi] >> t) & 0x01010101u) * 0xEAu + 0x0B0B0B0Bu;
+    const uint32_t base = tile + (uint32_t)((wi >> 2) * rows * 128 + r * 128);
+    const int c0 = (wi & 3) * 2;
+    umma::sts128(base + (uint32_t)(((c0) ^ (r & 7)) << 4), o[0], o[1], o[2], o[3]);
+    umma::sts128(base + (uint32_t)(((c0 + 1) ^ (r & 7)) << 4), o[4], o[5], o[6], o[7]);
+  }
+}
+__device__ __forceinline__ void zero_row(uint32_t tile, int rows, int r) {
+#pragma unroll
+  for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) umma::sts128(tile + (uint32_t)(kb * rows * 128 + r * 128 + c * 16), 0, 0, 0, 0);
+}
+
+__device__ __forceinline__ uint32_t max2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.s16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t min2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("min.s16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+// fold two packed registers (four accumulators) into the packed running top-2: 5 instructions
+__device__ __forceinline__ void push2(uint32_t& m1, uint32_t& m2, uint32_t x, uint32_t y) {
+  const uint32_t hi = max2(x, y), lo = min2(x, y);
+  m2 = max2(max2(min2(m1, hi), m2), lo);
+  m1 = max2(m1, hi);
+}
+__device__ __forceinline__ void merge2(uint32_t& a1, uint32_t& a2, uint32_t b1, uint32_t b2) {
+  const uint32_t lo = min2(a1, b1);
+  a1 = max2(a1, b1);
+  a2 = max2(lo, max2(a2, b2));
+}
+__device__ __forceinline__ void merge_min(uint32_t& a1, uint32_t& a2, uint32_t b1, uint32_t b2) {
+  const uint32_t hi = max(a1, b1);
+  a1 = min(a1, b1);
+  a2 = min(hi, min(a2, b2));
+}
+
+// 16-bit accumulator -> (hamming << 16 | global From index), the key order of hamming_knn.cu
+__device__ __forceinline__ uint32_t acc_to_key(int v, int tile_base) {
+  if (v <= kNoneV) return kNoneKey;
+  const int kp = kScale * 256 - v;  // 242 * hamming + column
+  const int ham = kp / kStep;
+  return ((uint32_t)ham << 16) | (uint32_t)(tile_base + kp - ham * kStep);
+}
+
+__device__ __forceinline__ void scan32(const uint32_t (&r)[16], uint32_t (&m1)[2], uint32_t (&m2)[2]) {
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    push2(m1[0], m2[0], r[j], r[j + 1]);
+    push2(m1[1], m2[1], r[j + 2], r[j + 3]);
+  }
+}
+
+__global__ void __launch_bounds__(kThreadsT, 1)
+hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs, float nndr, int strict,
+                   int32_t* __restrict__ knn_idx, int32_t* __restrict__ knn_dist, int32_t* __restrict__ n_matches,
+                   uint16_t* __restrict__ match_from, uint16_t* __restrict__ match_to,
+                   int32_t* __restrict__ n_unique_to) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sB = smem;                                  // [2 K-blocks][CH][128]
+  uint8_t* sA = sB + kBBytes;                          // [2 buffers][2 K-blocks][TM][128]
+  uint8_t* sBx = sA + 2 * kABytes;                     // [CH/8][2][8][16]
+  uint8_t* sAx = sBx + kBxBytes;                       // [TM/8][2][8][16]
+  uint32_t* s_top = reinterpret_cast<uint32_t*>(sAx + kAxBytes);  // [2][to.max_feat][2] keys
+  // tail arrays alias the operand tiles (all MMAs have completed by then)
+  int32_t* s_assigned = reinterpret_cast<int32_t*>(sB);
+  uint32_t* s_count = reinterpret_cast<uint32_t*>(s_assigned + to.max_feat);
+  uint16_t* s_owner = reinterpret_cast<uint16_t*>(s_count + from.max_feat);
+  __shared__ uint64_t bar_a_full[2], bar_a_empty[2], bar_b_full, bar_b_empty, bar_t_full[2], bar_t_empty[2];
+  __shared__ uint32_t tmem_slot;
+  __shared__ int s_scan[kThreadsT / 32];
+  __shared__ int s_dropped;
+
+  const int pair = blockIdx.x;
+  if (pair >= n_pairs) return;
+  const int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool valid_pair = fi >= 0 && fi < from.size && ti >= 0 && ti < to.size;
+  const int nf = valid_pair ? min(from.count[fi], from.max_feat) : 0;
+  const int nt = valid_pair ? min(to.count[ti], to.max_feat) : 0;
+  const uint4* g_train = reinterpret_cast<const uint4*>(from.desc + (size_t)(valid_pair ? fi : 0) * from.max_feat * 32);
+  const uint4* g_query = reinterpret_cast<const uint4*>(to.desc + (size_t)(valid_pair ? ti : 0) * to.max_feat * 32);
+
+  if (nt == 0 || nf == 0) {  // block-uniform: nothing to multiply
+    for (int qi = tid; qi < nt; qi += kThreadsT) {
+      const size_t o = ((size_t)pair * to.max_feat + qi) * 2;
+      if (knn_idx) knn_idx[o] = knn_idx[o + 1] = -1;
+      if (knn_dist) knn_dist[o] = knn_dist[o + 1] = -1;
+    }
+    if (tid == 0) {
+      n_matches[pair] = 0;
+      if (n_unique_to) n_unique_to[pair] = nt;
+    }
+    return;
+  }
+
+  // ---- setup -----------------------------------------------------------------------------------
+  for (int i = tid; i < 4 * to.max_feat; i += kThreadsT) s_top[i] = kNoneKey;
+  for (int i = tid; i < (kBxBytes + kAxBytes) / 16; i += kThreadsT)
+    reinterpret_cast<uint4*>(sBx)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  for (int r = tid; r < CH; r += kThreadsT) {
+    const int col = r >= TN ? r - TN : r;
+    uint8_t* p = sBx + (r >> 3) * 256 + (r & 7) * 16;
+    p[0] = (uint8_t)(col >> 6);
+    p[1] = (uint8_t)(col & 63);
+  }
+  for (int r = tid; r < TM; r += kThreadsT) {
+    *reinterpret_cast<uint32_t*>(sAx + (r >> 3) * 256 + (r & 7) * 16) = 0x8080FFC0u;  // (-64, -1, -128, -128)
+  }
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      umma::mbar_init(&bar_a_full[s], kProdThreads);
+      umma::mbar_init(&bar_a_empty[s], 1);
+      umma::mbar_init(&bar_t_full[s], 1);
+      umma::mbar_init(&bar_t_empty[s], 4);  // one arrive per epilogue warp of the buffer's group
+    }
+    umma::mbar_init(&bar_b_full, kProdThreads);
+    umma::mbar_init(&bar_b_empty, 1);
+    umma::fence_mbar_init();
+    s_dropped = 0;
+  }
+  if (warp == kMmaWarp) umma::tmem_alloc(&tmem_slot, 512);
+  umma::fence_proxy_async();  // index K-blocks were written through the generic proxy
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  const int n_chunks = (nf + CH - 1) / CH, n_mt = (nt + TM - 1) / TM;
+
+  if (warp >= kProdWarp0) {
+    // ---- producers ---------------------------------------------------------------------------
+    const int p = tid - kProdWarp0 * 32;
+    const uint32_t sB_a = umma::smem_u32(sB), sA_a = umma::smem_u32(sA);
+    int it = 0;
+    for (int c = 0; c < n_chunks; ++c) {
+      const int rows = min(CH, nf - c * CH);
+      // the last tile of the chunk is padded to a multiple of 32 columns with "no neighbour" rows
+      const int tail_base = rows > TN ? TN : 0;
+      const int rows_pad = tail_base + ((rows - tail_base + 31) & ~31);
+      umma::mbar_wait(&bar_b_empty, (uint32_t)((c & 1) ^ 1));
+      for (int r = p; r < rows_pad; r += kProdThreads) {
+        if (r < rows) {
+          expand_row(sB_a, CH, r, g_train + 2 * (size_t)(c * CH + r));
+        } else {
+          zero_row(sB_a, CH, r);
+          uint8_t* px = sBx + (r >> 3) * 256 + (r & 7) * 16;
+          px[2] = 127;
+          px[3] = 127;
+        }
+      }
+      umma::fence_proxy_async();
+      umma::mbar_arrive(&bar_b_full);
+      for (int m = 0; m < n_mt; ++m, ++it) {
+        const int s = it & 1;
+        umma::mbar_wait(&bar_a_empty[s], (uint32_t)(((it >> 1) & 1) ^ 1));
+        const int row = m * TM + p;
+        if (row < nt) expand_row(sA_a + (uint32_t)(s * kABytes), TM, p, g_query + 2 * (size_t)row);
+        umma::fence_proxy_async();
+        umma::mbar_arrive(&bar_a_full[s]);
+      }
+    }
+  } else if (warp == kMmaWarp) {
+    // ---- MMA issuer ----------------------------------------------------------------------------
+    if (lane == 0) {
+      const uint32_t a_base = umma::smem_u32(sA), b_base = umma::smem_u32(sB);
+      const uint64_t adesc_x = umma::smem_desc_interleave(umma::smem_u32(sAx), 128, 256);
+      const uint32_t bx_base = umma::smem_u32(sBx);
+      int it = 0;
+      uint32_t use0 = 0, use1 = 0;
+      for (int c = 0; c < n_chunks; ++c) {
+        const int rows = min(CH, nf - c * CH);
+        umma::mbar_wait(&bar_b_full, (uint32_t)(c & 1));
+        for (int m = 0; m < n_mt; ++m, ++it) {
+          const int s = it & 1;
+          umma::mbar_wait(&bar_a_full[s], (uint32_t)((it >> 1) & 1));
+          umma::tc_fence_after();
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int ncols = min(TN, rows - h * TN);
+            if (ncols <= 0) break;
+            uint32_t& use = h ? use1 : use0;
+            umma::mbar_wait(&bar_t_empty[h], (use & 1) ^ 1);
+            umma::tc_fence_after();
+            const uint32_t idesc = umma::instr_desc(2, 1, 1, TM, (uint32_t)((ncols + 31) & ~31));
+            const uint32_t d = tmem + (uint32_t)(h * kTmemBuf);
+#pragma unroll
+            for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma::mma_i8(d, umma::smem_desc_sw128(a_base + s * kABytes + kb * TM * 128 + k * 32),
+                             umma::smem_desc_sw128(b_base + kb * CH * 128 + h * TN * 128 + k * 32), idesc, (kb | k) != 0);
+            umma::mma_i8(d, adesc_x, umma::smem_desc_interleave(bx_base + h * TN * 32, 128, 256), idesc, true);
+            umma::mma_commit(&bar_t_full[h]);
+            ++use;
+          }
+          umma::mma_commit(&bar_a_empty[s]);
+        }
+        umma::mma_commit(&bar_b_empty);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- epilogue ------------------------------------------------------------------------------
+    const int h = warp >> 2, lq = warp & 3;
+    const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)(h * kTmemBuf);
+    uint32_t use = 0;
+    for (int c = 0; c < n_chunks; ++c) {
+      const int rows = min(CH, nf - c * CH);
+      const int ncols = min(TN, rows - h * TN);
+      if (ncols <= 0) continue;  // warp-uniform
+      const int nch = (ncols + 31) >> 5;  // the producers padded the tile to nch * 32 columns
+      for (int m = 0; m < n_mt; ++m, ++use) {
+        umma::mbar_wait(&bar_t_full[h], use & 1);
+        umma::tc_fence_after();
+        uint32_t m1[2] = {kNone2, kNone2}, m2[2] = {kNone2, kNone2};
+        uint32_t ra[16], rb[16];
+        umma::tmem_ld32_pack16(taddr, ra);
+        for (int ch = 0; ch < nch; ch += 2) {
+          umma::tmem_ld_wait();
+          if (ch + 1 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 1) * 32), rb);
+          scan32(ra, m1, m2);
+          if (ch + 1 < nch) {
+            umma::tmem_ld_wait();
+            if (ch + 2 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 2) * 32), ra);
+            scan32(rb, m1, m2);
+          }
+        }
+        umma::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive(&bar_t_empty[h]);
+        merge2(m1[0], m2[0], m1[1], m2[1]);
+        // unpack: even columns in the low halves, odd columns in the high halves
+        int v1 = (int)(int16_t)(m1[0] & 0xFFFFu), v2 = (int)(int16_t)(m2[0] & 0xFFFFu);
+        {
+          const int w1 = (int)(int16_t)(m1[0] >> 16), w2 = (int)(int16_t)(m2[0] >> 16);
+          const int lo = min(v1, w1);
+          v1 = max(v1, w1);
+          v2 = max(lo, max(v2, w2));
+        }
+        const int row = m * TM + lq * 32 + lane;
+        if (row < nt) {
+          uint32_t* slot = s_top + ((size_t)h * to.max_feat + row) * 2;
+          uint32_t k1 = slot[0], k2 = slot[1];
+          merge_min(k1, k2, acc_to_key(v1, c * CH + h * TN), acc_to_key(v2, c * CH + h * TN));
+          slot[0] = k1;
+          slot[1] = k2;
+        }
+      }
+    }
+  }
+
+  // ---- tail: NNDR, uniqueness, correspondence list (all warps) --------------------------------------
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    umma::tc_fence_after();
+    umma::tmem_dealloc(tmem, 512);
+  }
+  for (int i = tid; i < nf; i += kThreadsT) s_count[i] = 0;
+  for (int qi = tid; qi < nt; qi += kThreadsT) {
+    uint32_t k1 = s_top[(size_t)qi * 2], k2 = s_top[(size_t)qi * 2 + 1];
+    merge_min(k1, k2, s_top[((size_t)to.max_feat + qi) * 2], s_top[((size_t)to.max_feat + qi) * 2 + 1]);
+    const int i1 = k1 == kNoneKey ? -1 : (int)(k1 & 0xFFFFu), d1 = k1 == kNoneKey ? -1 : (int)(k1 >> 16);
+    const int i2 = k2 == kNoneKey ? -1 : (int)(k2 & 0xFFFFu), d2 = k2 == kNoneKey ? -1 : (int)(k2 >> 16);
+    const size_t o = ((size_t)pair * to.max_feat + qi) * 2;
+    if (knn_idx) {
+      knn_idx[o] = i1;
+      knn_idx[o + 1] = i2;
+    }
+    if (knn_dist) {
+      knn_dist[o] = d1;
+      knn_dist[o + 1] = d2;
+    }
+    s_assigned[qi] = mtail::nndr_assign(i1, d1, i2, d2, nndr, strict);
+  }
+  __syncthreads();
+  const float* p3 = from.kp3d + (size_t)fi * from.max_feat * 3;
+  mtail::unique_and_compact<kThreadsT>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
+                                       (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to, n_unique_to);
+}
+
+}  // namespace
+
+size_t sepb_hamming_mma_smem(int max_feat_to) {
+  return (size_t)kBBytes + 2 * kABytes + kBxBytes + kAxBytes + (size_t)max_feat_to * 16 + 1024;
+}
+
+// largest To-frame feature count the tensor kernel supports (shared-memory budget of one CTA)
+bool sepb_hamming_mma_supported(const FramesView& from, const FramesView& to) {
+  const size_t tail = (size_t)to.max_feat * 4 + (size_t)from.max_feat * 6;
+  return sepb_hamming_mma_smem(to.max_feat) + 256 <= 232448 && tail <= (size_t)kBBytes && from.max_feat <= 65535;
+}
+
+int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                            float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
+                            uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to) {
+  if (n_pairs == 0) return SEPB_OK;
+  if (!sepb_hamming_mma_supported(from, to))
+    return sepb_fail(ctx, SEPB_E_SHAPE, "hamming_mma: frame too large for the tensor kernel", __FILE__, __LINE__);
+  const size_t smem = sepb_hamming_mma_smem(to.max_feat);
+  if (smem > ctx->cfg_hamming_mma_smem) {
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ctx->cfg_hamming_mma_smem = smem;
+  }
+  hamming_mma_kernel<<<n_pairs, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
+                                                               d_knn_dist, d_n_matches, d_match_from, d_match_to,
+                                                               d_n_unique_to);
+  ctx->launches++;
+  SEPB_CUDA(ctx, cudaGetLastError());
+  return SEPB_OK;
+}

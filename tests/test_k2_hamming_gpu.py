@@ -9,9 +9,11 @@ from oracle import matching
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def ctx():
+@pytest.fixture(scope="module", params=["popc", "tensor"])
+def ctx(request):
+    """every test runs once per matcher kernel: hamming_knn.cu (POPC pipe) and hamming_mma.cu (tcgen05)"""
     c = capi.Context(0)
+    c.set_match_kernel(request.param)
     yield c
     c.close()
 
@@ -112,3 +114,24 @@ def test_invalid_arguments(ctx):
         capi.match_pairs(ctx, fr, fr, [[0, 5]])
     with pytest.raises(capi.SepbError):
         capi.Frames(ctx, 4, 5000)
+
+
+def test_tensor_kernel_equals_popc_kernel_full_size():
+    """size-independent property at BASELINE configs[1] frame size: both kernels agree bit for bit on
+    every output (2-NN indices, distances, correspondence lists) over a few hundred 1000x1000 pairs."""
+    A, B = synth.make_robots(2, 48, n_feat=1000, dim=128, seed=2002)
+    rng = np.random.default_rng(11)
+    pairs = rng.integers(0, 48, (256, 2)).astype(np.int32)
+    outs = []
+    for which in ("popc", "tensor"):
+        c = capi.Context(0)
+        c.set_match_kernel(which)
+        fa, fb = capi.frames_from_robot(c, A), capi.frames_from_robot(c, B)
+        outs.append(capi.match_pairs(c, fa, fb, pairs, nndr=0.8))
+        fa.close(); fb.close(); c.close()
+    for k in ("knn_idx", "knn_dist", "n_matches", "n_unique_to"):
+        assert np.array_equal(outs[0][k], outs[1][k]), k
+    for p in range(len(pairs)):
+        m = outs[0]["n_matches"][p]
+        assert np.array_equal(outs[0]["match_from"][p, :m], outs[1]["match_from"][p, :m])
+        assert np.array_equal(outs[0]["match_to"][p, :m], outs[1]["match_to"][p, :m])
