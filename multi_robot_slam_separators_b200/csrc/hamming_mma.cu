@@ -7,7 +7,7 @@
 //
 //   every descriptor bit b becomes the int8 value +11 (b = 0) or -11 (b = 1), so for a To row q and a
 //   From row t   sum_k q_k t_k = 121 * (256 - 2 * hamming(q, t));
-//   one extra K-block of 32 int8 carries the From row's column inside its 224-column accumulator tile:
+//   one extra K-block of 32 int8 carries the From row's column inside its 128-column accumulator tile:
 //   A_x = (-64, -1, -128, -128, 0...), B_x(col) = (col >> 6, col & 63, pad, pad, 0...) contributing -col
 //   (and -32512 for the padding rows of a partial tile, pad = 127).  The s32 accumulator is
 //       acc = 30976 - (242 * hamming + col)           in [-31199, 30976]: it fits 16 bits,
@@ -17,12 +17,14 @@
 //   no key building, no masking, and everything stays exact.
 //
 // One CTA per keyframe pair, warp-specialised:
-//   warps 0-7   epilogue: TMEM -> registers (tcgen05.ld), running top-2 per To row; warps 0-3 own
-//               accumulator buffer 0, warps 4-7 buffer 1 (TMEM lane quarter = warp & 3)
-//   warp  8     MMA issuer (one lane): per (To tile, From tile) 8 SWIZZLE_128B K-steps + 1 index K-step
-//   warps 9-12  producers: expand descriptor bits into the +-11 operand tiles in shared memory
-// A resident chunk of 448 From rows (two 224-column accumulator tiles = double-buffered TMEM) is
-// expanded once; the 128-row To tiles stream through a 2-deep ring against it.
+//   warps 0-7   epilogue: TMEM -> registers (tcgen05.ld), running top-2 per To row; two groups of four
+//               warps (TMEM lane quarter = warp & 3) take the accumulator tiles alternately
+//   warp  8     MMA issuer (one elected lane): per (To tile, From tile) 8 SWIZZLE_128B K-steps + 1 index K-step
+//               of M=128 x N=128 into one of FOUR 128-column TMEM stages (all 512 columns)
+//   warps 9-12  producers: expand descriptor bits into the +-11 operand tiles in shared memory (PRMT lookups)
+// A resident chunk of 384 From rows (three 128-row stages, each with its own full/empty barrier so the next
+// chunk is expanded while the last To tiles still run) is expanded once per chunk; the 128-row To tiles
+// stream through a 2-deep ring against it.
 #include <limits.h>
 
 #include "common.cuh"
@@ -38,9 +40,10 @@ constexpr int kProdWarps = 4;
 constexpr int kProdThreads = kProdWarps * 32;
 constexpr int kThreadsT = (kEpiWarps + 1 + kProdWarps) * 32;  // 416
 constexpr int TM = 128;             // To rows per A tile (= TMEM lanes)
-constexpr int TN = 224;             // From rows per accumulator tile
-constexpr int CH = 2 * TN;          // From rows per resident chunk
-constexpr int kTmemBuf = 256;       // TMEM column stride between the two accumulator buffers
+constexpr int TN = 128;             // From rows per accumulator tile (= one TMEM stage)
+constexpr int kBStages = 3;         // From-row stages resident in shared memory
+constexpr int CH = kBStages * TN;   // From rows per resident chunk
+constexpr int kTStages = 4;         // TMEM accumulator stages of TN columns
 constexpr int kBBytes = CH * 256;   // main K-blocks of the resident chunk
 constexpr int kABytes = TM * 256;
 constexpr int kBxBytes = CH * 32;   // index K-block (interleaved layout)
@@ -53,20 +56,26 @@ constexpr int32_t kNoneV = -32000;    // accumulators at or below this are paddi
 constexpr uint32_t kNone2 = 0x80008000u;
 
 // expand one 256-bit descriptor into 256 int8 (+11 / -11) at row r of a SWIZZLE_128B tile of `rows` rows
-// (shared-memory address `tile`).  Output word t of input word w holds bits {t, t+8, t+16, t+24} of w --
-// any fixed permutation of the 256 positions is fine as long as both operands use the same one.
+// (shared-memory address `tile`).  Any fixed permutation of the 256 bit positions along K is fine as long
+// as both operands use the same one; the one used here costs 13 instructions per 32 bits.
 __device__ __forceinline__ void expand_row(uint32_t tile, int rows, int r, const uint4* __restrict__ g) {
   const uint4 a = __ldg(g), b = __ldg(g + 1);
   const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  // byte lookups through PRMT: a selector nibble v (3 bits of the descriptor) picks byte v of an 8-byte table
+  // holding +11 where the wanted bit of v is 0 and -11 (0xF5) where it is 1
+  constexpr uint32_t T0 = 0xF50BF50Bu;                      // bit 0 of v
+  constexpr uint32_t T1 = 0xF5F50B0Bu;                      // bit 1 of v
+  constexpr uint32_t T2a = 0x0B0B0B0Bu, T2b = 0xF5F5F5F5u;  // bit 2 of v
 #pragma unroll
   for (int wi = 0; wi < 8; ++wi) {
-    uint32_t o[8];
-#pragma unroll
-    for (int t = 0; t < 8; ++t) o[t] = ((w[wi] >> t) & 0x01010101u) * 0xEAu + 0x0B0B0B0Bu;
+    const uint32_t wm = w[wi] & 0x77777777u, wn = (w[wi] >> 1) & 0x77777777u;
+    const uint32_t wmh = wm >> 16, wnh = wn >> 16;
     const uint32_t base = tile + (uint32_t)((wi >> 2) * rows * 128 + r * 128);
     const int c0 = (wi & 3) * 2;
-    umma::sts128(base + (uint32_t)(((c0) ^ (r & 7)) << 4), o[0], o[1], o[2], o[3]);
-    umma::sts128(base + (uint32_t)(((c0 + 1) ^ (r & 7)) << 4), o[4], o[5], o[6], o[7]);
+    umma::sts128(base + (uint32_t)(((c0) ^ (r & 7)) << 4), __byte_perm(T0, T0, wm), __byte_perm(T1, T1, wm),
+                 __byte_perm(T2a, T2b, wm), __byte_perm(T2a, T2b, wn));
+    umma::sts128(base + (uint32_t)(((c0 + 1) ^ (r & 7)) << 4), __byte_perm(T0, T0, wmh), __byte_perm(T1, T1, wmh),
+                 __byte_perm(T2a, T2b, wmh), __byte_perm(T2a, T2b, wnh));
   }
 }
 __device__ __forceinline__ void zero_row(uint32_t tile, int rows, int r) {
@@ -135,7 +144,8 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   int32_t* s_assigned = reinterpret_cast<int32_t*>(sB);
   uint32_t* s_count = reinterpret_cast<uint32_t*>(s_assigned + to.max_feat);
   uint16_t* s_owner = reinterpret_cast<uint16_t*>(s_count + from.max_feat);
-  __shared__ uint64_t bar_a_full[2], bar_a_empty[2], bar_b_full, bar_b_empty, bar_t_full[2], bar_t_empty[2];
+  __shared__ uint64_t bar_a_full[2], bar_a_empty[2], bar_b_full[kBStages], bar_b_empty[kBStages], bar_t_full[kTStages],
+      bar_t_empty[kTStages];
   __shared__ uint32_t tmem_slot;
   __shared__ int s_scan[kThreadsT / 32];
   __shared__ int s_dropped;
@@ -169,7 +179,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     reinterpret_cast<uint4*>(sBx)[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
   for (int r = tid; r < CH; r += kThreadsT) {
-    const int col = r >= TN ? r - TN : r;
+    const int col = r & (TN - 1);
     uint8_t* p = sBx + (r >> 3) * 256 + (r & 7) * 16;
     p[0] = (uint8_t)(col >> 6);
     p[1] = (uint8_t)(col & 63);
@@ -181,11 +191,15 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     for (int s = 0; s < 2; ++s) {
       umma::mbar_init(&bar_a_full[s], kProdThreads);
       umma::mbar_init(&bar_a_empty[s], 1);
-      umma::mbar_init(&bar_t_full[s], 1);
-      umma::mbar_init(&bar_t_empty[s], 4);  // one arrive per epilogue warp of the buffer's group
     }
-    umma::mbar_init(&bar_b_full, kProdThreads);
-    umma::mbar_init(&bar_b_empty, 1);
+    for (int s = 0; s < kBStages; ++s) {
+      umma::mbar_init(&bar_b_full[s], kProdThreads);
+      umma::mbar_init(&bar_b_empty[s], 1);
+    }
+    for (int s = 0; s < kTStages; ++s) {
+      umma::mbar_init(&bar_t_full[s], 1);
+      umma::mbar_init(&bar_t_empty[s], 4);  // one arrive per epilogue warp of the group that drains the stage
+    }
     umma::fence_mbar_init();
     s_dropped = 0;
   }
@@ -204,22 +218,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     int it = 0;
     for (int c = 0; c < n_chunks; ++c) {
       const int rows = min(CH, nf - c * CH);
-      // the last tile of the chunk is padded to a multiple of 32 columns with "no neighbour" rows
-      const int tail_base = rows > TN ? TN : 0;
-      const int rows_pad = tail_base + ((rows - tail_base + 31) & ~31);
-      umma::mbar_wait(&bar_b_empty, (uint32_t)((c & 1) ^ 1));
-      for (int r = p; r < rows_pad; r += kProdThreads) {
-        if (r < rows) {
-          expand_row(sB_a, CH, r, g_train + 2 * (size_t)(c * CH + r));
-        } else {
-          zero_row(sB_a, CH, r);
-          uint8_t* px = sBx + (r >> 3) * 256 + (r & 7) * 16;
-          px[2] = 127;
-          px[3] = 127;
-        }
-      }
-      umma::fence_proxy_async();
-      umma::mbar_arrive(&bar_b_full);
+      const int rows_pad = (rows + 31) & ~31;  // the last tile is padded to 32 columns with "no neighbour" rows
       for (int m = 0; m < n_mt; ++m, ++it) {
         const int s = it & 1;
         umma::mbar_wait(&bar_a_empty[s], (uint32_t)(((it >> 1) & 1) ^ 1));
@@ -227,93 +226,120 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
         if (row < nt) expand_row(sA_a + (uint32_t)(s * kABytes), TM, p, g_query + 2 * (size_t)row);
         umma::fence_proxy_async();
         umma::mbar_arrive(&bar_a_full[s]);
+        if (m == 0) {
+          // resident From stages of this chunk, each as soon as the previous chunk's last tile on it retired
+          for (int j = 0; j * TN < rows; ++j) {
+            umma::mbar_wait(&bar_b_empty[j], (uint32_t)((c & 1) ^ 1));
+            const int r = j * TN + p;
+            if (r < rows) {
+              expand_row(sB_a, CH, r, g_train + 2 * (size_t)(c * CH + r));
+            } else if (r < rows_pad) {
+              zero_row(sB_a, CH, r);
+              uint8_t* px = sBx + (r >> 3) * 256 + (r & 7) * 16;
+              px[2] = 127;
+              px[3] = 127;
+            }
+            umma::fence_proxy_async();
+            umma::mbar_arrive(&bar_b_full[j]);
+          }
+        }
       }
     }
   } else if (warp == kMmaWarp) {
-    // ---- MMA issuer ----------------------------------------------------------------------------
-    if (lane == 0) {
-      const uint32_t a_base = umma::smem_u32(sA), b_base = umma::smem_u32(sB);
-      const uint64_t adesc_x = umma::smem_desc_interleave(umma::smem_u32(sAx), 128, 256);
-      const uint32_t bx_base = umma::smem_u32(sBx);
-      int it = 0;
-      uint32_t use0 = 0, use1 = 0;
-      for (int c = 0; c < n_chunks; ++c) {
-        const int rows = min(CH, nf - c * CH);
-        umma::mbar_wait(&bar_b_full, (uint32_t)(c & 1));
-        for (int m = 0; m < n_mt; ++m, ++it) {
-          const int s = it & 1;
-          umma::mbar_wait(&bar_a_full[s], (uint32_t)((it >> 1) & 1));
-          umma::tc_fence_after();
+    // ---- MMA issuer: the whole warp walks the pipeline, one elected lane issues -----------------
+    // descriptors differ only in the 14-bit start-address field: precompute the low words once
+    const uint32_t a_lo = ((umma::smem_u32(sA) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t b_lo = ((umma::smem_u32(sB) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t sw_hi = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);         // SBO, version, SWIZZLE_128B
+    const uint32_t il_hi = (uint32_t)(256 >> 4) | (1u << 14);                        // SBO, version, no swizzle
+    const uint32_t ax_lo = ((umma::smem_u32(sAx) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
+    const uint32_t bx_lo = ((umma::smem_u32(sBx) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
+    auto desc = [](uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; };
+    int it = 0;
+    uint32_t g = 0;  // accumulator tiles issued so far: TMEM stage g & 3, use count g >> 2
+    for (int c = 0; c < n_chunks; ++c) {
+      const int rows = min(CH, nf - c * CH);
+      for (int m = 0; m < n_mt; ++m, ++it) {
+        const int s = it & 1;
+        umma::mbar_wait(&bar_a_full[s], (uint32_t)((it >> 1) & 1));
+        const uint32_t a_s = a_lo + (uint32_t)((s * kABytes) >> 4);
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int ncols = min(TN, rows - h * TN);
-            if (ncols <= 0) break;
-            uint32_t& use = h ? use1 : use0;
-            umma::mbar_wait(&bar_t_empty[h], (use & 1) ^ 1);
-            umma::tc_fence_after();
+        for (int j = 0; j < kBStages; ++j) {
+          const int ncols = min(TN, rows - j * TN);
+          if (ncols <= 0) break;
+          if (m == 0) umma::mbar_wait(&bar_b_full[j], (uint32_t)(c & 1));
+          const uint32_t st = g & (kTStages - 1);
+          umma::mbar_wait(&bar_t_empty[st], ((g >> 2) & 1) ^ 1);
+          umma::tc_fence_after();
+          if (umma::elect_one()) {
             const uint32_t idesc = umma::instr_desc(2, 1, 1, TM, (uint32_t)((ncols + 31) & ~31));
-            const uint32_t d = tmem + (uint32_t)(h * kTmemBuf);
+            const uint32_t d = tmem + st * TN;
 #pragma unroll
             for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                umma::mma_i8(d, umma::smem_desc_sw128(a_base + s * kABytes + kb * TM * 128 + k * 32),
-                             umma::smem_desc_sw128(b_base + kb * CH * 128 + h * TN * 128 + k * 32), idesc, (kb | k) != 0);
-            umma::mma_i8(d, adesc_x, umma::smem_desc_interleave(bx_base + h * TN * 32, 128, 256), idesc, true);
-            umma::mma_commit(&bar_t_full[h]);
-            ++use;
+                umma::mma_i8(d, desc(a_s + (uint32_t)((kb * TM * 128 + k * 32) >> 4), sw_hi),
+                             desc(b_lo + (uint32_t)((kb * CH * 128 + j * TN * 128 + k * 32) >> 4), sw_hi), idesc,
+                             (kb | k) != 0);
+            umma::mma_i8(d, desc(ax_lo, il_hi), desc(bx_lo + (uint32_t)((j * TN * 32) >> 4), il_hi), idesc, true);
+            umma::mma_commit(&bar_t_full[st]);
+            if (m == n_mt - 1) umma::mma_commit(&bar_b_empty[j]);  // last To tile against this From stage
           }
-          umma::mma_commit(&bar_a_empty[s]);
+          __syncwarp();
+          ++g;
         }
-        umma::mma_commit(&bar_b_empty);
+        if (umma::elect_one()) umma::mma_commit(&bar_a_empty[s]);
+        __syncwarp();
       }
     }
-    __syncwarp();
   } else {
     // ---- epilogue ------------------------------------------------------------------------------
-    const int h = warp >> 2, lq = warp & 3;
-    const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + (uint32_t)(h * kTmemBuf);
-    uint32_t use = 0;
+    const int grp = warp >> 2, lq = warp & 3;
+    uint32_t g = 0;
     for (int c = 0; c < n_chunks; ++c) {
       const int rows = min(CH, nf - c * CH);
-      const int ncols = min(TN, rows - h * TN);
-      if (ncols <= 0) continue;  // warp-uniform
-      const int nch = (ncols + 31) >> 5;  // the producers padded the tile to nch * 32 columns
-      for (int m = 0; m < n_mt; ++m, ++use) {
-        umma::mbar_wait(&bar_t_full[h], use & 1);
-        umma::tc_fence_after();
-        uint32_t m1[2] = {kNone2, kNone2}, m2[2] = {kNone2, kNone2};
-        uint32_t ra[16], rb[16];
-        umma::tmem_ld32_pack16(taddr, ra);
-        for (int ch = 0; ch < nch; ch += 2) {
-          umma::tmem_ld_wait();
-          if (ch + 1 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 1) * 32), rb);
-          scan32(ra, m1, m2);
-          if (ch + 1 < nch) {
+      for (int m = 0; m < n_mt; ++m) {
+        for (int j = 0; j * TN < rows; ++j, ++g) {
+          if ((int)(g & 1) != grp) continue;  // warp-uniform: the other group drains this tile
+          const int ncols = min(TN, rows - j * TN);
+          const int nch = (ncols + 31) >> 5;  // the producers padded the tile to nch * 32 columns
+          const uint32_t st = g & (kTStages - 1);
+          const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + st * TN;
+          umma::mbar_wait(&bar_t_full[st], (g >> 2) & 1);
+          umma::tc_fence_after();
+          uint32_t m1[2] = {kNone2, kNone2}, m2[2] = {kNone2, kNone2};
+          uint32_t ra[16], rb[16];
+          umma::tmem_ld32_pack16(taddr, ra);
+          for (int ch = 0; ch < nch; ch += 2) {
             umma::tmem_ld_wait();
-            if (ch + 2 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 2) * 32), ra);
-            scan32(rb, m1, m2);
+            if (ch + 1 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 1) * 32), rb);
+            scan32(ra, m1, m2);
+            if (ch + 1 < nch) {
+              umma::tmem_ld_wait();
+              if (ch + 2 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 2) * 32), ra);
+              scan32(rb, m1, m2);
+            }
           }
-        }
-        umma::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) umma::mbar_arrive(&bar_t_empty[h]);
-        merge2(m1[0], m2[0], m1[1], m2[1]);
-        // unpack: even columns in the low halves, odd columns in the high halves
-        int v1 = (int)(int16_t)(m1[0] & 0xFFFFu), v2 = (int)(int16_t)(m2[0] & 0xFFFFu);
-        {
-          const int w1 = (int)(int16_t)(m1[0] >> 16), w2 = (int)(int16_t)(m2[0] >> 16);
-          const int lo = min(v1, w1);
-          v1 = max(v1, w1);
-          v2 = max(lo, max(v2, w2));
-        }
-        const int row = m * TM + lq * 32 + lane;
-        if (row < nt) {
-          uint32_t* slot = s_top + ((size_t)h * to.max_feat + row) * 2;
-          uint32_t k1 = slot[0], k2 = slot[1];
-          merge_min(k1, k2, acc_to_key(v1, c * CH + h * TN), acc_to_key(v2, c * CH + h * TN));
-          slot[0] = k1;
-          slot[1] = k2;
+          umma::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) umma::mbar_arrive(&bar_t_empty[st]);
+          merge2(m1[0], m2[0], m1[1], m2[1]);
+          // unpack: even columns in the low halves, odd columns in the high halves
+          int v1 = (int)(int16_t)(m1[0] & 0xFFFFu), v2 = (int)(int16_t)(m2[0] & 0xFFFFu);
+          {
+            const int w1 = (int)(int16_t)(m1[0] >> 16), w2 = (int)(int16_t)(m2[0] >> 16);
+            const int lo = min(v1, w1);
+            v1 = max(v1, w1);
+            v2 = max(lo, max(v2, w2));
+          }
+          const int row = m * TM + lq * 32 + lane;
+          if (row < nt) {
+            uint32_t* slot = s_top + ((size_t)grp * to.max_feat + row) * 2;
+            uint32_t k1 = slot[0], k2 = slot[1];
+            merge_min(k1, k2, acc_to_key(v1, c * CH + j * TN), acc_to_key(v2, c * CH + j * TN));
+            slot[0] = k1;
+            slot[1] = k2;
+          }
         }
       }
     }

@@ -21,6 +21,8 @@ mt = torch.zeros((P, 1000), dtype=torch.int16, device="cuda")
 prm = capi.MatchParams(0.8, 0)
 L = capi.lib()
 stream = torch.cuda.ExternalStream(ctx.stream)
+which = sys.argv[3] if len(sys.argv) > 3 else "auto"
+ctx.set_match_kernel(which)
 def run():
     rc = L.sepb_match_pairs_dev(ctx._h, fa._h, fb._h, C.c_void_p(pairs.data_ptr()), P, C.byref(prm), None, None,
                                 C.c_void_p(nm.data_ptr()), C.c_void_p(mf.data_ptr()), C.c_void_p(mt.data_ptr()),
@@ -34,5 +36,5 @@ with torch.cuda.stream(stream):
     for _ in range(5): run()
     e1.record(stream); e1.synchronize()
 ms = e0.elapsed_time(e1) / 5
-print("K2: %d pairs in %.3f ms -> %.3e pairs/s, %.3e popc/s" % (P, ms, P / ms * 1e3, P * 8e6 / ms * 1e3))
+print(which, "K2: %d pairs in %.3f ms -> %.3e pairs/s, %.3e popc/s" % (P, ms, P / ms * 1e3, P * 8e6 / ms * 1e3))
 print("mean matches", nm.float().mean().item())
