@@ -131,6 +131,12 @@ SEPB_API int sepb_netvlad_topk(sepb_ctx* ctx, const sepb_db* db, const double* q
 SEPB_API int sepb_netvlad_topk_dev(sepb_ctx* ctx, const sepb_db* db, const double* d_queries, int nq, int k, int mode,
                                    const uint8_t* d_row_mask, const int32_t* d_ign_start, const int32_t* d_ign_col,
                                    int32_t* d_out_idx, double* d_out_dist);
+/* Test / profiling hook of the K1 filter (netvlad_gemm.cu): the SEPB_NN_TENSOR search on host queries, plus
+ * out_v [nq][db size] f32 = the raw filter values ||d||^2 - 2 q.d of the tcgen05 GEMM (NULL to skip) and
+ * stats[4] = {candidates re-ranked in f64, rows proven complete by the filter, rows sent to the exact scan, 0}.
+ * Lets the tests measure the GEMM's real error against the bound E the filter relies on (data_handler.py:170). */
+SEPB_API int sepb_netvlad_filter_debug(sepb_ctx* ctx, const sepb_db* db, const double* queries, int nq, int k,
+                                       float* out_v, int32_t* out_idx, double* out_dist, int32_t* stats);
 /* merge `lists` per-shard results (layout [lists][nq][k], e.g. after an all-gather) -> [nq][k] */
 SEPB_API int sepb_topk_merge_dev(sepb_ctx* ctx, const int32_t* d_in_idx, const double* d_in_dist, int lists, int nq,
                                  int k, int32_t* d_out_idx, double* d_out_dist);

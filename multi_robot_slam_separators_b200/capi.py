@@ -110,6 +110,8 @@ def _declare(L):
     L.sepb_netvlad_topk.restype = i32
     L.sepb_netvlad_topk_dev.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp, vp]
     L.sepb_netvlad_topk_dev.restype = i32
+    L.sepb_netvlad_filter_debug.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp]
+    L.sepb_netvlad_filter_debug.restype = i32
     L.sepb_topk_merge_dev.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
     L.sepb_topk_merge_dev.restype = i32
     L.sepb_select_matches.argtypes = [vp, vp, i32, C.c_double, i32, vp]
@@ -324,6 +326,19 @@ class NetvladDB:
         self.ctx.check(lib().sepb_netvlad_topk(self.ctx._h, self._h, _ptr(q), nq, k, mode, _ptr(rm), _ptr(ign),
                                                0 if ign is None else ign.shape[0], _ptr(idx), _ptr(dist)))
         return idx, dist
+
+    def filter_debug(self, queries, k=5, want_v=True):
+        """K1 tensor-core filter with its raw values exposed (tests / profiling):
+        (v [nq, size] f32 or None, idx, dist, stats[4])."""
+        q = np.ascontiguousarray(queries, dtype=np.float64).reshape(-1, self.dim)
+        nq = q.shape[0]
+        v = np.empty((nq, self.size), np.float32) if want_v else None
+        idx = np.full((nq, k), -1, np.int32)
+        dist = np.full((nq, k), np.inf, np.float64)
+        stats = np.zeros(4, np.int32)
+        self.ctx.check(lib().sepb_netvlad_filter_debug(self.ctx._h, self._h, _ptr(q), nq, k, _ptr(v), _ptr(idx),
+                                                       _ptr(dist), _ptr(stats)))
+        return v, idx, dist, stats
 
     def close(self):
         if self._h:

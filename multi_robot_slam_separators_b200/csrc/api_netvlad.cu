@@ -6,9 +6,11 @@
 #include <numeric>
 #include <vector>
 
+// netvlad_gemm.cu
+int sepb_netvlad_tensor_supported(int dim, int k);
 int sepb_netvlad_tensor_topk(sepb_ctx* ctx, const sepb_db* db, const double* d_q, int nq, int k,
                              const uint8_t* d_row_mask, const int32_t* d_ign_start, const int32_t* d_ign_col,
-                             int32_t* d_out_idx, double* d_out_dist);  // netvlad_gemm.cu
+                             int32_t* d_out_idx, double* d_out_dist, float* d_dbg_v, int32_t* d_stats);
 
 namespace {
 int exact_splits(const sepb_ctx* ctx, int nq, int n) {
@@ -53,6 +55,7 @@ void sepb_db_destroy(sepb_db* db) {
   cudaFree(db->col_mask);
   cudaFree(db->split);
   cudaFree(db->norm2);
+  cudaFree(db->maxnorm2);
   delete db;
 }
 
@@ -110,8 +113,10 @@ int sepb_netvlad_topk_dev(sepb_ctx* ctx, const sepb_db* db, const double* d_q, i
   if (nq == 0) return SEPB_OK;
   SEPB_REQUIRE(ctx, d_q && d_out_idx && d_out_dist, SEPB_E_INVALID);
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
-  if (mode == SEPB_NN_TENSOR)
-    return sepb_netvlad_tensor_topk(ctx, db, d_q, nq, k, d_row_mask, d_ign_start, d_ign_col, d_out_idx, d_out_dist);
+  // the filter's per-row lists hold k <= 8; larger k takes the exact scan (same results either way)
+  if (mode == SEPB_NN_TENSOR && sepb_netvlad_tensor_supported(db->dim, k))
+    return sepb_netvlad_tensor_topk(ctx, db, d_q, nq, k, d_row_mask, d_ign_start, d_ign_col, d_out_idx, d_out_dist,
+                                    nullptr, nullptr);
   const int splits = exact_splits(ctx, nq, db->size);
   int32_t* part_i = nullptr;
   double* part_d = nullptr;
@@ -184,6 +189,43 @@ int sepb_netvlad_topk(sepb_ctx* ctx, const sepb_db* db, const double* queries, i
     if (rc) return rc;
     if (e != cudaSuccess) return sepb_fail(ctx, (int)e, "netvlad_topk sync", __FILE__, __LINE__);
   }
+  return SEPB_OK;
+}
+
+// test / profiling hook of the tensor-core filter: same search as SEPB_NN_TENSOR plus the raw filter values
+int sepb_netvlad_filter_debug(sepb_ctx* ctx, const sepb_db* db, const double* queries, int nq, int k, float* out_v,
+                              int32_t* out_idx, double* out_dist, int32_t* stats) {
+  if (!ctx || !db) return SEPB_E_INVALID;
+  SEPB_REQUIRE(ctx, nq > 0 && k >= 1 && sepb_netvlad_tensor_supported(db->dim, k) && db->size > 0, SEPB_E_SHAPE);
+  SEPB_REQUIRE(ctx, queries && out_idx && out_dist, SEPB_E_INVALID);
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t n = db->size;
+  const size_t b_q = align_up((size_t)nq * db->dim * 8, 256), b_v = align_up(out_v ? (size_t)nq * n * 4 : 4, 256),
+               b_oi = align_up((size_t)nq * k * 4, 256), b_od = align_up((size_t)nq * k * 8, 256);
+  uint8_t* buf = nullptr;
+  SEPB_CUDA(ctx, cudaMalloc(&buf, b_q + b_v + b_oi + b_od + 256));
+  double* d_q = (double*)buf;
+  float* d_v = (float*)(buf + b_q);
+  int32_t* d_idx = (int32_t*)(buf + b_q + b_v);
+  double* d_dist = (double*)(buf + b_q + b_v + b_oi);
+  int32_t* d_stats = (int32_t*)(buf + b_q + b_v + b_oi + b_od);
+  cudaMemcpyAsync(d_q, queries, (size_t)nq * db->dim * 8, cudaMemcpyHostToDevice, ctx->stream);
+  cudaMemsetAsync(d_stats, 0, 16, ctx->stream);
+  if (out_v) cudaMemsetAsync(d_v, 0xFF, (size_t)nq * n * 4, ctx->stream);
+  int rc = sepb_netvlad_tensor_topk(ctx, db, d_q, nq, k, nullptr, nullptr, nullptr, d_idx, d_dist, out_v ? d_v : nullptr,
+                                    d_stats);
+  if (rc == SEPB_OK) {
+    if (out_v) cudaMemcpyAsync(out_v, d_v, (size_t)nq * n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    cudaMemcpyAsync(out_idx, d_idx, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    cudaMemcpyAsync(out_dist, d_dist, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    if (stats) cudaMemcpyAsync(stats, d_stats, 16, cudaMemcpyDeviceToHost, ctx->stream);
+  }
+  cudaError_t e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(buf);
+  if (rc) return rc;
+  if (e != cudaSuccess) return sepb_fail(ctx, (int)e, "netvlad_filter_debug", __FILE__, __LINE__);
+  if (stats) stats[2] = nq - stats[1];
   return SEPB_OK;
 }
 

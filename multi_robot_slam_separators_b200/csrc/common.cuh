@@ -38,9 +38,13 @@ struct sepb_db {
   uint8_t* col_mask = nullptr; // [capacity] other_kf_already_used
   bool has_mask = false;
   // tensor-core filter operands (K1): split-bf16 rows [capacity][3*dim_pad] and squared norms, filled lazily
-  uint16_t* split = nullptr;
-  float* norm2 = nullptr;
+  uint16_t* split = nullptr;   // [capacity][2*dim_pad] bf16: hi | lo
+  float* norm2 = nullptr;      // [capacity] squared norms (f32, from the f64 sum)
+  float* maxnorm2 = nullptr;   // device scalar: max of norm2 over converted rows (bit pattern ordered as u32)
+  int dim_pad = 0;             // dim rounded up to 64
   int split_rows = 0;          // rows [0, split_rows) are converted
+  alignas(64) unsigned char tmap[128];  // CUtensorMap over `split` with tmap_rows rows
+  int tmap_rows = -1;
 };
 
 struct sepb_frames {
@@ -140,6 +144,7 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
 int sepb_launch_netvlad_exact(sepb_ctx* ctx, const double* d_q, int nq, const double* d_db, int n, int D, int k,
                               int64_t base, const uint8_t* d_row_mask, const uint8_t* d_col_mask,
                               const int32_t* d_ign_start, const int32_t* d_ign_col, int splits, int32_t* d_part_idx,
-                              double* d_part_dist, int32_t* d_out_idx, double* d_out_dist);
+                              double* d_part_dist, int32_t* d_out_idx, double* d_out_dist,
+                              const int32_t* d_row_list = nullptr, const int32_t* d_n_rows = nullptr);
 int sepb_launch_topk_merge(sepb_ctx* ctx, const int32_t* d_in_idx, const double* d_in_dist, int lists, int nq, int k,
                            int32_t* d_out_idx, double* d_out_dist);

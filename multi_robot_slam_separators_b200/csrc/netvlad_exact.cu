@@ -31,6 +31,10 @@ struct ExactParams {
   int splits;             // database split count (grid.y)
   int32_t* out_idx;       // [splits][nq][k]
   double* out_dist;       // [splits][nq][k]
+  // gather mode (fallback rows of the tensor-core filter): scan only the rows row_list[0 .. *n_rows), results
+  // are written at list position; both null = every row in order
+  const int32_t* row_list;
+  const int32_t* n_rows;
 };
 
 __device__ __forceinline__ bool better(double d, int64_t i, double d2, int64_t i2) {
@@ -45,7 +49,10 @@ __global__ void __launch_bounds__(QB) netvlad_exact_kernel(ExactParams p) {
   int32_t* top_i = reinterpret_cast<int32_t*>(top_d + KMAX * QB);  // [KMAX][QB]
   const int tid = threadIdx.x;
   const int q0 = blockIdx.x * QB;
-  const int qi = q0 + tid;
+  const int n_act = p.n_rows ? min(*p.n_rows, p.nq) : p.nq;   // rows to scan (device-side count in gather mode)
+  if (q0 >= n_act) return;
+  const int qpos = q0 + tid;                                    // position in the output / row list
+  const int qi = qpos < n_act ? (p.row_list ? p.row_list[qpos] : qpos) : p.nq;   // query row (p.nq = none)
   const int k = p.k;
   // database slice of this split, in whole tiles
   const int tiles = (p.n + NB - 1) / NB;
@@ -69,7 +76,10 @@ __global__ void __launch_bounds__(QB) netvlad_exact_kernel(ExactParams p) {
       for (int e = tid; e < QB * DC; e += QB) {
         const int r = e / DC, c = e % DC;
         double v = 0.0;
-        if (q0 + r < p.nq && kc + c < p.D) v = p.q[(size_t)(q0 + r) * p.D + kc + c];
+        if (q0 + r < n_act && kc + c < p.D) {
+          const int qr = p.row_list ? p.row_list[q0 + r] : q0 + r;
+          v = p.q[(size_t)qr * p.D + kc + c];
+        }
         q_s[r * DC + ((((c >> 1) ^ (r & 31)) << 1) | (c & 1))] = v;
       }
       for (int e = tid; e < NB * DC; e += QB) {
@@ -123,7 +133,7 @@ __global__ void __launch_bounds__(QB) netvlad_exact_kernel(ExactParams p) {
     }
   }
   if (qi < p.nq) {
-    const size_t o = ((size_t)blockIdx.y * p.nq + qi) * k;
+    const size_t o = ((size_t)blockIdx.y * p.nq + qpos) * k;
     for (int j = 0; j < k; ++j) {
       p.out_idx[o + j] = top_i[j * QB + tid];
       p.out_dist[o + j] = top_d[j * QB + tid];
@@ -133,9 +143,11 @@ __global__ void __launch_bounds__(QB) netvlad_exact_kernel(ExactParams p) {
 
 // merge `lists` sorted top-k lists per row (layout [lists][nq][k]) into one; thread per row
 __global__ void topk_merge_kernel(const int32_t* __restrict__ in_idx, const double* __restrict__ in_dist, int lists,
-                                  int nq, int k, int32_t* __restrict__ out_idx, double* __restrict__ out_dist) {
+                                  int nq, int k, int32_t* __restrict__ out_idx, double* __restrict__ out_dist,
+                                  const int32_t* __restrict__ row_list, const int32_t* __restrict__ n_rows) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= nq) return;
+  if (q >= (n_rows ? min(*n_rows, nq) : nq)) return;
+  const int qo = row_list ? row_list[q] : q;   // gather mode: scatter to the original row
   int head[64];
   for (int l = 0; l < lists; ++l) head[l] = 0;
   for (int j = 0; j < k; ++j) {
@@ -154,8 +166,8 @@ __global__ void topk_merge_kernel(const int32_t* __restrict__ in_idx, const doub
         bi = i;
       }
     }
-    out_idx[(size_t)q * k + j] = bi;
-    out_dist[(size_t)q * k + j] = bl < 0 ? INFINITY : bd;
+    out_idx[(size_t)qo * k + j] = bi;
+    out_dist[(size_t)qo * k + j] = bl < 0 ? INFINITY : bd;
     if (bl >= 0) head[bl]++;
   }
 }
@@ -165,10 +177,15 @@ __global__ void topk_merge_kernel(const int32_t* __restrict__ in_idx, const doub
 int sepb_launch_netvlad_exact(sepb_ctx* ctx, const double* d_q, int nq, const double* d_db, int n, int D, int k,
                               int64_t base, const uint8_t* d_row_mask, const uint8_t* d_col_mask,
                               const int32_t* d_ign_start, const int32_t* d_ign_col, int splits, int32_t* d_part_idx,
-                              double* d_part_dist, int32_t* d_out_idx, double* d_out_dist) {
+                              double* d_part_dist, int32_t* d_out_idx, double* d_out_dist, const int32_t* d_row_list,
+                              const int32_t* d_n_rows) {
   if (nq == 0) return SEPB_OK;
+  const bool gather = d_row_list != nullptr;
+  if (gather && (!d_part_idx || !d_part_dist || !d_n_rows))
+    return sepb_fail(ctx, SEPB_E_INVALID, "netvlad_exact: gather mode needs partial buffers", __FILE__, __LINE__);
+  const bool two_pass = splits > 1 || gather;
   ExactParams p{d_q, d_db, nq, n, D, k, base, d_row_mask, d_col_mask, d_ign_start, d_ign_col, splits,
-                splits > 1 ? d_part_idx : d_out_idx, splits > 1 ? d_part_dist : d_out_dist};
+                two_pass ? d_part_idx : d_out_idx, two_pass ? d_part_dist : d_out_dist, d_row_list, d_n_rows};
   const size_t smem = (size_t)(QB * DC + NB * DC + KMAX * QB) * 8 + (size_t)KMAX * QB * 4;
   bool& configured = ctx->cfg_exact;
   if (!configured) {
@@ -179,8 +196,9 @@ int sepb_launch_netvlad_exact(sepb_ctx* ctx, const double* d_q, int nq, const do
   netvlad_exact_kernel<<<grid, QB, smem, ctx->stream>>>(p);
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());
-  if (splits > 1) {
-    topk_merge_kernel<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(d_part_idx, d_part_dist, splits, nq, k, d_out_idx, d_out_dist);
+  if (two_pass) {
+    topk_merge_kernel<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(d_part_idx, d_part_dist, splits, nq, k, d_out_idx,
+                                                                 d_out_dist, d_row_list, d_n_rows);
     ctx->launches++;
     SEPB_CUDA(ctx, cudaGetLastError());
   }
@@ -191,7 +209,8 @@ int sepb_launch_topk_merge(sepb_ctx* ctx, const int32_t* d_in_idx, const double*
                            int32_t* d_out_idx, double* d_out_dist) {
   if (nq == 0) return SEPB_OK;
   if (lists > 64) return sepb_fail(ctx, SEPB_E_SHAPE, "topk_merge: more than 64 lists", __FILE__, __LINE__);
-  topk_merge_kernel<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(d_in_idx, d_in_dist, lists, nq, k, d_out_idx, d_out_dist);
+  topk_merge_kernel<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(d_in_idx, d_in_dist, lists, nq, k, d_out_idx, d_out_dist,
+                                                               nullptr, nullptr);
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());
   return SEPB_OK;
