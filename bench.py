@@ -379,7 +379,8 @@ def main():
     ap.add_argument("--feat", type=int, default=1000)
     ap.add_argument("--dim", type=int, default=128)
     ap.add_argument("--topk", type=int, default=5)
-    ap.add_argument("--nn", default="exact", choices=["exact", "tensor"])
+    ap.add_argument("--nn", default="tensor", choices=["exact", "tensor"],
+                    help="NetVLAD search: tcgen05 split-bf16 filter + exact f64 re-rank (tensor) or full f64 scan (exact); identical results")
     ap.add_argument("--match", default="auto", choices=["auto", "popc", "tensor"],
                     help="Hamming matcher kernel: tcgen05 int8 GEMM (tensor), POPC pipe (popc); identical results")
     ap.add_argument("--e2e-steps", type=int, default=2)

@@ -134,7 +134,8 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
                    uint16_t* __restrict__ match_from, uint16_t* __restrict__ match_to,
                    int32_t* __restrict__ n_unique_to) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  // 1024-byte alignment by pointer arithmetic on the shared array (keeps the shared address space: LDS/STS, not LD.E)
+  uint8_t* smem = smem_raw + ((1024u - (umma::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sB = smem;                                  // [2 K-blocks][CH][128]
   uint8_t* sA = sB + kBBytes;                          // [2 buffers][2 K-blocks][TM][128]
   uint8_t* sBx = sA + 2 * kABytes;                     // [CH/8][2][8][16]

@@ -116,7 +116,8 @@ __global__ void netvlad_split_kernel(const double* __restrict__ src, int r0, int
 __global__ void __launch_bounds__(kThreads, 1)
 netvlad_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmD, GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  // 1024-byte alignment by pointer arithmetic on the shared array (keeps the shared address space: LDS/STS, not LD.E)
+  uint8_t* smem = smem_raw + ((1024u - (umma::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sB = smem;                                        // [kStages][2][BN][128]
   uint8_t* sA = sB + kStages * 2 * kBBlockBytes;             // [2 * kStages slots][BM][128]
   float* s_lv = reinterpret_cast<float*>(sA + 2 * kStages * kABlockBytes);   // [2 groups][KP][128]
@@ -691,6 +692,10 @@ int sepb_netvlad_tensor_topk(sepb_ctx* ctx, const sepb_db* cdb, const double* d_
   const int row_blocks = (nq + BM - 1) / BM, tiles_n = (n + BN - 1) / BN;
   int splits, grid;
   choose_splits(ctx->sm_count, row_blocks, tiles_n, &splits, &grid);
+  if (const char* e = getenv("SEPB_K1_SPLITS")) {   // developer override
+    splits = std::max(1, std::min(atoi(e), std::min(tiles_n, kMaxLists / 2)));
+    grid = std::min(ctx->sm_count, row_blocks * splits);
+  }
   const int lists = 2 * splits;
   const int fb_splits = std::max(1, std::min(64, (n + 31) / 32));
   size_t off = 0;
