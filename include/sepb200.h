@@ -218,6 +218,9 @@ SEPB_API int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const
 /* ---- measurement support (roofline denominators not in MEASURED_PEAKS.json) ----------------
  * kind 0: POPC instructions/s (K2's bounding pipe), kind 1: FP64 FMA/s (K3's).  Best of reps. */
 SEPB_API int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s);
+/* developer hook (K3): cycle counters {EPnP solve, Rodrigues, scoring, refit, chunk-solves, 12x12 Jacobi, Jacobi
+ * sweeps, 0} summed over warps; all zero and return 0 unless the library was built with SEPB_K3_PROFILE=1. */
+SEPB_API int sepb_debug_k3_prof(unsigned long long* out8, int reset);
 
 #ifdef __cplusplus
 }

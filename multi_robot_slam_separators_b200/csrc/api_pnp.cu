@@ -64,8 +64,8 @@ void sepb_pnp_set_guess(sepb_pnp_params* p, const double* G) {
     for (int j = 0; j < 3; ++j) Rinv[3 * i + j] = RP[3 * j + i];
   for (int i = 0; i < 3; ++i)
     p->guess_tvec[i] = (double)(float)(-(Rinv[3 * i] * tP[0] + Rinv[3 * i + 1] * tP[1] + Rinv[3 * i + 2] * tP[2]));
-  double scratch[21];
-  cvm::rodrigues_mat_to_vec(cvm::Heap{scratch, 1}, Rinv, p->guess_rvec);
+  double scratch[21 * cvm::kHeapStride];   // host call of the strided-heap routine
+  cvm::rodrigues_mat_to_vec(cvm::Heap{scratch}, Rinv, p->guess_rvec);
 }
 
 int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,

@@ -12,18 +12,32 @@
 // the x86-64 SSE2 build of cv2.  Written __host__ __device__ so the same text can be checked against
 // cv2 on the CPU by tests/host_harness (test-only build; the product path is the CUDA kernel).
 //
-// Storage: `Heap` is a strided view of per-thread scratch (stride 32 doubles in shared memory so
-// that the 32 lanes of a warp hit 32 different banks; stride 1 on the host).
+// Storage: `Heap` is a strided view of per-thread scratch (stride 16 doubles in shared memory: the
+// 16 solving lanes of a warp cover all 32 banks exactly once; stride 1 in the host test build).
 #pragma once
 #include <math.h>
 #include <stdint.h>
 
-#if defined(__CUDACC__)
+#if defined(__CUDACC__) && defined(SEPB_K3_PROFILE)
+#define CVM_HD __device__   // the counters of the developer build are device-only
+#define CVM_NOINLINE __noinline__
+#define CVM_UNROLL _Pragma("unroll")
+#define CVM_NOUNROLL _Pragma("unroll 1")
+#elif defined(__CUDACC__)
 #define CVM_HD __host__ __device__
 #define CVM_NOINLINE __noinline__
+#define CVM_UNROLL _Pragma("unroll")
+#define CVM_NOUNROLL _Pragma("unroll 1")
 #else
 #define CVM_HD
 #define CVM_NOINLINE __attribute__((noinline))
+#define CVM_UNROLL
+#define CVM_NOUNROLL
+#endif
+
+#ifndef K3_T0   // phase counters of the developer build (pnp_ransac.cu); no-ops everywhere else
+#define K3_T0(v)
+#define K3_ACC(slot, v)
 #endif
 
 namespace cvm {
@@ -35,11 +49,17 @@ struct Intrinsics {
   double fx, fy, cx, cy;
 };
 
+// compile-time stride: element i of a thread's scratch lives at p[i * kHeapStride], so every access with
+// a constant index is one LDS with an immediate offset (no 64-bit address arithmetic in the hot loops)
+#if defined(__CUDACC__)
+constexpr int kHeapStride = 32;   // == lanes of a warp that solve hypotheses at the same time (pnp_ransac.cu)
+#else
+constexpr int kHeapStride = 1;
+#endif
 struct Heap {
   double* p;
-  int stride;
-  CVM_HD double& operator[](int i) const { return p[(size_t)i * stride]; }
-  CVM_HD Heap at(int off) const { return Heap{p + (size_t)off * stride, stride}; }
+  CVM_HD double& operator[](int i) const { return p[i * kHeapStride]; }
+  CVM_HD Heap at(int off) const { return Heap{p + off * kHeapStride}; }
 };
 
 // cv::RNG (multiply-with-carry)
@@ -70,27 +90,40 @@ CVM_HD inline double cv_hypot(double a, double b) {
 // JacobiSVDImpl_<double>: At is n rows of length m (row r at At[r*m + k]); on return rows of At are the
 // unit left singular vectors of A = At^T, W descending, Vt (n x n, optional) the right vectors.
 // n1 = number of rows to normalise / complete (== n at every call site on this path).
-CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt, bool want_v, int m, int n) {
+// m, n, want_v are template parameters so that the loops over k unroll: the loads of a rotation are
+// issued together and the independent element updates overlap; the ORDER of the arithmetic on every
+// accumulator is unchanged (sequential in k), which is what bit-exactness against cv2 needs.
+template <int m, int n, bool want_v>
+CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
   const double eps = kDblEps * 10;
   for (int i = 0; i < n; ++i) {
     double sd = 0;
+    CVM_UNROLL
     for (int k = 0; k < m; ++k) {
       const double t = At[i * m + k];
       sd += t * t;
     }
     W[i] = sd;
     if (want_v) {
+      CVM_UNROLL
       for (int k = 0; k < n; ++k) Vt[i * n + k] = 0;
       Vt[i * n + i] = 1;
     }
   }
   const int max_iter = m > 30 ? m : 30;
+  CVM_NOUNROLL
   for (int iter = 0; iter < max_iter; ++iter) {
     bool changed = false;
+#if defined(SEPB_K3_PROFILE) && defined(__CUDA_ARCH__)
+    if (m == 12 && (threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[6], 1ull);
+#endif
+    CVM_NOUNROLL
     for (int i = 0; i < n - 1; ++i)
+      CVM_NOUNROLL
       for (int j = i + 1; j < n; ++j) {
         const Heap Ai = At.at(i * m), Aj = At.at(j * m);
         double a = W[i], p = 0, b = W[j];
+        CVM_UNROLL
         for (int k = 0; k < m; ++k) p += Ai[k] * Aj[k];
         if (fabs(p) <= eps * sqrt(a * b)) continue;
         p *= 2;
@@ -105,6 +138,7 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt, bool want_v
           s = p / (gamma * c * 2);
         }
         a = b = 0;
+        CVM_UNROLL
         for (int k = 0; k < m; ++k) {
           const double x = Ai[k], y = Aj[k];
           const double t0 = c * x + s * y;
@@ -119,6 +153,7 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt, bool want_v
         changed = true;
         if (want_v) {
           const Heap Vi = Vt.at(i * n), Vj = Vt.at(j * n);
+          CVM_UNROLL
           for (int k = 0; k < n; ++k) {
             const double x = Vi[k], y = Vj[k];
             Vi[k] = c * x + s * y;
@@ -128,14 +163,17 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt, bool want_v
       }
     if (!changed) break;
   }
+  CVM_NOUNROLL
   for (int i = 0; i < n; ++i) {
     double sd = 0;
+    CVM_UNROLL
     for (int k = 0; k < m; ++k) {
       const double t = At[i * m + k];
       sd += t * t;
     }
     W[i] = sqrt(sd);
   }
+  CVM_NOUNROLL
   for (int i = 0; i < n - 1; ++i) {
     int j = i;
     for (int k = i + 1; k < n; ++k)
@@ -148,26 +186,35 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt, bool want_v
     }
   }
   Rng rng(0x12345678);
+  CVM_NOUNROLL
   for (int i = 0; i < n; ++i) {
     double sd = W[i];
+    CVM_NOUNROLL
     for (int ii = 0; ii < 100 && sd <= kDblMin; ++ii) {
       // zero singular value: random +-1/m vector, orthogonalised against the previous rows
       const double val0 = 1. / m;
+      CVM_NOUNROLL
       for (int k = 0; k < m; ++k) At[i * m + k] = (rng.next() & 256) != 0 ? val0 : -val0;
+      CVM_NOUNROLL
       for (int it = 0; it < 2; ++it)
+        CVM_NOUNROLL
         for (int j = 0; j < i; ++j) {
           sd = 0;
+          CVM_NOUNROLL
           for (int k = 0; k < m; ++k) sd += At[i * m + k] * At[j * m + k];
           double asum = 0;
+          CVM_NOUNROLL
           for (int k = 0; k < m; ++k) {
             const double t = At[i * m + k] - sd * At[j * m + k];
             At[i * m + k] = t;
             asum += fabs(t);
           }
           asum = asum > eps * 100 ? 1 / asum : 0;
+          CVM_NOUNROLL
           for (int k = 0; k < m; ++k) At[i * m + k] *= asum;
         }
       sd = 0;
+      CVM_NOUNROLL
       for (int k = 0; k < m; ++k) {
         const double t = At[i * m + k];
         sd += t * t;
@@ -175,6 +222,7 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt, bool want_v
       sd = sqrt(sd);
     }
     const double s = sd > kDblMin ? 1 / sd : 0.;
+    CVM_UNROLL
     for (int k = 0; k < m; ++k) At[i * m + k] *= s;
   }
 }

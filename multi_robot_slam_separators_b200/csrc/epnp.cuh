@@ -21,11 +21,11 @@ CVM_HD inline double dot3(const double* a, const double* b) { return a[0] * b[0]
 
 // cvSolve(A[6 x NC], rho, x, CV_SVD) with A's columns picked from L_6x10
 template <int NC>
-CVM_HD inline void solve_cols(Heap h, const int (&cols)[NC], const double* rho, double* x) {
+CVM_HD CVM_NOINLINE inline void solve_cols(Heap h, const int (&cols)[NC], const double* rho, double* x) {
   Heap At = h.at(H_SAT), W = h.at(H_SW), Vt = h.at(H_SVT);
   for (int c = 0; c < NC; ++c)
     for (int r = 0; r < 6; ++r) At[c * 6 + r] = h[H_L + r * 10 + cols[c]];
-  jacobi_svd(At, W, Vt, true, 6, NC);
+  jacobi_svd<6, NC, true>(At, W, Vt);
   svd_backsubst(At, W, Vt, 6, NC, rho, x);
 }
 
@@ -99,7 +99,7 @@ CVM_HD inline bool qr_solve_6x4(double* A, double* b, double* X) {
   return true;
 }
 
-CVM_HD inline void gauss_newton(Heap h, const double* rho, double* betas) {
+CVM_HD CVM_NOINLINE inline void gauss_newton(Heap h, const double* rho, double* betas) {
   double x_stale[4] = {0, 0, 0, 0};  // epnp::gauss_newton's local x[4] = {}
   for (int it = 0; it < 5; ++it) {
     double A[24], b[6];
@@ -124,7 +124,7 @@ CVM_HD inline void gauss_newton(Heap h, const double* rho, double* betas) {
 }
 
 // compute_ccs / compute_pcs / solve_for_sign / estimate_R_and_t / reprojection_error
-CVM_HD inline double compute_R_and_t(Heap h, const float* o, const double* us, const Intrinsics& K, const double* betas,
+CVM_HD CVM_NOINLINE inline double compute_R_and_t(Heap h, const float* o, const double* us, const Intrinsics& K, const double* betas,
                                      double* R, double* t) {
   double ccs[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
   for (int i = 0; i < 4; ++i) {
@@ -163,7 +163,7 @@ CVM_HD inline double compute_R_and_t(Heap h, const float* o, const double* us, c
   Heap At = h.at(H_SAT), W = h.at(H_SW), Vt = h.at(H_SVT);
   for (int r = 0; r < 3; ++r)
     for (int c = 0; c < 3; ++c) At[c * 3 + r] = abt[3 * r + c];
-  jacobi_svd(At, W, Vt, true, 3, 3);
+  jacobi_svd<3, 3, true>(At, W, Vt);
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j)
       R[3 * i + j] = At[0 * 3 + i] * Vt[0 * 3 + j] + At[1 * 3 + i] * Vt[1 * 3 + j] + At[2 * 3 + i] * Vt[2 * 3 + j];
@@ -193,7 +193,7 @@ CVM_HD inline double compute_R_and_t(Heap h, const float* o, const double* us, c
 }  // namespace detail
 
 // o: 5 object points (f32 xyz), im: 5 image points (f32 pixel uv).  Outputs R (row-major), t.
-CVM_HD inline void epnp5(Heap h, const float* o, const float* im, const Intrinsics& K, double* R, double* t) {
+CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, const Intrinsics& K, double* R, double* t) {
   using namespace detail;
   // undistortPoints (no distortion): double math, stored as f32; epnp::init_points rescales in double
   const double ifx = 1. / K.fx, ify = 1. / K.fy;
@@ -222,7 +222,7 @@ CVM_HD inline void epnp5(Heap h, const float* o, const float* im, const Intrinsi
     Heap At = h.at(0), W = h.at(9), Vt = h.at(12);
     for (int r = 0; r < 3; ++r)
       for (int c = 0; c < 3; ++c) At[c * 3 + r] = ptp[3 * r + c];
-    jacobi_svd(At, W, Vt, true, 3, 3);
+    jacobi_svd<3, 3, true>(At, W, Vt);
     for (int j = 0; j < 3; ++j) h[H_CWS + j] = c0[j];
     for (int i = 1; i < 4; ++i) {
       const double k = sqrt(W[i - 1] / kN);
@@ -235,7 +235,7 @@ CVM_HD inline void epnp5(Heap h, const float* o, const float* im, const Intrinsi
     // CC[i][j-1] = cws[j][i] - cws[0][i]; Jacobi runs on rows of CC^T: At[c][r] = CC[r][c]
     for (int i = 0; i < 3; ++i)
       for (int j = 1; j < 4; ++j) At[(j - 1) * 3 + i] = h[H_CWS + 3 * j + i] - h[H_CWS + i];
-    jacobi_svd(At, W, Vt, true, 3, 3);
+    jacobi_svd<3, 3, true>(At, W, Vt);
     double ci[9];
     for (int c = 0; c < 3; ++c) {
       const double e[3] = {c == 0 ? 1. : 0., c == 1 ? 1. : 0., c == 2 ? 1. : 0.};
@@ -273,7 +273,9 @@ CVM_HD inline void epnp5(Heap h, const float* o, const float* im, const Intrinsi
         At[a * 12 + b] = s;  // symmetric: row a of MtM^T == row a of MtM
         At[b * 12 + a] = s;
       }
-    jacobi_svd(At, h.at(H_W), h.at(H_W), false, 12, 12);
+    K3_T0(t_j);
+    jacobi_svd<12, 12, false>(At, h.at(H_W), h.at(H_W));
+    K3_ACC(5, t_j);
   }
   // ---- L_6x10 and rho
   {

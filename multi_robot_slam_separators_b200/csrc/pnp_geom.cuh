@@ -7,11 +7,11 @@
 namespace cvm {
 
 // 3x3 -> rvec: orthonormalise through SVD (R = U Vt), then axis-angle.  scratch: >= 21 doubles.
-CVM_HD inline void rodrigues_mat_to_vec(Heap scratch, const double* Rin, double* r) {
+CVM_HD CVM_NOINLINE inline void rodrigues_mat_to_vec(Heap scratch, const double* Rin, double* r) {
   Heap At = scratch.at(0), W = scratch.at(9), Vt = scratch.at(12);
   for (int i = 0; i < 3; ++i)
     for (int c = 0; c < 3; ++c) At[c * 3 + i] = Rin[3 * i + c];
-  jacobi_svd(At, W, Vt, true, 3, 3);
+  jacobi_svd<3, 3, true>(At, W, Vt);
   double R[9];
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j)

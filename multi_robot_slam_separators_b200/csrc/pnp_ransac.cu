@@ -12,12 +12,24 @@
 // one, which reproduces the sequential result exactly and keeps most of its early exit.
 // Compiled with -fmad=false (see build.py): no multiply-add contraction, like the cv2 build.
 #include "common.cuh"
+
+// developer build (SEPB_K3_PROFILE=1 python -m ...build): cycle counters per phase, read by sepb_debug_k3_prof
+#ifdef SEPB_K3_PROFILE
+__device__ unsigned long long g_k3_prof[8];
+#define K3_T0(v) const long long v = clock64()
+#define K3_ACC(slot, v) if ((threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[slot], (unsigned long long)(clock64() - (v)))
+#else
+#define K3_T0(v)
+#define K3_ACC(slot, v)
+#endif
+
 #include "epnp.cuh"
 #include "pnp_geom.cuh"
 
 namespace {
 
 constexpr int kWarp = 32;
+constexpr int kSolveLanes = cvm::kHeapStride;   // hypotheses solved at once by a warp (one lane each)
 constexpr int kMaskWords = SEPB_MAX_FEATURES / 32;
 
 struct PnpKernelParams {
@@ -76,7 +88,7 @@ struct Corr {  // correspondence accessor of one pair
 };
 
 // residuals / normal equations of the ITERATIVE refit over the inlier set, warp-cooperative
-__device__ void lm_accumulate(const Corr& cr, const uint32_t* mask, int M, const cvm::Intrinsics& K, const double* param,
+__device__ __noinline__ void lm_accumulate(const Corr& cr, const uint32_t* mask, int M, const cvm::Intrinsics& K, const double* param,
                               bool want_jac, double* JtJ /*21 upper*/, double* JtE /*6*/, double& err2) {
   const int lane = threadIdx.x & 31;
   double R[9], dRdr[27];
@@ -132,7 +144,7 @@ __device__ void lm_accumulate(const Corr& cr, const uint32_t* mask, int M, const
 }
 
 // CvLevMarq::step(): (JtJ with diag *= 1 + lambda) x = JtErr by SVD; param = prev - x
-__device__ void lm_step(cvm::Heap h, const double* JtJ, const double* JtE, int lambda_lg10, const double* prev,
+__device__ __noinline__ void lm_step(cvm::Heap h, const double* JtJ, const double* JtE, int lambda_lg10, const double* prev,
                         double* param) {
   const double lambda = exp(lambda_lg10 * log(10.));
   cvm::Heap At = h.at(0), W = h.at(36), Vt = h.at(42);
@@ -144,10 +156,19 @@ __device__ void lm_step(cvm::Heap h, const double* JtJ, const double* JtE, int l
       At[b * 6 + a] = v;
     }
   for (int a = 0; a < 6; ++a) At[a * 6 + a] = At[a * 6 + a] * (1. + lambda);
-  cvm::jacobi_svd(At, W, Vt, true, 6, 6);
+  cvm::jacobi_svd<6, 6, true>(At, W, Vt);
   double x[6];
   cvm::svd_backsubst(At, W, Vt, 6, 6, JtE, x);
   for (int i = 0; i < 6; ++i) param[i] = prev[i] - x[i];
+}
+
+// every lane needs the new parameters, but only the first kSolveLanes lanes own scratch: lane 0's result is broadcast
+__device__ __forceinline__ void lm_step_warp(cvm::Heap h, const double* JtJ, const double* JtE, int lambda_lg10,
+                                             const double* prev, double* param) {
+  if ((threadIdx.x & 31) < kSolveLanes) lm_step(h, JtJ, JtE, lambda_lg10, prev, param);
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < 6; ++i) param[i] = __shfl_sync(0xFFFFFFFFu, param[i], 0);
 }
 
 __global__ void __launch_bounds__(kWarp)
@@ -161,11 +182,11 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
                   int32_t* __restrict__ best_hyp, int32_t* __restrict__ iters_run) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   double* heap_base = reinterpret_cast<double*>(smem_raw);
-  uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)cvm::kEpnpHeap * 32 * 8);  // 2 * kMaskWords
+  uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)cvm::kEpnpHeap * kSolveLanes * 8);  // 2 * kMaskWords
   const int lane = threadIdx.x;
   const int pair = blockIdx.x;
   if (pair >= n_pairs) return;
-  const cvm::Heap heap{heap_base + lane, 32};
+  const cvm::Heap heap{heap_base + lane};
   int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
   const bool valid_pair = fi >= 0 && fi < from.size && ti >= 0 && ti < to.size;
   if (!valid_pair) fi = ti = 0;
@@ -219,9 +240,11 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
   if (M == 5) {  // count == modelPoints: one EPnP over all five, no refit, all inliers
     float o[15], im[10];
     for (int i = 0; i < 5; ++i) cr.load(i, o + 3 * i, im + 2 * i);
-    double R[9], p6[6];
-    cvm::epnp5(heap, o, im, prm.K, R, p6 + 3);
-    cvm::rodrigues_mat_to_vec(heap, R, p6);
+    double R[9], p6[6] = {0, 0, 0, 0, 0, 0};
+    if (lane < kSolveLanes) {   // only these lanes own a slice of the scratch heap; lane 0 reports
+      cvm::epnp5(heap, o, im, prm.K, R, p6 + 3);
+      cvm::rodrigues_mat_to_vec(heap, R, p6);
+    }
     if (out_mask && lane == 0) out_mask[0] = 0x1Fu;
     finish(5 >= prm.min_inliers ? 1 : 3, 5, p6, 0, 1);
     return;
@@ -229,26 +252,32 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
 
   int niters = prm.iterations > 1 ? prm.iterations : 1;
   int best_good = 0, best_h = -1, cur = 0, hk = 0;
-  for (int chunk = 0; chunk < niters; chunk += 32) {
-    // ---- solve: lane <-> hypothesis
+  for (int chunk = 0; chunk < niters; chunk += kSolveLanes) {
+    // ---- solve: lane <-> hypothesis (the first kSolveLanes lanes; more resident warps hide the f64 latency
+    //      better than wider warps, and shorter chunks waste fewer hypotheses past the adaptive stop)
     int h = chunk + lane;
     if (h >= niters) h = niters - 1;
-    float o[15], im[10];
-    for (int i = 0; i < 5; ++i) {
-      const int s = custom_samples ? custom_samples[((size_t)pair * custom_h + h) * 5 + i]
-                                   : table[((size_t)M * prm.table_h + h) * 5 + i];
-      cr.load(min(max(s, 0), M - 1), o + 3 * i, im + 2 * i);
-    }
-    double Rh[9], th[3];
-    {
+    double Rh[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, th[3] = {0, 0, 0};
+    if (lane < kSolveLanes) {
+      float o[15], im[10];
+      for (int i = 0; i < 5; ++i) {
+        const int s = custom_samples ? custom_samples[((size_t)pair * custom_h + h) * 5 + i]
+                                     : table[((size_t)M * prm.table_h + h) * 5 + i];
+        cr.load(min(max(s, 0), M - 1), o + 3 * i, im + 2 * i);
+      }
       double R0[9], rv[3];
+      K3_T0(t_e);
       cvm::epnp5(heap, o, im, prm.K, R0, th);
+      K3_ACC(0, t_e);
+      K3_T0(t_r);
       cvm::rodrigues_mat_to_vec(heap, R0, rv);   // runKernel hands the model on as rvec
       cvm::rodrigues_vec_to_mat(rv, Rh, nullptr);  // projectPoints turns it back into a matrix
+      K3_ACC(1, t_r);
     }
     __syncwarp();
+    K3_T0(t_s);
     // ---- score: warp <-> hypothesis, in RANSAC order
-    for (int k = 0; k < 32; ++k) {
+    for (int k = 0; k < kSolveLanes; ++k) {
       hk = chunk + k;
       if (hk >= niters) break;
       double R[9], t[3];
@@ -278,8 +307,13 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
       }
       hk = hk + 1;
     }
+    K3_ACC(2, t_s);
+#ifdef SEPB_K3_PROFILE
+    if (lane == 0) atomicAdd(&g_k3_prof[4], 1ull);
+#endif
   }
   __syncwarp();
+  K3_T0(t_lm);
   if (best_h < 0) {
     finish(2, 0, g, -1, hk);
     return;
@@ -299,14 +333,14 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
   for (;;) {
     // CALC_J
     for (int i = 0; i < 6; ++i) prev[i] = param[i];
-    lm_step(heap, JtJ, JtE, lambda_lg10, prev, param);
+    lm_step_warp(heap, JtJ, JtE, lambda_lg10, prev, param);
     if (iters == 0) prev_err_norm = sqrt(err2);
     double dJ[21], dE[6];
     lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
     // CHECK_ERR
     double err_norm = sqrt(err2);
     while (err_norm > prev_err_norm && ++lambda_lg10 <= 16) {
-      lm_step(heap, JtJ, JtE, lambda_lg10, prev, param);
+      lm_step_warp(heap, JtJ, JtE, lambda_lg10, prev, param);
       lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
       err_norm = sqrt(err2);
     }
@@ -320,12 +354,29 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
     prev_err_norm = err_norm;
     lm_accumulate(cr, best, M, prm.K, param, true, JtJ, JtE, err2);
   }
+  K3_ACC(3, t_lm);
   finish(best_good >= prm.min_inliers ? 1 : 3, best_good, param, best_h, hk);
 }
 
 }  // namespace
 
-struct PnpLaunchArgs;  // (reserved)
+// developer hook: {epnp5, rodrigues, scoring, refit} cycles summed over warps, chunk-solves; zeros unless built with
+// SEPB_K3_PROFILE.  reset != 0 clears the counters.
+extern "C" SEPB_API int sepb_debug_k3_prof(unsigned long long* out8, int reset) {
+#ifdef SEPB_K3_PROFILE
+  cudaDeviceSynchronize();
+  if (out8) cudaMemcpyFromSymbol(out8, g_k3_prof, sizeof(unsigned long long) * 8);
+  if (reset) {
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaMemcpyToSymbol(g_k3_prof, z, sizeof z);
+  }
+  return 1;
+#else
+  if (out8) for (int i = 0; i < 8; ++i) out8[i] = 0;
+  (void)reset;
+  return 0;
+#endif
+}
 
 int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H) {
   const int threads = 128;
@@ -356,7 +407,7 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   }
   for (int i = 0; i < 9; ++i) k.local_R[i] = p->local_R[i];
   k.table_h = table_h;
-  const size_t smem = (size_t)cvm::kEpnpHeap * 32 * 8 + 2 * kMaskWords * 4;
+  const size_t smem = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
   bool& configured = ctx->cfg_pnp;
   if (!configured) {
     SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -6,15 +6,24 @@
 
 extern "C" {
 
-void hh_svd(double* At, int m, int n, double* W, double* Vt) {
-  cvm::jacobi_svd(cvm::Heap{At, 1}, cvm::Heap{W, 1}, cvm::Heap{Vt, 1}, true, m, n);
+// the product instantiates the Jacobi SVD per shape; returns -1 for a shape the path never uses
+int hh_svd(double* At, int m, int n, double* W, double* Vt) {
+  const cvm::Heap a{At}, w{W}, v{Vt};
+  if (m == 12 && n == 12) cvm::jacobi_svd<12, 12, true>(a, w, v);
+  else if (m == 3 && n == 3) cvm::jacobi_svd<3, 3, true>(a, w, v);
+  else if (m == 6 && n == 3) cvm::jacobi_svd<6, 3, true>(a, w, v);
+  else if (m == 6 && n == 4) cvm::jacobi_svd<6, 4, true>(a, w, v);
+  else if (m == 6 && n == 5) cvm::jacobi_svd<6, 5, true>(a, w, v);
+  else if (m == 6 && n == 6) cvm::jacobi_svd<6, 6, true>(a, w, v);
+  else return -1;
+  return 0;
 }
 
 void hh_epnp5(const float* obj, const float* img, const double* K4, double* R, double* t, double* rvec, double* R2) {
   double heap[cvm::kEpnpHeap];
   cvm::Intrinsics K{K4[0], K4[1], K4[2], K4[3]};
-  cvm::epnp5(cvm::Heap{heap, 1}, obj, img, K, R, t);
-  cvm::rodrigues_mat_to_vec(cvm::Heap{heap, 1}, R, rvec);
+  cvm::epnp5(cvm::Heap{heap}, obj, img, K, R, t);
+  cvm::rodrigues_mat_to_vec(cvm::Heap{heap}, R, rvec);
   cvm::rodrigues_vec_to_mat(rvec, R2, nullptr);
 }
 
