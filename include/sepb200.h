@@ -74,6 +74,14 @@ SEPB_API int sepb_frames_size(const sepb_frames* f);
 SEPB_API int sepb_frames_upload(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc,
                        const float* kp2d, const float* kp3d, const int32_t* octave, const int32_t* count);
 
+/* Same, without waiting: the copies run on the context's copy stream, concurrently with kernels already enqueued
+ * (the next round's keyframes travel while the current round is verified).  The host arrays must stay valid (and
+ * should be pinned) until sepb_frames_wait() or any later synchronising call that uses the store returns.  Kernels
+ * enqueued afterwards wait for the upload on the device; an upload waits for kernels that still read the store. */
+SEPB_API int sepb_frames_upload_async(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc,
+                                      const float* kp2d, const float* kp3d, const int32_t* octave, const int32_t* count);
+SEPB_API int sepb_frames_wait(sepb_ctx* ctx, sepb_frames* f);
+
 /* ---- K2: brute-force Hamming 2-NN + NNDR + one-to-one filter ----------------------------
  * Replaces the global matching block R/src/myRegistrationVis.cpp:839-894 in brute-force mode
  * (VWDictionary::addNewWords(descriptorsTo, 2) == cv::BFMatcher(NORM_HAMMING).knnMatch(k=2),
@@ -210,6 +218,12 @@ typedef struct sepb_verify_out {
 SEPB_API int sepb_verify_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
                                int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
                                const int32_t* custom_samples, int custom_h, sepb_verify_out* out);
+/* same call, returning as soon as the work (H2D of the pair list, K2, K3, D2H of the results) is enqueued: `pairs`
+ * and the arrays inside `out` must be pinned host memory and stay untouched until sepb_ctx_sync(ctx) returns.  Lets
+ * a caller start the next round's sepb_frames_upload_async behind it (double-buffered stores). */
+SEPB_API int sepb_verify_pairs_async(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                                     int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                                     const int32_t* custom_samples, int custom_h, sepb_verify_out* out);
 /* same, everything (pairs and the arrays inside `out`) in device memory, asynchronous on the ctx stream */
 SEPB_API int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
                                    int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,

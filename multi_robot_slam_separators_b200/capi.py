@@ -81,8 +81,12 @@ def _declare(L):
     L.sepb_frames_destroy.restype = None
     L.sepb_frames_size.argtypes = [vp]
     L.sepb_frames_size.restype = i32
-    L.sepb_frames_upload.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp]
-    L.sepb_frames_upload.restype = i32
+    for name in ("sepb_frames_upload", "sepb_frames_upload_async"):
+        f = getattr(L, name)
+        f.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp]
+        f.restype = i32
+    L.sepb_frames_wait.argtypes = [vp, vp]
+    L.sepb_frames_wait.restype = i32
     L.sepb_measure_peak.argtypes = [vp, i32, i32, C.POINTER(C.c_double)]
     L.sepb_measure_peak.restype = i32
     L.sepb_pnp_params_init.argtypes = [C.POINTER(PnpParams), C.c_double, C.c_double, C.c_double, C.c_double]
@@ -116,7 +120,7 @@ def _declare(L):
     L.sepb_topk_merge_dev.restype = i32
     L.sepb_select_matches.argtypes = [vp, vp, i32, C.c_double, i32, vp]
     L.sepb_select_matches.restype = i32
-    for name in ("sepb_verify_pairs", "sepb_verify_pairs_dev"):
+    for name in ("sepb_verify_pairs", "sepb_verify_pairs_dev", "sepb_verify_pairs_async"):
         f = getattr(L, name)
         f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), C.POINTER(PnpParams), vp, i32,
                       C.POINTER(VerifyOut)]
@@ -191,7 +195,9 @@ class Frames:
         self._h = C.c_void_p()
         ctx.check(lib().sepb_frames_create(ctx._h, capacity, max_feat, C.byref(self._h)))
 
-    def upload(self, first, desc, kp2d, kp3d, count, octave=None):
+    def upload(self, first, desc, kp2d, kp3d, count, octave=None, async_=False):
+        """async_=True: enqueue on the copy stream and return (arrays must stay alive, ideally pinned, until
+        wait() or the next blocking call that uses the store)."""
         desc = np.ascontiguousarray(desc, dtype=np.uint8)
         n = desc.shape[0]
         assert desc.shape == (n, self.max_feat, 32)
@@ -200,8 +206,14 @@ class Frames:
         count = np.ascontiguousarray(count, dtype=np.int32).reshape(n)
         if octave is not None:
             octave = np.ascontiguousarray(octave, dtype=np.int32).reshape(n, self.max_feat)
-        self.ctx.check(lib().sepb_frames_upload(self.ctx._h, self._h, first, n, _ptr(desc), _ptr(kp2d), _ptr(kp3d),
-                                                _ptr(octave), _ptr(count)))
+        fn = lib().sepb_frames_upload_async if async_ else lib().sepb_frames_upload
+        self.ctx.check(fn(self.ctx._h, self._h, first, n, _ptr(desc), _ptr(kp2d), _ptr(kp3d), _ptr(octave), _ptr(count)))
+        if async_:
+            self._pending = (desc, kp2d, kp3d, count, octave)     # keep the host arrays alive
+
+    def wait(self):
+        self.ctx.check(lib().sepb_frames_wait(self.ctx._h, self._h))
+        self._pending = None
 
     @property
     def size(self):
@@ -246,18 +258,26 @@ def match_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, nnd
                 n_unique_to=n_unique)
 
 
+def verify_buffers(P, F, want_lists=True, alloc=np.zeros):
+    """Result arrays of verify_pairs; `alloc(shape, dtype)` lets a caller hand in pinned memory."""
+    res = dict(status=alloc(P, np.int32), n_matches=alloc(P, np.int32), n_inliers=alloc(P, np.int32),
+               pose=alloc((P, 6), np.float64), transform=alloc((P, 12), np.float32),
+               best_hyp=alloc(P, np.int32), iters_run=alloc(P, np.int32))
+    if want_lists:
+        res.update(match_from=alloc((P, F), np.uint16), match_to=alloc((P, F), np.uint16),
+                   inlier_mask=alloc((P, (F + 31) // 32), np.uint32))
+    return res
+
+
 def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pnp: PnpParams, nndr=0.8, strict=False,
-                 custom_samples=None, want_lists=True):
+                 custom_samples=None, want_lists=True, out=None, async_=False):
     """Host-buffer fused K2 -> K3 call (estimate_transformation pass 1 for a batch of pairs).
-    want_lists=False skips the D2H of match lists / inlier masks (only what EstTransform.srv returns)."""
+    want_lists=False skips the D2H of match lists / inlier masks (only what EstTransform.srv returns).
+    async_=True (sepb_verify_pairs_async): returns once enqueued; `pairs` and `out` must be pinned and the results
+    are valid after ctx.sync()."""
     pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
     P, F = pairs.shape[0], frames_from.max_feat
-    res = dict(status=np.zeros(P, np.int32), n_matches=np.zeros(P, np.int32), n_inliers=np.zeros(P, np.int32),
-               pose=np.zeros((P, 6), np.float64), transform=np.zeros((P, 12), np.float32),
-               best_hyp=np.zeros(P, np.int32), iters_run=np.zeros(P, np.int32))
-    if want_lists:
-        res.update(match_from=np.zeros((P, F), np.uint16), match_to=np.zeros((P, F), np.uint16),
-                   inlier_mask=np.zeros((P, (F + 31) // 32), np.uint32))
+    res = out if out is not None else verify_buffers(P, F, want_lists)
     out = VerifyOut(**{k: v.ctypes.data for k, v in res.items()})
     cs, ch = None, 0
     if custom_samples is not None:
@@ -265,8 +285,9 @@ def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pn
         assert cs.ndim == 3 and cs.shape[0] == P and cs.shape[2] == 5
         ch = cs.shape[1]
     mp = MatchParams(nndr, 1 if strict else 0)
-    ctx.check(lib().sepb_verify_pairs(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(mp), C.byref(pnp),
-                                      _ptr(cs), ch, C.byref(out)))
+    fn = lib().sepb_verify_pairs_async if async_ else lib().sepb_verify_pairs
+    ctx.check(fn(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(mp), C.byref(pnp), _ptr(cs), ch,
+                 C.byref(out)))
     return res
 
 

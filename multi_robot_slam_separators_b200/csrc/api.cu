@@ -33,7 +33,9 @@ int sepb_ctx_create(int device, sepb_ctx** out) {
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
   e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
+    if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return (int)e;
   }
@@ -45,7 +47,10 @@ void sepb_ctx_destroy(sepb_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  cudaStreamSynchronize(ctx->copy_stream);
+  cudaStreamDestroy(ctx->copy_stream);
   if (ctx->scratch) cudaFree(ctx->scratch);
+  if (ctx->io) cudaFree(ctx->io);
   if (ctx->table) cudaFree(ctx->table);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -99,8 +104,14 @@ int sepb_frames_create(sepb_ctx* ctx, int capacity, int max_feat, sepb_frames** 
     sepb_frames_destroy(f);
     return sepb_fail(ctx, (int)e, "cudaMalloc(frames)", __FILE__, __LINE__);
   }
+  if ((e = cudaEventCreateWithFlags(&f->ev_uploaded, cudaEventDisableTiming)) != cudaSuccess ||
+      (e = cudaEventCreateWithFlags(&f->ev_last_use, cudaEventDisableTiming)) != cudaSuccess) {
+    sepb_frames_destroy(f);
+    return sepb_fail(ctx, (int)e, "cudaEventCreate(frames)", __FILE__, __LINE__);
+  }
   cudaMemsetAsync(f->count, 0, (size_t)capacity * 4, ctx->stream);
   cudaMemsetAsync(f->octave, 0, nf * 4, ctx->stream);
+  cudaStreamSynchronize(ctx->stream);   // uploads run on the copy stream: the store must be initialised before the first one
   *out = f;
   return SEPB_OK;
 }
@@ -110,7 +121,10 @@ void sepb_frames_destroy(sepb_frames* f) {
   if (f->ctx) {
     cudaSetDevice(f->ctx->device);
     cudaStreamSynchronize(f->ctx->stream);
+    cudaStreamSynchronize(f->ctx->copy_stream);
   }
+  if (f->ev_uploaded) cudaEventDestroy(f->ev_uploaded);
+  if (f->ev_last_use) cudaEventDestroy(f->ev_last_use);
   cudaFree(f->desc);
   cudaFree(f->kp2d);
   cudaFree(f->kp3d);
@@ -121,8 +135,8 @@ void sepb_frames_destroy(sepb_frames* f) {
 
 int sepb_frames_size(const sepb_frames* f) { return f ? f->size : 0; }
 
-int sepb_frames_upload(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc, const float* kp2d,
-                       const float* kp3d, const int32_t* octave, const int32_t* count) {
+static int frames_upload_impl(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc, const float* kp2d,
+                              const float* kp3d, const int32_t* octave, const int32_t* count, bool async) {
   if (!ctx || !f) return SEPB_E_INVALID;
   SEPB_REQUIRE(ctx, n >= 0 && first >= 0 && first + n <= f->capacity, SEPB_E_SHAPE);
   if (n == 0) return SEPB_OK;
@@ -130,15 +144,36 @@ int sepb_frames_upload(sepb_ctx* ctx, sepb_frames* f, int first, int n, const ui
   for (int i = 0; i < n; ++i) SEPB_REQUIRE(ctx, count[i] >= 0 && count[i] <= f->max_feat, SEPB_E_SHAPE);
   std::lock_guard<std::mutex> lk(ctx->mu);
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  // the copy stream must not overwrite slots a kernel enqueued earlier is still reading
+  cudaStream_t cs = ctx->copy_stream;
+  if (f->has_use) SEPB_CUDA(ctx, cudaStreamWaitEvent(cs, f->ev_last_use, 0));
   const size_t off = (size_t)first * f->max_feat, nf = (size_t)n * f->max_feat;
-  SEPB_CUDA(ctx, cudaMemcpyAsync(f->desc + off * 32, desc, nf * 32, cudaMemcpyHostToDevice, ctx->stream));
-  SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp2d + off * 2, kp2d, nf * 8, cudaMemcpyHostToDevice, ctx->stream));
-  SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp3d + off * 3, kp3d, nf * 12, cudaMemcpyHostToDevice, ctx->stream));
-  if (octave)
-    SEPB_CUDA(ctx, cudaMemcpyAsync(f->octave + off, octave, nf * 4, cudaMemcpyHostToDevice, ctx->stream));
-  SEPB_CUDA(ctx, cudaMemcpyAsync(f->count + first, count, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
-  SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  SEPB_CUDA(ctx, cudaMemcpyAsync(f->desc + off * 32, desc, nf * 32, cudaMemcpyHostToDevice, cs));
+  SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp2d + off * 2, kp2d, nf * 8, cudaMemcpyHostToDevice, cs));
+  SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp3d + off * 3, kp3d, nf * 12, cudaMemcpyHostToDevice, cs));
+  if (octave) SEPB_CUDA(ctx, cudaMemcpyAsync(f->octave + off, octave, nf * 4, cudaMemcpyHostToDevice, cs));
+  SEPB_CUDA(ctx, cudaMemcpyAsync(f->count + first, count, (size_t)n * 4, cudaMemcpyHostToDevice, cs));
+  SEPB_CUDA(ctx, cudaEventRecord(f->ev_uploaded, cs));
+  f->has_upload = true;
+  if (!async) SEPB_CUDA(ctx, cudaStreamSynchronize(cs));
   if (first + n > f->size) f->size = first + n;
+  return SEPB_OK;
+}
+
+int sepb_frames_upload(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc, const float* kp2d,
+                       const float* kp3d, const int32_t* octave, const int32_t* count) {
+  return frames_upload_impl(ctx, f, first, n, desc, kp2d, kp3d, octave, count, false);
+}
+
+int sepb_frames_upload_async(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc, const float* kp2d,
+                             const float* kp3d, const int32_t* octave, const int32_t* count) {
+  return frames_upload_impl(ctx, f, first, n, desc, kp2d, kp3d, octave, count, true);
+}
+
+int sepb_frames_wait(sepb_ctx* ctx, sepb_frames* f) {
+  if (!ctx || !f) return SEPB_E_INVALID;
+  SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (f->has_upload) SEPB_CUDA(ctx, cudaEventSynchronize(f->ev_uploaded));
   return SEPB_OK;
 }
 
@@ -152,8 +187,11 @@ int sepb_match_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_fram
   if (n_pairs == 0) return SEPB_OK;
   SEPB_REQUIRE(ctx, d_pairs && d_n_matches, SEPB_E_INVALID);
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
-  return sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, prm->nndr, prm->nndr_strict,
+  sepb_frames_acquire(ctx, from, to);
+  const int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, prm->nndr, prm->nndr_strict,
                                    d_knn_idx, d_knn_dist, d_n_matches, d_match_from, d_match_to, d_n_unique_to);
+  sepb_frames_release(ctx, from, to);
+  return rc;
 }
 
 int sepb_match_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs, int n_pairs,
@@ -184,8 +222,10 @@ int sepb_match_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* 
   SEPB_CUDA(ctx, cudaMemcpyAsync(d_pairs, pairs, P * 8, cudaMemcpyHostToDevice, ctx->stream));
   if (d_ki) SEPB_CUDA(ctx, cudaMemsetAsync(d_ki, 0xFF, P * to->max_feat * 8, ctx->stream));
   if (d_kd) SEPB_CUDA(ctx, cudaMemsetAsync(d_kd, 0xFF, P * to->max_feat * 8, ctx->stream));
+  sepb_frames_acquire(ctx, from, to);
   int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, prm->nndr, prm->nndr_strict,
                                      d_ki, d_kd, d_nm, d_mf, d_mt, d_nu);
+  sepb_frames_release(ctx, from, to);
   if (rc) return rc;
   if (knn_idx) SEPB_CUDA(ctx, cudaMemcpyAsync(knn_idx, d_ki, P * to->max_feat * 8, cudaMemcpyDeviceToHost, ctx->stream));
   if (knn_dist) SEPB_CUDA(ctx, cudaMemcpyAsync(knn_dist, d_kd, P * to->max_feat * 8, cudaMemcpyDeviceToHost, ctx->stream));

@@ -156,12 +156,13 @@ int sepb_netvlad_topk(sepb_ctx* ctx, const sepb_db* db, const double* queries, i
   {
     std::lock_guard<std::mutex> lk(ctx->mu);
     SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
-    // the call owns its own buffers: ctx scratch is used by the launch underneath
+    // staging lives in the context's second grow-only buffer (the launch underneath uses ctx scratch); no
+    // cudaMalloc / cudaFree per call: those synchronise the whole device, including uploads in flight
     const size_t b_q = align_up((size_t)nq * db->dim * 8, 256), b_rm = align_up((size_t)nq, 256),
                  b_st = align_up((size_t)(nq + 1) * 4, 256), b_co = align_up((size_t)std::max(n_ignored, 1) * 4, 256),
                  b_oi = align_up((size_t)nq * k * 4, 256), b_od = align_up((size_t)nq * k * 8, 256);
-    uint8_t* buf = nullptr;
-    SEPB_CUDA(ctx, cudaMalloc(&buf, b_q + b_rm + b_st + b_co + b_oi + b_od));
+    uint8_t* buf = (uint8_t*)sepb_scratch_io(ctx, b_q + b_rm + b_st + b_co + b_oi + b_od);
+    if (!buf) return (int)cudaErrorMemoryAllocation;
     uint8_t* s = buf;
     double* d_q = (double*)s; s += b_q;
     uint8_t* d_rm = (uint8_t*)s; s += b_rm;
@@ -170,7 +171,7 @@ int sepb_netvlad_topk(sepb_ctx* ctx, const sepb_db* db, const double* queries, i
     d_idx = (int32_t*)s; s += b_oi;
     double* d_dist = (double*)s;
     int rc = SEPB_OK;
-    auto fail = [&](cudaError_t e) { cudaFree(buf); return sepb_fail(ctx, (int)e, "netvlad_topk copy", __FILE__, __LINE__); };
+    auto fail = [&](cudaError_t e) { return sepb_fail(ctx, (int)e, "netvlad_topk copy", __FILE__, __LINE__); };
     cudaError_t e;
     if ((e = cudaMemcpyAsync(d_q, queries, (size_t)nq * db->dim * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if (row_mask && (e = cudaMemcpyAsync(d_rm, row_mask, nq, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
@@ -185,7 +186,6 @@ int sepb_netvlad_topk(sepb_ctx* ctx, const sepb_db* db, const double* queries, i
       if ((e = cudaMemcpyAsync(out_dist, d_dist, (size_t)nq * k * 8, cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess) return fail(e);
     }
     e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(buf);
     if (rc) return rc;
     if (e != cudaSuccess) return sepb_fail(ctx, (int)e, "netvlad_topk sync", __FILE__, __LINE__);
   }

@@ -88,10 +88,13 @@ int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frame
     rc = ensure_table(ctx, from->max_feat, prm->iterations);
     if (rc) return rc;
   }
-  return sepb_launch_pnp_ransac(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from,
-                                d_match_to, d_n_unique_to, ctx->table, ctx->table_h, d_custom_samples, custom_h, d_guess,
-                                prm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words, d_best_hyp,
-                                d_iters_run);
+  sepb_frames_acquire(ctx, from, to);
+  rc = sepb_launch_pnp_ransac(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from,
+                              d_match_to, d_n_unique_to, ctx->table, ctx->table_h, d_custom_samples, custom_h, d_guess,
+                              prm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words, d_best_hyp,
+                              d_iters_run);
+  sepb_frames_release(ctx, from, to);
+  return rc;
 }
 
 int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
@@ -106,6 +109,7 @@ int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_fra
   // n_unique_to lives in a small grow-only scratch slice owned by the context
   int32_t* d_nu = (int32_t*)sepb_scratch(ctx, align_up((size_t)n_pairs * 4, 256));
   if (!d_nu) return (int)cudaErrorMemoryAllocation;
+  sepb_frames_acquire(ctx, from, to);
   int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, mprm->nndr, mprm->nndr_strict,
                                      nullptr, nullptr, o->n_matches, o->match_from, o->match_to, d_nu);
   if (rc) return rc;
@@ -114,9 +118,9 @@ int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_fra
                              o->inlier_mask, (from->max_feat + 31) / 32, o->best_hyp, o->iters_run);
 }
 
-int sepb_verify_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs, int n_pairs,
-                      const sepb_match_params* mprm, const sepb_pnp_params* pprm, const int32_t* custom_samples,
-                      int custom_h, sepb_verify_out* out) {
+static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                             int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                             const int32_t* custom_samples, int custom_h, sepb_verify_out* out, bool wait) {
   if (!ctx || !from || !to || !mprm || !pprm || !out) return SEPB_E_INVALID;
   SEPB_REQUIRE(ctx, n_pairs >= 0, SEPB_E_SHAPE);
   if (n_pairs == 0) return SEPB_OK;
@@ -170,8 +174,20 @@ int sepb_verify_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames*
   D2H(match_to, P * F * 2);
   D2H(inlier_mask, P * MW * 4);
 #undef D2H
-  SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (wait) SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SEPB_OK;
+}
+
+int sepb_verify_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs, int n_pairs,
+                      const sepb_match_params* mprm, const sepb_pnp_params* pprm, const int32_t* custom_samples,
+                      int custom_h, sepb_verify_out* out) {
+  return verify_pairs_impl(ctx, from, to, pairs, n_pairs, mprm, pprm, custom_samples, custom_h, out, true);
+}
+
+int sepb_verify_pairs_async(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                            int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                            const int32_t* custom_samples, int custom_h, sepb_verify_out* out) {
+  return verify_pairs_impl(ctx, from, to, pairs, n_pairs, mprm, pprm, custom_samples, custom_h, out, false);
 }
 
 }  // extern "C"

@@ -13,12 +13,16 @@
 struct sepb_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;   // H2D of sepb_frames_upload_async, concurrent with the kernels on `stream`
   std::string err;
   int64_t launches = 0;
   std::mutex mu;
   // grow-only device scratch (pairs, outputs of host-level calls)
   void* scratch = nullptr;
   size_t scratch_bytes = 0;
+  // second grow-only buffer: staging of the host-buffer entry points whose launches use `scratch` underneath
+  void* io = nullptr;
+  size_t io_bytes = 0;
   int sm_count = 148;
   // cv::RNG(-1) minimal-sample index table [count][table_h][5] (K3)
   uint16_t* table = nullptr;
@@ -57,6 +61,9 @@ struct sepb_frames {
   float* kp3d = nullptr;     // [capacity][max_feat][3]
   int32_t* octave = nullptr; // [capacity][max_feat]
   int32_t* count = nullptr;  // [capacity]
+  // asynchronous uploads: kernels wait for ev_uploaded, the next upload waits for ev_last_use
+  cudaEvent_t ev_uploaded = nullptr, ev_last_use = nullptr;
+  mutable bool has_upload = false, has_use = false;
 };
 
 // device view of a frame store passed by value to kernels
@@ -72,6 +79,21 @@ struct FramesView {
 
 static inline FramesView view_of(const sepb_frames* f) {
   return FramesView{f->desc, f->kp2d, f->kp3d, f->octave, f->count, f->max_feat, f->size};
+}
+
+// order the compute stream after pending asynchronous uploads of the frame stores a launch is about to read ...
+static inline void sepb_frames_acquire(sepb_ctx* ctx, const sepb_frames* a, const sepb_frames* b) {
+  if (a->has_upload) cudaStreamWaitEvent(ctx->stream, a->ev_uploaded, 0);
+  if (b != a && b->has_upload) cudaStreamWaitEvent(ctx->stream, b->ev_uploaded, 0);
+}
+// ... and remember the last kernel that read them, so that a later upload does not overwrite data still in use
+static inline void sepb_frames_release(sepb_ctx* ctx, const sepb_frames* a, const sepb_frames* b) {
+  cudaEventRecord(a->ev_last_use, ctx->stream);
+  a->has_use = true;
+  if (b != a) {
+    cudaEventRecord(b->ev_last_use, ctx->stream);
+    b->has_use = true;
+  }
 }
 
 static inline int sepb_fail(sepb_ctx* ctx, int code, const char* what, const char* file, int line) {
@@ -112,6 +134,24 @@ static inline void* sepb_scratch(sepb_ctx* ctx, size_t bytes) {
   }
   ctx->scratch_bytes = want;
   return ctx->scratch;
+}
+
+static inline void* sepb_scratch_io(sepb_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->io_bytes) return ctx->io;
+  if (ctx->io) {
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->io);
+    ctx->io = nullptr;
+    ctx->io_bytes = 0;
+  }
+  const size_t want = bytes + bytes / 4 + 4096;
+  cudaError_t e = cudaMalloc(&ctx->io, want);
+  if (e != cudaSuccess) {
+    sepb_fail(ctx, (int)e, "cudaMalloc(io)", __FILE__, __LINE__);
+    return nullptr;
+  }
+  ctx->io_bytes = want;
+  return ctx->io;
 }
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

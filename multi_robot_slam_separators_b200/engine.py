@@ -34,10 +34,13 @@ class SeparatorEngine:
 
     def __init__(self, cam: Camera, max_feat: int, dim: int, local_capacity: int, peer_capacity: int, device: int = 0,
                  iterations: int = 300, min_inliers: int = 5, reproj_error: float = 2.0, nndr: float = 0.8,
-                 db_base: int = 0):
+                 db_base: int = 0, ctx: capi.Context | None = None):
+        """ctx: share another engine's context (one stream, one copy stream): two engines then act as the two
+        buffers of a pipeline -- the next round's keyframes upload while the current round is verified."""
         self.device = device
         torch.cuda.set_device(device)
-        self.ctx = capi.Context(device)
+        self._owns_ctx = ctx is None
+        self.ctx = capi.Context(device) if ctx is None else ctx
         self.stream = torch.cuda.ExternalStream(self.ctx.stream, device=device)
         self.max_feat, self.dim = max_feat, dim
         self.local = capi.Frames(self.ctx, local_capacity, max_feat)
@@ -51,12 +54,12 @@ class SeparatorEngine:
         self._buf = {}
 
     # ---- data in (host buffers; H2D inside the C ABI) -------------------------------------
-    def add_local_keyframes(self, desc, kp2d, kp3d, count, octave=None):
-        self.local.upload(self.n_local, desc, kp2d, kp3d, count, octave)
+    def add_local_keyframes(self, desc, kp2d, kp3d, count, octave=None, async_=False):
+        self.local.upload(self.n_local, desc, kp2d, kp3d, count, octave, async_=async_)
         self.n_local += len(count)
 
-    def add_peer_keyframes(self, desc, kp2d, kp3d, count, octave=None):
-        self.peer.upload(self.n_peer, desc, kp2d, kp3d, count, octave)
+    def add_peer_keyframes(self, desc, kp2d, kp3d, count, octave=None, async_=False):
+        self.peer.upload(self.n_peer, desc, kp2d, kp3d, count, octave, async_=async_)
         self.n_peer += len(count)
 
     def receive_descriptors(self, netvlad_rows):
@@ -136,5 +139,5 @@ class SeparatorEngine:
         self.ctx.sync()
 
     def close(self):
-        for obj in (self.local, self.peer, self.db, self.ctx):
+        for obj in (self.local, self.peer, self.db) + ((self.ctx,) if self._owns_ctx else ()):
             obj.close()
