@@ -229,6 +229,38 @@ SEPB_API int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const
                                    int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
                                    const int32_t* d_custom_samples, int custom_h, const sepb_verify_out* d_out);
 
+/* ---- the full estimate_transformation service call, batched ----------------------------------------
+ * StereoCamGeometricTools::estimateTransformation (R/src/stereoCamGeometricTools.cpp:122-178) calls
+ * computeTransformationFromFeats TWICE: with the identity guess (:141-152 -> global matching, sepb_verify_pairs) and
+ * again with the first result as guess (:153-164).  When the first result is valid the second call matches inside a
+ * window around the projected guess (R/src/myRegistrationVis.cpp:477-825: projectPoints with (guess*local)^-1, To
+ * keypoints within Vis/CorGuessWinSize px, equal octaves, 2-NN Hamming with the STRICT ratio test d1 < nndr*d2,
+ * first-come ownership) and PnP-RANSAC is seeded with that guess; when it is null the second call repeats the first.
+ * `out` then holds the SECOND call's result (what the service returns: success = !result2.isNull()); match lists and
+ * inlier masks are those of the second call where it ran.  status_pass1 (optional, [P]) receives the first call's.
+ * The reference's radius search is FLANN's approximate randomised kd-tree (:672-680, not reproducible); this is the
+ * exact search it approximates. */
+typedef struct sepb_guess_params {
+  int32_t image_width, image_height;  /* cameraModel.imageSize() (image_size_ is 0x0 in the node, :469-472) */
+  float win_size;                     /* Vis/CorGuessWinSize, pixels (20) */
+} sepb_guess_params;
+SEPB_API void sepb_guess_params_init(sepb_guess_params* g, int image_width, int image_height);
+/* K2G alone (host buffers): the second call's correspondence lists for explicit first-call transforms
+ * [P][12] f32 (3x4 row-major, From-base <- To-base); guess_out [P][6] f64 (optional) = rvec, tvec of
+ * (guess * localTransform)^-1, the seed handed to PnP. */
+SEPB_API int sepb_guess_match_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                                    int n_pairs, const float* transforms, const sepb_pnp_params* pprm,
+                                    const sepb_guess_params* gprm, float nndr, int32_t* n_matches, uint16_t* match_from,
+                                    uint16_t* match_to, double* guess_out);
+SEPB_API int sepb_estimate_transformations(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to,
+                                           const int32_t* pairs, int n_pairs, const sepb_match_params* mprm,
+                                           const sepb_pnp_params* pprm, const sepb_guess_params* gprm,
+                                           sepb_verify_out* out, int32_t* status_pass1);
+SEPB_API int sepb_estimate_transformations_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to,
+                                               const int32_t* d_pairs, int n_pairs, const sepb_match_params* mprm,
+                                               const sepb_pnp_params* pprm, const sepb_guess_params* gprm,
+                                               const sepb_verify_out* d_out, int32_t* d_status_pass1);
+
 /* ---- measurement support (roofline denominators not in MEASURED_PEAKS.json) ----------------
  * kind 0: POPC instructions/s (K2's bounding pipe), kind 1: FP64 FMA/s (K3's).  Best of reps. */
 SEPB_API int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s);

@@ -18,7 +18,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
           "-I", os.path.join(ROOT, "include")]
 # per-file extra flags.  pnp_ransac.cu replays OpenCV's double-precision operation order bit for
 # bit (x86-64 baseline build of cv2 has no FMA contraction), hence -fmad=false there.
-EXTRA = {"pnp_ransac.cu": ["-fmad=false"] + (["-DSEPB_K3_PROFILE"] if os.environ.get("SEPB_K3_PROFILE") else [])}
+EXTRA = {"guess_match.cu": ["-fmad=false"], "pnp_ransac.cu": ["-fmad=false"] + (["-DSEPB_K3_PROFILE"] if os.environ.get("SEPB_K3_PROFILE") else [])}
 
 
 def nvcc() -> str:

@@ -42,6 +42,10 @@ class PnpParams(C.Structure):
                 ("local_R", C.c_double * 9), ("local_t", C.c_double * 3)]
 
 
+class GuessParams(C.Structure):
+    _fields_ = [("image_width", C.c_int32), ("image_height", C.c_int32), ("win_size", C.c_float)]
+
+
 class VerifyOut(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("status", "n_matches", "n_inliers", "pose", "transform", "match_from",
                                           "match_to", "inlier_mask", "best_hyp", "iters_run")]
@@ -124,6 +128,16 @@ def _declare(L):
         f = getattr(L, name)
         f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), C.POINTER(PnpParams), vp, i32,
                       C.POINTER(VerifyOut)]
+        f.restype = i32
+    L.sepb_guess_params_init.argtypes = [C.POINTER(GuessParams), i32, i32]
+    L.sepb_guess_params_init.restype = None
+    L.sepb_guess_match_pairs.argtypes = [vp, vp, vp, vp, i32, vp, C.POINTER(PnpParams), C.POINTER(GuessParams), C.c_float,
+                                         vp, vp, vp, vp]
+    L.sepb_guess_match_pairs.restype = i32
+    for name in ("sepb_estimate_transformations", "sepb_estimate_transformations_dev"):
+        f = getattr(L, name)
+        f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), C.POINTER(PnpParams), C.POINTER(GuessParams),
+                      C.POINTER(VerifyOut), vp]
         f.restype = i32
     for name in ("sepb_match_pairs", "sepb_match_pairs_dev"):
         f = getattr(L, name)
@@ -288,6 +302,41 @@ def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pn
     fn = lib().sepb_verify_pairs_async if async_ else lib().sepb_verify_pairs
     ctx.check(fn(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(mp), C.byref(pnp), _ptr(cs), ch,
                  C.byref(out)))
+    return res
+
+
+def guess_params(width, height, win_size=20.0):
+    g = GuessParams()
+    lib().sepb_guess_params_init(C.byref(g), int(width), int(height))
+    g.win_size = float(win_size)
+    return g
+
+
+def guess_match_pairs(ctx, frames_from, frames_to, pairs, transforms, pnp: PnpParams, gprm: GuessParams, nndr=0.8):
+    """K2G on host buffers: pass-2 correspondence lists for explicit first-pass transforms [P,12] f32."""
+    pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+    P, F = pairs.shape[0], frames_from.max_feat
+    T = np.ascontiguousarray(transforms, dtype=np.float32).reshape(P, 12)
+    nm = np.zeros(P, np.int32)
+    mf, mt = np.zeros((P, F), np.uint16), np.zeros((P, F), np.uint16)
+    g = np.zeros((P, 6), np.float64)
+    ctx.check(lib().sepb_guess_match_pairs(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, _ptr(T), C.byref(pnp),
+                                           C.byref(gprm), float(nndr), _ptr(nm), _ptr(mf), _ptr(mt), _ptr(g)))
+    return dict(n_matches=nm, match_from=mf, match_to=mt, guess=g)
+
+
+def estimate_transformations(ctx, frames_from, frames_to, pairs, pnp: PnpParams, gprm: GuessParams, nndr=0.8,
+                             want_lists=True):
+    """The batched estimate_transformation service (both calls of stereoCamGeometricTools.cpp:141-164)."""
+    pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+    P, F = pairs.shape[0], frames_from.max_feat
+    res = verify_buffers(P, F, want_lists)
+    out = VerifyOut(**{k: v.ctypes.data for k, v in res.items()})
+    st1 = np.zeros(P, np.int32)
+    mp = MatchParams(nndr, 0)
+    ctx.check(lib().sepb_estimate_transformations(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(mp),
+                                                  C.byref(pnp), C.byref(gprm), C.byref(out), _ptr(st1)))
+    res["status_pass1"] = st1
     return res
 
 

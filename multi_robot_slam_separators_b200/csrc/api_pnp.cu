@@ -68,12 +68,13 @@ void sepb_pnp_set_guess(sepb_pnp_params* p, const double* G) {
   cvm::rodrigues_mat_to_vec(cvm::Heap{scratch}, Rinv, p->guess_rvec);
 }
 
-int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
-                        int n_pairs, const int32_t* d_n_matches, const uint16_t* d_match_from,
-                        const uint16_t* d_match_to, const int32_t* d_n_unique_to, const sepb_pnp_params* prm,
-                        const int32_t* d_custom_samples, int custom_h, const double* d_guess, int32_t* d_status,
-                        int32_t* d_n_inliers, double* d_pose, float* d_transform, uint32_t* d_inlier_mask,
-                        int mask_words, int32_t* d_best_hyp, int32_t* d_iters_run) {
+static int pnp_ransac_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                           int n_pairs, const int32_t* d_n_matches, const uint16_t* d_match_from,
+                           const uint16_t* d_match_to, const int32_t* d_n_unique_to, const sepb_pnp_params* prm,
+                           const int32_t* d_custom_samples, int custom_h, const double* d_guess,
+                           const int32_t* d_only_if_ok, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
+                           float* d_transform, uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp,
+                           int32_t* d_iters_run) {
   if (!ctx || !from || !to || !prm) return SEPB_E_INVALID;
   SEPB_REQUIRE(ctx, n_pairs >= 0, SEPB_E_SHAPE);
   if (n_pairs == 0) return SEPB_OK;
@@ -91,36 +92,80 @@ int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frame
   sepb_frames_acquire(ctx, from, to);
   rc = sepb_launch_pnp_ransac(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from,
                               d_match_to, d_n_unique_to, ctx->table, ctx->table_h, d_custom_samples, custom_h, d_guess,
-                              prm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words, d_best_hyp,
-                              d_iters_run);
+                              d_only_if_ok, prm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words,
+                              d_best_hyp, d_iters_run);
   sepb_frames_release(ctx, from, to);
   return rc;
 }
 
-int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
-                          int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
-                          const int32_t* d_custom_samples, int custom_h, const sepb_verify_out* o) {
+int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                        int n_pairs, const int32_t* d_n_matches, const uint16_t* d_match_from,
+                        const uint16_t* d_match_to, const int32_t* d_n_unique_to, const sepb_pnp_params* prm,
+                        const int32_t* d_custom_samples, int custom_h, const double* d_guess, int32_t* d_status,
+                        int32_t* d_n_inliers, double* d_pose, float* d_transform, uint32_t* d_inlier_mask,
+                        int mask_words, int32_t* d_best_hyp, int32_t* d_iters_run) {
+  return pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, d_n_matches, d_match_from, d_match_to, d_n_unique_to, prm,
+                         d_custom_samples, custom_h, d_guess, nullptr, d_status, d_n_inliers, d_pose, d_transform,
+                         d_inlier_mask, mask_words, d_best_hyp, d_iters_run);
+}
+
+// gprm == nullptr: pass 1 only (sepb_verify_pairs*); otherwise the two-pass driver of estimate_transformation
+static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                           int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                           const sepb_guess_params* gprm, const int32_t* d_custom_samples, int custom_h,
+                           const sepb_verify_out* o, int32_t* d_status_pass1) {
   if (!ctx || !from || !to || !mprm || !pprm || !o) return SEPB_E_INVALID;
   SEPB_REQUIRE(ctx, n_pairs >= 0, SEPB_E_SHAPE);
   if (n_pairs == 0) return SEPB_OK;
   SEPB_REQUIRE(ctx, o->status && o->n_matches && o->n_inliers && o->pose && o->transform && o->match_from &&
                         o->match_to, SEPB_E_INVALID);
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
-  // n_unique_to lives in a small grow-only scratch slice owned by the context
-  int32_t* d_nu = (int32_t*)sepb_scratch(ctx, align_up((size_t)n_pairs * 4, 256));
-  if (!d_nu) return (int)cudaErrorMemoryAllocation;
+  if (gprm) SEPB_REQUIRE(ctx, gprm->image_width > 1 && gprm->image_height > 1 && gprm->win_size > 0, SEPB_E_INVALID);
+  // n_unique_to (and the pass-2 guesses) live in the head of the context's grow-only scratch
+  const size_t b_nu = align_up((size_t)n_pairs * 4, 256), b_g = gprm ? align_up((size_t)n_pairs * 48, 256) : 0;
+  uint8_t* s0 = (uint8_t*)sepb_scratch(ctx, b_nu + b_g);
+  if (!s0) return (int)cudaErrorMemoryAllocation;
+  int32_t* d_nu = (int32_t*)s0;
+  double* d_guess = (double*)(s0 + b_nu);
+  const int mw = (from->max_feat + 31) / 32;
   sepb_frames_acquire(ctx, from, to);
   int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, mprm->nndr, mprm->nndr_strict,
                                      nullptr, nullptr, o->n_matches, o->match_from, o->match_to, d_nu);
   if (rc) return rc;
-  return sepb_pnp_ransac_dev(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm,
-                             d_custom_samples, custom_h, nullptr, o->status, o->n_inliers, o->pose, o->transform,
-                             o->inlier_mask, (from->max_feat + 31) / 32, o->best_hyp, o->iters_run);
+  rc = pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm,
+                       d_custom_samples, custom_h, nullptr, nullptr, o->status, o->n_inliers, o->pose, o->transform,
+                       o->inlier_mask, mw, o->best_hyp, o->iters_run);
+  if (rc || !gprm) return rc;
+  // ---- pass 2 (stereoCamGeometricTools.cpp:153-164): guess = first result; only where the first pass succeeded
+  if (d_status_pass1)
+    SEPB_CUDA(ctx, cudaMemcpyAsync(d_status_pass1, o->status, (size_t)n_pairs * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  rc = sepb_launch_guess_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, o->status, o->transform, pprm,
+                               gprm->image_width, gprm->image_height, gprm->win_size, mprm->nndr, o->n_matches,
+                               o->match_from, o->match_to, d_nu, d_guess);
+  if (rc) return rc;
+  return pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm, nullptr, 0,
+                         d_guess, o->status, o->status, o->n_inliers, o->pose, o->transform, o->inlier_mask, mw,
+                         o->best_hyp, o->iters_run);
+}
+
+int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                          int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                          const int32_t* d_custom_samples, int custom_h, const sepb_verify_out* o) {
+  return verify_dev_impl(ctx, from, to, d_pairs, n_pairs, mprm, pprm, nullptr, d_custom_samples, custom_h, o, nullptr);
+}
+
+int sepb_estimate_transformations_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to,
+                                      const int32_t* d_pairs, int n_pairs, const sepb_match_params* mprm,
+                                      const sepb_pnp_params* pprm, const sepb_guess_params* gprm,
+                                      const sepb_verify_out* d_out, int32_t* d_status_pass1) {
+  if (!gprm) return SEPB_E_INVALID;
+  return verify_dev_impl(ctx, from, to, d_pairs, n_pairs, mprm, pprm, gprm, nullptr, 0, d_out, d_status_pass1);
 }
 
 static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
                              int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
-                             const int32_t* custom_samples, int custom_h, sepb_verify_out* out, bool wait) {
+                             const int32_t* custom_samples, int custom_h, sepb_verify_out* out, bool wait,
+                             const sepb_guess_params* gprm = nullptr, int32_t* status_pass1 = nullptr) {
   if (!ctx || !from || !to || !mprm || !pprm || !out) return SEPB_E_INVALID;
   SEPB_REQUIRE(ctx, n_pairs >= 0, SEPB_E_SHAPE);
   if (n_pairs == 0) return SEPB_OK;
@@ -133,11 +178,12 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   std::lock_guard<std::mutex> lk(ctx->mu);
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
   const size_t P = (size_t)n_pairs, F = (size_t)from->max_feat, MW = (F + 31) / 32;
-  const size_t b_nu = align_up(P * 4, 256);  // first slice: n_unique_to (used by verify_pairs_dev)
+  // head of the scratch: n_unique_to and pass-2 guesses (used by verify_dev_impl)
+  const size_t b_nu = align_up(P * 4, 256) + (gprm ? align_up(P * 48, 256) : 0);
   const size_t b_pairs = align_up(P * 8, 256), b_i = align_up(P * 4, 256), b_pose = align_up(P * 48, 256),
                b_T = align_up(P * 48, 256), b_m = align_up(P * F * 2, 256), b_mask = align_up(P * MW * 4, 256),
                b_cs = custom_samples ? align_up(P * custom_h * 5 * 4, 256) : 0;
-  const size_t total = b_nu + b_pairs + 5 * b_i + b_pose + b_T + 2 * b_m + b_mask + b_cs;
+  const size_t total = b_nu + b_pairs + 6 * b_i + b_pose + b_T + 2 * b_m + b_mask + b_cs;
   uint8_t* s = (uint8_t*)sepb_scratch(ctx, total);
   if (!s) return (int)cudaErrorMemoryAllocation;
   s += b_nu;
@@ -148,6 +194,7 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   d.n_inliers = (int32_t*)s; s += b_i;
   d.best_hyp = (int32_t*)s; s += b_i;
   d.iters_run = (int32_t*)s; s += b_i;
+  int32_t* d_st1 = (int32_t*)s; s += b_i;
   d.pose = (double*)s; s += b_pose;
   d.transform = (float*)s; s += b_T;
   d.match_from = (uint16_t*)s; s += b_m;
@@ -159,8 +206,10 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
     SEPB_CUDA(ctx, cudaMemcpyAsync(d_cs, custom_samples, P * custom_h * 5 * 4, cudaMemcpyHostToDevice, ctx->stream));
   }
   SEPB_CUDA(ctx, cudaMemcpyAsync(d_pairs, pairs, P * 8, cudaMemcpyHostToDevice, ctx->stream));
-  rc = sepb_verify_pairs_dev(ctx, from, to, d_pairs, n_pairs, mprm, pprm, d_cs, custom_h, &d);
+  rc = verify_dev_impl(ctx, from, to, d_pairs, n_pairs, mprm, pprm, gprm, d_cs, custom_h, &d, gprm ? d_st1 : nullptr);
   if (rc) return rc;
+  if (gprm && status_pass1)
+    SEPB_CUDA(ctx, cudaMemcpyAsync(status_pass1, d_st1, P * 4, cudaMemcpyDeviceToHost, ctx->stream));
 #define D2H(field, bytes) \
   if (out->field) SEPB_CUDA(ctx, cudaMemcpyAsync(out->field, d.field, (bytes), cudaMemcpyDeviceToHost, ctx->stream))
   D2H(status, P * 4);
@@ -182,6 +231,62 @@ int sepb_verify_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames*
                       const sepb_match_params* mprm, const sepb_pnp_params* pprm, const int32_t* custom_samples,
                       int custom_h, sepb_verify_out* out) {
   return verify_pairs_impl(ctx, from, to, pairs, n_pairs, mprm, pprm, custom_samples, custom_h, out, true);
+}
+
+int sepb_estimate_transformations(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                                  int n_pairs, const sepb_match_params* mprm, const sepb_pnp_params* pprm,
+                                  const sepb_guess_params* gprm, sepb_verify_out* out, int32_t* status_pass1) {
+  if (!gprm) return SEPB_E_INVALID;
+  return verify_pairs_impl(ctx, from, to, pairs, n_pairs, mprm, pprm, nullptr, 0, out, true, gprm, status_pass1);
+}
+
+// K2G alone on host buffers: pass-2 correspondences for explicit first-pass transforms (parity tests feed the oracle's)
+int sepb_guess_match_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                           int n_pairs, const float* transforms, const sepb_pnp_params* pprm,
+                           const sepb_guess_params* gprm, float nndr, int32_t* n_matches, uint16_t* match_from,
+                           uint16_t* match_to, double* guess_out) {
+  if (!ctx || !from || !to || !pprm || !gprm) return SEPB_E_INVALID;
+  SEPB_REQUIRE(ctx, n_pairs >= 0, SEPB_E_SHAPE);
+  if (n_pairs == 0) return SEPB_OK;
+  SEPB_REQUIRE(ctx, pairs && transforms && n_matches && match_from && match_to, SEPB_E_INVALID);
+  SEPB_REQUIRE(ctx, gprm->image_width > 1 && gprm->image_height > 1 && gprm->win_size > 0, SEPB_E_INVALID);
+  for (int i = 0; i < n_pairs; ++i)
+    SEPB_REQUIRE(ctx, pairs[2 * i] >= 0 && pairs[2 * i] < from->size && pairs[2 * i + 1] >= 0 &&
+                          pairs[2 * i + 1] < to->size, SEPB_E_SHAPE);
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t P = (size_t)n_pairs, F = (size_t)from->max_feat;
+  const size_t b_pairs = align_up(P * 8, 256), b_T = align_up(P * 48, 256), b_i = align_up(P * 4, 256),
+               b_m = align_up(P * F * 2, 256), b_g = align_up(P * 48, 256);
+  uint8_t* s = (uint8_t*)sepb_scratch(ctx, b_pairs + b_T + 2 * b_i + 2 * b_m + b_g);
+  if (!s) return (int)cudaErrorMemoryAllocation;
+  int32_t* d_pairs = (int32_t*)s; s += b_pairs;
+  float* d_T = (float*)s; s += b_T;
+  int32_t* d_nm = (int32_t*)s; s += b_i;
+  int32_t* d_nu = (int32_t*)s; s += b_i;
+  uint16_t* d_mf = (uint16_t*)s; s += b_m;
+  uint16_t* d_mt = (uint16_t*)s; s += b_m;
+  double* d_g = (double*)s;
+  SEPB_CUDA(ctx, cudaMemcpyAsync(d_pairs, pairs, P * 8, cudaMemcpyHostToDevice, ctx->stream));
+  SEPB_CUDA(ctx, cudaMemcpyAsync(d_T, transforms, P * 48, cudaMemcpyHostToDevice, ctx->stream));
+  sepb_frames_acquire(ctx, from, to);
+  int rc = sepb_launch_guess_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, nullptr, d_T, pprm, gprm->image_width,
+                                   gprm->image_height, gprm->win_size, nndr, d_nm, d_mf, d_mt, d_nu, d_g);
+  sepb_frames_release(ctx, from, to);
+  if (rc) return rc;
+  SEPB_CUDA(ctx, cudaMemcpyAsync(n_matches, d_nm, P * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SEPB_CUDA(ctx, cudaMemcpyAsync(match_from, d_mf, P * F * 2, cudaMemcpyDeviceToHost, ctx->stream));
+  SEPB_CUDA(ctx, cudaMemcpyAsync(match_to, d_mt, P * F * 2, cudaMemcpyDeviceToHost, ctx->stream));
+  if (guess_out) SEPB_CUDA(ctx, cudaMemcpyAsync(guess_out, d_g, P * 48, cudaMemcpyDeviceToHost, ctx->stream));
+  SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SEPB_OK;
+}
+
+void sepb_guess_params_init(sepb_guess_params* g, int image_width, int image_height) {
+  if (!g) return;
+  g->image_width = image_width;
+  g->image_height = image_height;
+  g->win_size = 20.f;   // Vis/CorGuessWinSize (RTAB-Map <= 0.20; 40 in later versions)
 }
 
 int sepb_verify_pairs_async(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,

@@ -28,7 +28,7 @@ struct sepb_ctx {
   uint16_t* table = nullptr;
   int table_m = -1, table_h = 0;
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
-  size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0;
+  size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_guess_smem = 0;
   int opt_match_kernel = SEPB_MATCH_AUTO;
   int opt_nn_mode = -1;  // reserved
   bool cfg_pnp = false, cfg_exact = false, cfg_gemm = false;
@@ -172,12 +172,16 @@ int sepb_launch_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32
                       int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
                       uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to);
 
+int sepb_launch_guess_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                            const int32_t* d_status1, const float* d_transform1, const sepb_pnp_params* p, int width,
+                            int height, float win, float nndr, int32_t* d_n_matches, uint16_t* d_match_from,
+                            uint16_t* d_match_to, int32_t* d_n_unique_to, double* d_guess);
 int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H);
 int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                            const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,
                            const int32_t* d_n_unique_to, const uint16_t* d_table, int table_h,
                            const int32_t* d_custom_samples, int custom_h, const double* d_guess,
-                           const sepb_pnp_params* p, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
+                           const int32_t* d_only_if_ok, const sepb_pnp_params* p, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
                            float* d_transform, uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp,
                            int32_t* d_iters_run);
 

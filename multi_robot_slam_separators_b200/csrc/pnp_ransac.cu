@@ -176,7 +176,8 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
                   const int32_t* __restrict__ n_matches, const uint16_t* __restrict__ match_from,
                   const uint16_t* __restrict__ match_to, const int32_t* __restrict__ n_unique_to,
                   const uint16_t* __restrict__ table, const int32_t* __restrict__ custom_samples, int custom_h,
-                  const double* __restrict__ guess /*[P][6] or null*/, PnpKernelParams prm,
+                  const double* __restrict__ guess /*[P][6] or null*/, const int32_t* __restrict__ only_if_ok,
+                  PnpKernelParams prm,
                   int32_t* __restrict__ status, int32_t* __restrict__ n_inliers, double* __restrict__ pose /*[P][6]*/,
                   float* __restrict__ transform /*[P][12]*/, uint32_t* __restrict__ inlier_mask, int mask_words,
                   int32_t* __restrict__ best_hyp, int32_t* __restrict__ iters_run) {
@@ -186,6 +187,8 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
   const int lane = threadIdx.x;
   const int pair = blockIdx.x;
   if (pair >= n_pairs) return;
+  // second pass (estimate_transformation's call with guess = first result): pairs whose first pass failed keep it
+  if (only_if_ok && only_if_ok[pair] != 1) return;
   const cvm::Heap heap{heap_base + lane};
   int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
   const bool valid_pair = fi >= 0 && fi < from.size && ti >= 0 && ti < to.size;
@@ -390,7 +393,7 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
                            const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,
                            const int32_t* d_n_unique_to, const uint16_t* d_table, int table_h,
                            const int32_t* d_custom_samples, int custom_h, const double* d_guess,
-                           const sepb_pnp_params* p, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
+                           const int32_t* d_only_if_ok, const sepb_pnp_params* p, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
                            float* d_transform, uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp,
                            int32_t* d_iters_run) {
   if (n_pairs == 0) return SEPB_OK;
@@ -415,7 +418,7 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   }
   pnp_ransac_kernel<<<n_pairs, kWarp, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, d_n_matches, d_match_from,
                                                           d_match_to, d_n_unique_to, d_table, d_custom_samples, custom_h,
-                                                          d_guess, k, d_status, d_n_inliers, d_pose, d_transform,
+                                                          d_guess, d_only_if_ok, k, d_status, d_n_inliers, d_pose, d_transform,
                                                           d_inlier_mask, mask_words, d_best_hyp, d_iters_run);
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());

@@ -178,7 +178,12 @@ def make_frames(place_ids, robot, seed, n_feat=1000, dim=128, n_landmarks=700, f
         kp2d[s:s + B, :, 1] = np.take_along_axis(vn, perm, axis=1)
         kp3d[s:s + B] = pb[bi, perm]
         lmk[s:s + B] = np.take_along_axis(lid, perm, axis=1)
-        octave[s:s + B] = r.integers(0, 8, (B, F), dtype=np.int32)
+        oc = r.integers(0, 8, (B, F), dtype=np.int32)                 # clutter: any pyramid level
+        lm_now = lmk[s:s + B]
+        # a landmark is detected at the same pyramid level in every view (pass 2 only pairs equal octaves,
+        # R/src/myRegistrationVis.cpp:723-734); derived from its id so the random stream is unchanged
+        oc_lm = ((lm_now.astype(np.int64) * 2654435761) >> 7) % 8
+        octave[s:s + B] = np.where(lm_now >= 0, oc_lm, oc).astype(np.int32)
     netvlad = make_netvlad(np.asarray(place_ids), dim, seed)
     return RobotFrames(desc=desc, kp2d=kp2d, kp3d=kp3d, octave=octave,
                        count=np.full(n, F, dtype=np.int32), netvlad=netvlad,
