@@ -271,6 +271,7 @@ def run_ours(args):
                                              C.c_void_p(mf.data_ptr()), C.c_void_p(mt.data_ptr()), C.c_void_p(nu.data_ptr())))
     ms_k2 = timed(k2, 3)
     ms_verify = timed(lambda: eng.verify_dev(pairs), 3)
+    ms_two_pass = timed(lambda: eng.verify_dev(pairs, two_pass=True), 3)   # + second call of estimate_transformation
     ms_k3 = max(ms_verify - ms_k2, 0.0)
 
     # ---- end to end through the host-buffer C ABI -------------------------------------------
@@ -382,6 +383,9 @@ def run_ours(args):
                 "kernels_ms": {"K1_netvlad_topk": ms_k1, "K2_hamming_match": ms_k2, "K3_pnp_ransac": ms_k3,
                                "step_share_K2": ms_k2 / (ms_total / args.steps)},
                 "fp64_fma_peak_per_s": dfma_peak,
+                "two_pass": {"ms_verify": ms_two_pass, "pairs_per_s": world * P / ((ms_k1 + ms_two_pass) * 1e-3),
+                             "note": "whole estimate_transformation service call: K2 + K3, then K2G + K3 seeded with the first result "
+                                     "(R/src/stereoCamGeometricTools.cpp:141-164); rank-0 timing x n_gpus"},
                 "nn_queries_per_s": args.frames / (ms_k1 * 1e-3), "nn_mode": args.nn, "match_kernel": match_kernel,
                 "verified_ok_per_step": n_ok, "pairs_with_ransac_per_step": n_ransac, "ransac_iters_mean": iters_mean,
                 "synth_seconds": t_gen}

@@ -34,7 +34,7 @@ class SeparatorEngine:
 
     def __init__(self, cam: Camera, max_feat: int, dim: int, local_capacity: int, peer_capacity: int, device: int = 0,
                  iterations: int = 300, min_inliers: int = 5, reproj_error: float = 2.0, nndr: float = 0.8,
-                 db_base: int = 0, ctx: capi.Context | None = None):
+                 db_base: int = 0, ctx: capi.Context | None = None, image_size=(1241, 376), guess_win_size: float = 20.0):
         """ctx: share another engine's context (one stream, one copy stream): two engines then act as the two
         buffers of a pipeline -- the next round's keyframes upload while the current round is verified."""
         self.device = device
@@ -49,6 +49,7 @@ class SeparatorEngine:
         self.pnp = capi.pnp_params(cam.fx, cam.fy, cam.cx, cam.cy, iterations=iterations, min_inliers=min_inliers,
                                    reproj_error=reproj_error)
         self.mp = capi.MatchParams(nndr, 0)
+        self.guess = capi.guess_params(image_size[0], image_size[1], guess_win_size)
         self.n_local = 0
         self.n_peer = 0
         self._buf = {}
@@ -98,8 +99,9 @@ class SeparatorEngine:
             pairs = torch.stack([idx.reshape(-1), rows], dim=1).contiguous()
         return pairs
 
-    def verify_dev(self, d_pairs: torch.Tensor):
-        """K2 -> K3 on resident pairs [P,2] i32 -> dict of device tensors (asynchronous)."""
+    def verify_dev(self, d_pairs: torch.Tensor, two_pass: bool = False):
+        """K2 -> K3 on resident pairs [P,2] i32 -> dict of device tensors (asynchronous).
+        two_pass: the whole estimate_transformation call (second pass with guess = first result, K2G -> K3)."""
         P, F = d_pairs.shape[0], self.max_feat
         o = dict(status=self._tensor("status", (P,), torch.int32), n_matches=self._tensor("n_matches", (P,), torch.int32),
                  n_inliers=self._tensor("n_inliers", (P,), torch.int32), pose=self._tensor("pose", (P, 6), torch.float64),
@@ -109,9 +111,16 @@ class SeparatorEngine:
                  inlier_mask=self._tensor("inlier_mask", (P, (F + 31) // 32), torch.int32),
                  best_hyp=self._tensor("best_hyp", (P,), torch.int32), iters_run=self._tensor("iters_run", (P,), torch.int32))
         out = capi.VerifyOut(**{k: v.data_ptr() for k, v in o.items()})
-        self.ctx.check(capi.lib().sepb_verify_pairs_dev(self.ctx._h, self.peer._h, self.local._h,
-                                                        C.c_void_p(d_pairs.data_ptr()), P, C.byref(self.mp),
-                                                        C.byref(self.pnp), None, 0, C.byref(out)))
+        if two_pass:
+            st1 = self._tensor("status_pass1", (P,), torch.int32)
+            self.ctx.check(capi.lib().sepb_estimate_transformations_dev(
+                self.ctx._h, self.peer._h, self.local._h, C.c_void_p(d_pairs.data_ptr()), P, C.byref(self.mp),
+                C.byref(self.pnp), C.byref(self.guess), C.byref(out), C.c_void_p(st1.data_ptr())))
+            o = dict(o, status_pass1=st1)
+        else:
+            self.ctx.check(capi.lib().sepb_verify_pairs_dev(self.ctx._h, self.peer._h, self.local._h,
+                                                            C.c_void_p(d_pairs.data_ptr()), P, C.byref(self.mp),
+                                                            C.byref(self.pnp), None, 0, C.byref(out)))
         return o
 
     def step_dev(self, d_queries: torch.Tensor, k: int, mode=capi.NN_EXACT):
@@ -130,9 +139,12 @@ class SeparatorEngine:
         i1, d1 = self.db.topk(local_descriptors, 1, mode, local_used, pairs_ignored)
         return capi.select_matches(i1, d1, netvlad_distance, max_matches_nb)
 
-    def estimate_transformations(self, matches):
-        """estimate_transformation pass 1 for [(idx_local, idx_other)]: From = peer frame, To = local frame."""
+    def estimate_transformations(self, matches, two_pass: bool = False):
+        """estimate_transformation for [(idx_local, idx_other)]: From = peer frame, To = local frame.  two_pass=False:
+        the first call only (global matching, stereoCamGeometricTools.cpp:141-152); True: both calls (:141-164)."""
         pairs = np.array([[o, l] for (l, o) in matches], dtype=np.int32).reshape(-1, 2)
+        if two_pass:
+            return capi.estimate_transformations(self.ctx, self.peer, self.local, pairs, self.pnp, self.guess, self.mp.nndr)
         return capi.verify_pairs(self.ctx, self.peer, self.local, pairs, self.pnp, self.mp.nndr, bool(self.mp.nndr_strict))
 
     def sync(self):
