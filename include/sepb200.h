@@ -213,6 +213,10 @@ typedef struct sepb_verify_out {
   uint32_t* inlier_mask; /* [P][(max_feat+31)/32] */
   int32_t* best_hyp;     /* [P] */
   int32_t* iters_run;    /* [P] */
+  double* covariance;    /* [P][36] row-major 6x6 of info.covariance (needs inlier_mask): I6 with the translation block
+                          * scaled by 2.1981 * lower-quartile squared 3-D residual and the rotation block by the same
+                          * of the ray angles (RTAB-Map estimateMotion3DTo2D), diagonal clamped to >= 1e-9
+                          * (R/src/myRegistration.cpp:279-295); I6 when there is no transform */
 } sepb_verify_out;
 
 SEPB_API int sepb_verify_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,

@@ -48,7 +48,7 @@ class GuessParams(C.Structure):
 
 class VerifyOut(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("status", "n_matches", "n_inliers", "pose", "transform", "match_from",
-                                          "match_to", "inlier_mask", "best_hyp", "iters_run")]
+                                          "match_to", "inlier_mask", "best_hyp", "iters_run", "covariance")]
 
 
 def pnp_params(fx, fy, cx, cy, iterations=300, min_inliers=5, reproj_error=2.0, confidence=0.99, guess=None):
@@ -279,7 +279,7 @@ def verify_buffers(P, F, want_lists=True, alloc=np.zeros):
                best_hyp=alloc(P, np.int32), iters_run=alloc(P, np.int32))
     if want_lists:
         res.update(match_from=alloc((P, F), np.uint16), match_to=alloc((P, F), np.uint16),
-                   inlier_mask=alloc((P, (F + 31) // 32), np.uint32))
+                   inlier_mask=alloc((P, (F + 31) // 32), np.uint32), covariance=alloc((P, 36), np.float64))
     return res
 
 

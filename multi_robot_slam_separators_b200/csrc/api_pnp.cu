@@ -135,7 +135,14 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   rc = pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm,
                        d_custom_samples, custom_h, nullptr, nullptr, o->status, o->n_inliers, o->pose, o->transform,
                        o->inlier_mask, mw, o->best_hyp, o->iters_run);
-  if (rc || !gprm) return rc;
+  auto covariance = [&]() -> int {
+    if (!o->covariance) return SEPB_OK;
+    SEPB_REQUIRE(ctx, o->inlier_mask != nullptr, SEPB_E_INVALID);
+    return sepb_launch_pose_cov(ctx, view_of(from), view_of(to), d_pairs, n_pairs, o->status, o->n_matches, o->match_from,
+                                o->match_to, o->inlier_mask, mw, o->transform, o->covariance);
+  };
+  if (rc) return rc;
+  if (!gprm) return covariance();
   // ---- pass 2 (stereoCamGeometricTools.cpp:153-164): guess = first result; only where the first pass succeeded
   if (d_status_pass1)
     SEPB_CUDA(ctx, cudaMemcpyAsync(d_status_pass1, o->status, (size_t)n_pairs * 4, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -143,9 +150,11 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
                                gprm->image_width, gprm->image_height, gprm->win_size, mprm->nndr, o->n_matches,
                                o->match_from, o->match_to, d_nu, d_guess);
   if (rc) return rc;
-  return pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm, nullptr, 0,
-                         d_guess, o->status, o->status, o->n_inliers, o->pose, o->transform, o->inlier_mask, mw,
-                         o->best_hyp, o->iters_run);
+  rc = pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm, nullptr, 0,
+                       d_guess, o->status, o->status, o->n_inliers, o->pose, o->transform, o->inlier_mask, mw, o->best_hyp,
+                       o->iters_run);
+  if (rc) return rc;
+  return covariance();
 }
 
 int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
@@ -183,7 +192,8 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   const size_t b_pairs = align_up(P * 8, 256), b_i = align_up(P * 4, 256), b_pose = align_up(P * 48, 256),
                b_T = align_up(P * 48, 256), b_m = align_up(P * F * 2, 256), b_mask = align_up(P * MW * 4, 256),
                b_cs = custom_samples ? align_up(P * custom_h * 5 * 4, 256) : 0;
-  const size_t total = b_nu + b_pairs + 6 * b_i + b_pose + b_T + 2 * b_m + b_mask + b_cs;
+  const size_t b_cov = out->covariance ? align_up(P * 288, 256) : 0;
+  const size_t total = b_nu + b_pairs + 6 * b_i + b_pose + b_T + 2 * b_m + b_mask + b_cs + b_cov;
   uint8_t* s = (uint8_t*)sepb_scratch(ctx, total);
   if (!s) return (int)cudaErrorMemoryAllocation;
   s += b_nu;
@@ -200,6 +210,7 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   d.match_from = (uint16_t*)s; s += b_m;
   d.match_to = (uint16_t*)s; s += b_m;
   d.inlier_mask = (uint32_t*)s; s += b_mask;
+  if (out->covariance) { d.covariance = (double*)s; s += b_cov; }
   int32_t* d_cs = nullptr;
   if (custom_samples) {
     d_cs = (int32_t*)s;
@@ -222,6 +233,7 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   D2H(match_from, P * F * 2);
   D2H(match_to, P * F * 2);
   D2H(inlier_mask, P * MW * 4);
+  D2H(covariance, P * 288);
 #undef D2H
   if (wait) SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SEPB_OK;

@@ -176,6 +176,10 @@ int sepb_launch_guess_match(sepb_ctx* ctx, FramesView from, FramesView to, const
                             const int32_t* d_status1, const float* d_transform1, const sepb_pnp_params* p, int width,
                             int height, float win, float nndr, int32_t* d_n_matches, uint16_t* d_match_from,
                             uint16_t* d_match_to, int32_t* d_n_unique_to, double* d_guess);
+int sepb_launch_pose_cov(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                         const int32_t* d_status, const int32_t* d_n_matches, const uint16_t* d_match_from,
+                         const uint16_t* d_match_to, const uint32_t* d_inlier_mask, int mask_words,
+                         const float* d_transform, double* d_cov);
 int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H);
 int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                            const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,

@@ -109,7 +109,8 @@ class SeparatorEngine:
                  match_from=self._tensor("match_from", (P, F), torch.int16),
                  match_to=self._tensor("match_to", (P, F), torch.int16),
                  inlier_mask=self._tensor("inlier_mask", (P, (F + 31) // 32), torch.int32),
-                 best_hyp=self._tensor("best_hyp", (P,), torch.int32), iters_run=self._tensor("iters_run", (P,), torch.int32))
+                 best_hyp=self._tensor("best_hyp", (P,), torch.int32), iters_run=self._tensor("iters_run", (P,), torch.int32),
+                 covariance=self._tensor("covariance", (P, 36), torch.float64))
         out = capi.VerifyOut(**{k: v.data_ptr() for k, v in o.items()})
         if two_pass:
             st1 = self._tensor("status_pass1", (P,), torch.int32)

@@ -256,3 +256,36 @@ def lm_refine(obj64, img64, K, rvec0, tvec0, max_iter=20, eps=1.1920928955078125
         state = "CALC_J"
     R, _ = _rodrigues_with_jac(param[:3])
     return param[:3].copy(), param[3:].copy(), R
+
+
+def pose_covariance(T12, from3d, to3d, inliers):
+    """Covariance as RTAB-Map's util3d::estimateMotion3DTo2D fills it (SURVEY.md A.3 item 5, restated from the
+    published source; reached from R/src/myRegistrationVis.cpp:1077-1090) and Registration clamps it
+    (R/src/myRegistration.cpp:279-295).  T12: f32 3x4 transform (From-base <- To-base); from3d / to3d: [M,3] f32 points
+    of the correspondences; inliers: indices into them.  All geometry in f32, like cv::Point3f / Eigen::Vector4f."""
+    T = np.asarray(T12, np.float32).reshape(3, 4)
+    cov = np.eye(6)
+    d2s, angs = [], []
+    f32 = np.float32
+    for i in inliers:
+        b = np.asarray(to3d[i], f32)
+        if not np.all(np.isfinite(b)):
+            continue
+        a = np.asarray(from3d[i], f32)
+        n = [f32(f32(f32(f32(T[r, 0] * b[0]) + f32(T[r, 1] * b[1])) + f32(T[r, 2] * b[2])) + T[r, 3]) for r in range(3)]
+        d = [f32(a[k] - n[k]) for k in range(3)]
+        d2s.append(f32(f32(f32(d[0] * d[0]) + f32(d[1] * d[1])) + f32(d[2] * d[2])))
+        v1 = [f32(a[k] - T[k, 3]) for k in range(3)]
+        v2 = [f32(n[k] - T[k, 3]) for k in range(3)]
+        n1 = np.sqrt(f32(f32(f32(v1[0] * v1[0]) + f32(v1[1] * v1[1])) + f32(v1[2] * v1[2])), dtype=f32)
+        n2 = np.sqrt(f32(f32(f32(v2[0] * v2[0]) + f32(v2[1] * v2[1])) + f32(v2[2] * v2[2])), dtype=f32)
+        rad = f32(f32(f32(f32(v1[0] / n1) * f32(v2[0] / n2)) + f32(f32(v1[1] / n1) * f32(v2[1] / n2))) + f32(f32(v1[2] / n1) * f32(v2[2] / n2)))
+        rad = min(max(rad, f32(-1)), f32(1))
+        angs.append(np.arccos(rad, dtype=f32))
+    if d2s:
+        vl = 2.1981 * float(sorted(d2s)[len(d2s) >> 2])
+        va = 2.1981 * float(sorted(angs)[len(angs) >> 2])
+        for i in range(3):
+            cov[i, i] = max(vl, 1e-9)
+            cov[3 + i, 3 + i] = max(va, 1e-9)
+    return cov

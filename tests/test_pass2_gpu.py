@@ -127,6 +127,7 @@ def test_two_pass_driver(world):
         assert (one["status"][p] == 1) == ok1
         if not ok1:                                     # second call repeats the first and fails again
             assert res["status"][p] != 1 and not res["transform"][p].any()
+            assert np.array_equal(res["covariance"][p].reshape(6, 6), np.eye(6))      # no transform: identity stands
             continue
         T1 = matching.transform_from_pnp(rv1, tv1, synth.R_LOCAL, np.zeros(3))
         pr, rvg, tvg = oracle_pass2(w, o, l, T1)
@@ -142,5 +143,13 @@ def test_two_pass_driver(world):
         assert (res["status"][p] == 1) == bool(ok and len(inl) >= 5)
         assert np.array_equal(capi.inlier_indices(res["inlier_mask"][p], m), inl)
         assert np.abs(res["pose"][p, :3] - rv).max() < 1e-4 and np.abs(res["pose"][p, 3:] - tv).max() < 1e-4
+        # covariance of the returned pose (f32 geometry: compared to 1e-4 relative), from the GPU's own transform
+        if res["status"][p] == 1:
+            fi = res["match_from"][p, :m].astype(int)
+            ti = res["match_to"][p, :m].astype(int)
+            want = pnp.pose_covariance(res["transform"][p], w["A"].kp3d[o][fi], w["B"].kp3d[l][ti], inl)
+            got_c = res["covariance"][p].reshape(6, 6)
+            assert np.allclose(got_c, want, rtol=1e-4, atol=1e-12), (np.diag(got_c), np.diag(want))
+            assert got_c[0, 0] != 1.0 and got_c[3, 3] != 1.0
         n2 += 1
     assert n2 >= 8
