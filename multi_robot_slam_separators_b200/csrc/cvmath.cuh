@@ -56,11 +56,37 @@ constexpr int kHeapStride = 32;   // == lanes of a warp that solve hypotheses at
 #else
 constexpr int kHeapStride = 1;
 #endif
+#if defined(__CUDA_ARCH__)
+// Device build: the scratch always lives in shared memory, so the view keeps a 32-bit shared-space address and goes
+// through ld/st.shared (LDS/STS with immediate offsets) instead of generic LD/ST + 64-bit address arithmetic.
+struct HeapRef {
+  uint32_t a;
+  __device__ __forceinline__ operator double() const {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+  }
+  __device__ __forceinline__ const HeapRef& operator=(double v) const {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v));   // ordered against the other volatile accesses; no other alias
+    return *this;
+  }
+  __device__ __forceinline__ const HeapRef& operator=(const HeapRef& o) const { return *this = (double)o; }
+  __device__ __forceinline__ const HeapRef& operator*=(double v) const { return *this = (double)*this * v; }
+};
+struct Heap {
+  uint32_t a;
+  __device__ __forceinline__ Heap(double* p) : a((uint32_t)__cvta_generic_to_shared(p)) {}
+  __device__ __forceinline__ Heap(uint32_t addr, int) : a(addr) {}
+  __device__ __forceinline__ HeapRef operator[](int i) const { return HeapRef{a + (uint32_t)(i * kHeapStride * 8)}; }
+  __device__ __forceinline__ Heap at(int off) const { return Heap(a + (uint32_t)(off * kHeapStride * 8), 0); }
+};
+#else
 struct Heap {
   double* p;
   CVM_HD double& operator[](int i) const { return p[i * kHeapStride]; }
   CVM_HD Heap at(int off) const { return Heap{p + off * kHeapStride}; }
 };
+#endif
 
 // cv::RNG (multiply-with-carry)
 struct Rng {
@@ -228,20 +254,32 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
 }
 
 // SVBkSb, one right-hand side: x[n] = V diag(1/w) U^T b, with U^T = rows of At (n x m), Vt n x n.
-CVM_HD inline void svd_backsubst(Heap At, Heap W, Heap Vt, int m, int n, const double* b, double* x) {
+// m, n are template parameters so that b[] / x[] keep static indices (registers, not local memory).
+template <int m, int n>
+CVM_HD inline void svd_backsubst(Heap At, Heap W, Heap Vt, const double* b_in, double* x_out) {
+  double b[m], x[n];   // private copies: the caller's arrays may alias and would be re-read after every store
+  CVM_UNROLL
+  for (int k = 0; k < m; ++k) b[k] = b_in[k];
   double threshold = 0;
+  CVM_UNROLL
   for (int i = 0; i < n; ++i) threshold += W[i];
   threshold *= kDblEps * 2;
+  CVM_UNROLL
   for (int k = 0; k < n; ++k) x[k] = 0;
+  CVM_UNROLL
   for (int i = 0; i < n; ++i) {
     double wi = W[i];
     if (fabs(wi) <= threshold) continue;
     wi = 1 / wi;
     double s = 0;
+    CVM_UNROLL
     for (int k = 0; k < m; ++k) s += At[i * m + k] * b[k];
     s *= wi;
+    CVM_UNROLL
     for (int k = 0; k < n; ++k) x[k] = x[k] + s * Vt[i * n + k];
   }
+  CVM_UNROLL
+  for (int k = 0; k < n; ++k) x_out[k] = x[k];
 }
 
 }  // namespace cvm

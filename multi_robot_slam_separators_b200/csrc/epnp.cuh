@@ -26,17 +26,19 @@ CVM_HD CVM_NOINLINE inline void solve_cols(Heap h, const int (&cols)[NC], const 
   for (int c = 0; c < NC; ++c)
     for (int r = 0; r < 6; ++r) At[c * 6 + r] = h[H_L + r * 10 + cols[c]];
   jacobi_svd<6, NC, true>(At, W, Vt);
-  svd_backsubst(At, W, Vt, 6, NC, rho, x);
+  svd_backsubst<6, NC>(At, W, Vt, rho, x);
 }
 
 // epnp::qr_solve for the 6x4 Gauss-Newton system (A row-major 6x4, b[6]) -> X[4]; false if singular
 CVM_HD inline bool qr_solve_6x4(double* A, double* b, double* X) {
   const int nr = 6, nc = 4;
   double A1[4], A2[4];
+  CVM_UNROLL
   for (int k = 0; k < nc; ++k) {
     const int kk = k * nc + k;
     int p = kk;
     double eta = fabs(A[p]);
+    CVM_UNROLL
     for (int i = k + 1; i < nr; ++i) {  // (sic) scans rows k..nr-2
       const double elt = fabs(A[p]);
       if (eta < elt) eta = elt;
@@ -46,6 +48,7 @@ CVM_HD inline bool qr_solve_6x4(double* A, double* b, double* X) {
     const double inv_eta = 1. / eta;
     double sum2 = 0;
     p = kk;
+    CVM_UNROLL
     for (int i = k; i < nr; ++i) {
       A[p] *= inv_eta;
       sum2 += A[p] * A[p];
@@ -56,40 +59,48 @@ CVM_HD inline bool qr_solve_6x4(double* A, double* b, double* X) {
     A[kk] += sigma;
     A1[k] = sigma * A[kk];
     A2[k] = -eta * sigma;
+    CVM_UNROLL
     for (int j = k + 1; j < nc; ++j) {
       double sum = 0;
       p = kk;
+      CVM_UNROLL
       for (int i = k; i < nr; ++i) {
         sum += A[p] * A[p + j - k];
         p += nc;
       }
       const double tau = sum / A1[k];
       p = kk;
+      CVM_UNROLL
       for (int i = k; i < nr; ++i) {
         A[p + j - k] -= tau * A[p];
         p += nc;
       }
     }
   }
+  CVM_UNROLL
   for (int j = 0; j < nc; ++j) {
     const int jj = j * nc + j;
     double tau = 0;
     int p = jj;
+    CVM_UNROLL
     for (int i = j; i < nr; ++i) {
       tau += A[p] * b[i];
       p += nc;
     }
     tau /= A1[j];
     p = jj;
+    CVM_UNROLL
     for (int i = j; i < nr; ++i) {
       b[i] -= tau * A[p];
       p += nc;
     }
   }
   X[nc - 1] = b[nc - 1] / A2[nc - 1];
+  CVM_UNROLL
   for (int i = nc - 2; i >= 0; --i) {
     double sum = 0;
     int p = i * nc + (i + 1);
+    CVM_UNROLL
     for (int j = i + 1; j < nc; ++j) {
       sum += A[p] * X[j];
       ++p;
@@ -101,10 +112,13 @@ CVM_HD inline bool qr_solve_6x4(double* A, double* b, double* X) {
 
 CVM_HD CVM_NOINLINE inline void gauss_newton(Heap h, const double* rho, double* betas) {
   double x_stale[4] = {0, 0, 0, 0};  // epnp::gauss_newton's local x[4] = {}
+  CVM_NOUNROLL
   for (int it = 0; it < 5; ++it) {
     double A[24], b[6];
+    CVM_UNROLL
     for (int i = 0; i < 6; ++i) {
       double r[10];
+      CVM_UNROLL
       for (int c = 0; c < 10; ++c) r[c] = h[H_L + i * 10 + c];
       A[i * 4 + 0] = 2 * r[0] * betas[0] + r[1] * betas[1] + r[3] * betas[2] + r[6] * betas[3];
       A[i * 4 + 1] = r[1] * betas[0] + 2 * r[2] * betas[1] + r[4] * betas[2] + r[7] * betas[3];
@@ -117,8 +131,10 @@ CVM_HD CVM_NOINLINE inline void gauss_newton(Heap h, const double* rho, double* 
     }
     double x[4];
     if (qr_solve_6x4(A, b, x)) {
+      CVM_UNROLL
       for (int i = 0; i < 4; ++i) x_stale[i] = x[i];
     }  // singular: qr_solve returns early and X keeps its previous content
+    CVM_UNROLL
     for (int i = 0; i < 4; ++i) betas[i] += x_stale[i];
   }
 }
@@ -240,7 +256,7 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
     for (int c = 0; c < 3; ++c) {
       const double e[3] = {c == 0 ? 1. : 0., c == 1 ? 1. : 0., c == 2 ? 1. : 0.};
       double x[3];
-      svd_backsubst(At, W, Vt, 3, 3, e, x);
+      svd_backsubst<3, 3>(At, W, Vt, e, x);
       ci[c] = x[0]; ci[3 + c] = x[1]; ci[6 + c] = x[2];
     }
     for (int i = 0; i < kN; ++i) {

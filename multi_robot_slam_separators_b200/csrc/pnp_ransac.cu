@@ -31,6 +31,7 @@ namespace {
 constexpr int kWarp = 32;
 constexpr int kSolveLanes = cvm::kHeapStride;   // hypotheses solved at once by a warp (one lane each)
 constexpr int kMaskWords = SEPB_MAX_FEATURES / 32;
+constexpr int kScoreIlp = 4;                    // correspondences per lane scored together
 
 struct PnpKernelParams {
   cvm::Intrinsics K;
@@ -75,15 +76,41 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+// The part of the scratch heap above what the refit's 6x6 solve touches (78 strided doubles) doubles as a staging
+// area for the pair's correspondences while no EPnP solve is running: scoring and the refit then read them with
+// conflict-free LDS instead of two dependent gathers through L2 (four resident pairs overflow the small L1).
+constexpr int kStageOffBytes = 80 * cvm::kHeapStride * 8;
+constexpr int kStageCap = (cvm::kEpnpHeap * cvm::kHeapStride * 8 - kStageOffBytes) / 20;   // correspondences
+
 struct Corr {  // correspondence accessor of one pair
   const float* kp3d;   // From frame 3-D points
   const float* kp2d;   // To frame pixels
   const uint16_t* mf;
   const uint16_t* mt;
-  __device__ __forceinline__ void load(int m, float* o3, float* i2) const {
+  const float* st;     // staged copy (SoA, stride kStageCap) or nullptr when the pair has too many correspondences
+  __device__ __forceinline__ void load_global(int m, float* o3, float* i2) const {
     const int f = mf[m], t = mt[m];
     o3[0] = kp3d[3 * f]; o3[1] = kp3d[3 * f + 1]; o3[2] = kp3d[3 * f + 2];
     i2[0] = kp2d[2 * t]; i2[1] = kp2d[2 * t + 1];
+  }
+  __device__ __forceinline__ void load(int m, float* o3, float* i2) const {
+    if (st) {
+      o3[0] = st[m]; o3[1] = st[kStageCap + m]; o3[2] = st[2 * kStageCap + m];
+      i2[0] = st[3 * kStageCap + m]; i2[1] = st[4 * kStageCap + m];
+    } else {
+      load_global(m, o3, i2);
+    }
+  }
+  // (re)fill the staging area; the whole warp calls it whenever the heap is not in use by a solve
+  __device__ __forceinline__ void stage(float* dst, int M) const {
+    if (!st) return;
+    for (int m = threadIdx.x & 31; m < M; m += 32) {
+      float o3[3], i2[2];
+      load_global(m, o3, i2);
+      dst[m] = o3[0]; dst[kStageCap + m] = o3[1]; dst[2 * kStageCap + m] = o3[2];
+      dst[3 * kStageCap + m] = i2[0]; dst[4 * kStageCap + m] = i2[1];
+    }
+    __syncwarp();
   }
 };
 
@@ -158,7 +185,7 @@ __device__ __noinline__ void lm_step(cvm::Heap h, const double* JtJ, const doubl
   for (int a = 0; a < 6; ++a) At[a * 6 + a] = At[a * 6 + a] * (1. + lambda);
   cvm::jacobi_svd<6, 6, true>(At, W, Vt);
   double x[6];
-  cvm::svd_backsubst(At, W, Vt, 6, 6, JtE, x);
+  cvm::svd_backsubst<6, 6>(At, W, Vt, JtE, x);
   for (int i = 0; i < 6; ++i) param[i] = prev[i] - x[i];
 }
 
@@ -196,8 +223,10 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
   const int M = valid_pair ? n_matches[pair] : 0;
   const int nf = valid_pair ? from.count[fi] : 0;
   const int nu = n_unique_to ? n_unique_to[pair] : M;
+  float* stage_buf = reinterpret_cast<float*>(smem_raw + kStageOffBytes);
   Corr cr{from.kp3d + (size_t)fi * from.max_feat * 3, to.kp2d + (size_t)ti * to.max_feat * 2,
-          match_from + (size_t)pair * from.max_feat, match_to + (size_t)pair * from.max_feat};
+          match_from + (size_t)pair * from.max_feat, match_to + (size_t)pair * from.max_feat,
+          M <= kStageCap ? stage_buf : nullptr};
   double g[6];
   for (int i = 0; i < 3; ++i) {
     g[i] = guess ? guess[6 * pair + i] : prm.rvec0[i];
@@ -242,7 +271,7 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
 
   if (M == 5) {  // count == modelPoints: one EPnP over all five, no refit, all inliers
     float o[15], im[10];
-    for (int i = 0; i < 5; ++i) cr.load(i, o + 3 * i, im + 2 * i);
+    for (int i = 0; i < 5; ++i) cr.load_global(i, o + 3 * i, im + 2 * i);
     double R[9], p6[6] = {0, 0, 0, 0, 0, 0};
     if (lane < kSolveLanes) {   // only these lanes own a slice of the scratch heap; lane 0 reports
       cvm::epnp5(heap, o, im, prm.K, R, p6 + 3);
@@ -255,6 +284,7 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
 
   int niters = prm.iterations > 1 ? prm.iterations : 1;
   int best_good = 0, best_h = -1, cur = 0, hk = 0;
+  cr.stage(stage_buf, M);
   for (int chunk = 0; chunk < niters; chunk += kSolveLanes) {
     // ---- solve: lane <-> hypothesis (the first kSolveLanes lanes; more resident warps hide the f64 latency
     //      better than wider warps, and shorter chunks waste fewer hypotheses past the adaptive stop)
@@ -268,6 +298,7 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
                                      : table[((size_t)M * prm.table_h + h) * 5 + i];
         cr.load(min(max(s, 0), M - 1), o + 3 * i, im + 2 * i);
       }
+      __syncwarp();   // every lane has read its samples from the staging area before a solve overwrites it
       double R0[9], rv[3];
       K3_T0(t_e);
       cvm::epnp5(heap, o, im, prm.K, R0, th);
@@ -278,6 +309,7 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
       K3_ACC(1, t_r);
     }
     __syncwarp();
+    cr.stage(stage_buf, M);   // the solve overwrote the staging area
     K3_T0(t_s);
     // ---- score: warp <-> hypothesis, in RANSAC order
     for (int k = 0; k < kSolveLanes; ++k) {
@@ -290,17 +322,25 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
       for (int i = 0; i < 3; ++i) t[i] = __shfl_sync(0xFFFFFFFFu, th[i], k);
       uint32_t* cand = s_mask + (cur ^ 1) * kMaskWords;
       int good = 0;
-      for (int base = 0; base < M; base += 32) {
-        const int m = base + lane;
-        bool inl = false;
-        if (m < M) {
+      // kScoreIlp independent correspondences per lane in flight: the projection is a long dependent f64 chain
+      // behind two dependent loads, and a warp has only itself to hide that latency
+      for (int base = 0; base < M; base += 32 * kScoreIlp) {
+        bool inl[kScoreIlp];
+#pragma unroll
+        for (int u = 0; u < kScoreIlp; ++u) {
+          const int m = base + 32 * u + lane;
           float o3[3], i2[2];
-          cr.load(m, o3, i2);
-          inl = cvm::reproj_err_f32(R, t, prm.K, o3, i2) <= prm.thr2;
+          cr.load(min(m, M - 1), o3, i2);
+          inl[u] = (cvm::reproj_err_f32(R, t, prm.K, o3, i2) <= prm.thr2) && m < M;
         }
-        const uint32_t b = __ballot_sync(0xFFFFFFFFu, inl);
-        if (lane == 0) cand[base >> 5] = b;
-        good += __popc(b);
+#pragma unroll
+        for (int u = 0; u < kScoreIlp; ++u) {
+          const uint32_t b = __ballot_sync(0xFFFFFFFFu, inl[u]);
+          if (base + 32 * u < M) {
+            if (lane == 0) cand[(base >> 5) + u] = b;
+            good += __popc(b);
+          }
+        }
       }
       if (good > max(best_good, 4)) {
         cur ^= 1;

@@ -25,6 +25,8 @@ print("profile build:", built, "pairs with RANSAC:", len(it), "iters mean/max:",
       "hist chunks:", np.bincount((it + 31) // 32))
 ch = max(v[4], 1)
 print("chunk-solves:", int(v[4]))
+nm = res["n_matches"][res["n_matches"] >= 5].cpu().numpy(); ni = res["n_inliers"][res["n_matches"] >= 5].cpu().numpy()
+print("matches per RANSAC pair: mean %.1f min %d max %d; inliers mean %.1f" % (nm.mean(), nm.min(), nm.max(), ni.mean()))
 for name, i in (("epnp5", 0), ("  of which jacobi 12x12", 5), ("rodrigues", 1), ("scoring (32 hyp)", 2)):
     print(f"{name:26s} {v[i] / ch / 1e3:10.1f} kcycles per chunk")
 print(f"{'refit (per pair)':26s} {v[3] / max(len(it), 1) / 1e3:10.1f} kcycles")
