@@ -58,6 +58,9 @@ SEPB_API int64_t sepb_ctx_launch_count(const sepb_ctx* ctx);
 #define SEPB_MATCH_AUTO (-1)
 #define SEPB_MATCH_POPC 0
 #define SEPB_MATCH_TENSOR 1
+/* batches of more than this many pairs run PnP-RANSAC as two launches (first 32 hypotheses of every pair, then the
+ * rest longest-first; same results, shorter tail).  Default 4 x SM count; 0 forces it, INT_MAX disables it. */
+#define SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS 2
 SEPB_API int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value);
 SEPB_API int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value);
 

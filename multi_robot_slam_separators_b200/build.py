@@ -18,7 +18,10 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
           "-I", os.path.join(ROOT, "include")]
 # per-file extra flags.  pnp_ransac.cu replays OpenCV's double-precision operation order bit for
 # bit (x86-64 baseline build of cv2 has no FMA contraction), hence -fmad=false there.
-EXTRA = {"guess_match.cu": ["-fmad=false"], "pnp_ransac.cu": ["-fmad=false"] + (["-DSEPB_K3_PROFILE"] if os.environ.get("SEPB_K3_PROFILE") else [])}
+# SEPB_K3_DEFS: developer A/B switches for the K3 translation unit (e.g. "-DSEPB_JACOBI_ILP=0 -DSEPB_SCORE_ILP=2")
+EXTRA = {"guess_match.cu": ["-fmad=false"],
+         "pnp_ransac.cu": ["-fmad=false"] + (["-DSEPB_K3_PROFILE"] if os.environ.get("SEPB_K3_PROFILE") else [])
+                          + os.environ.get("SEPB_K3_DEFS", "").split()}
 
 
 def nvcc() -> str:
@@ -37,7 +40,7 @@ def _stamp():
     for f in sorted(os.listdir(CSRC)) + ["../../include/sepb200.h", "../build.py"]:
         with open(os.path.join(CSRC, f), "rb") as fh:
             h.update(fh.read())
-    h.update(os.environ.get("SEPB_K3_PROFILE", "").encode())
+    h.update((os.environ.get("SEPB_K3_PROFILE", "") + "|" + os.environ.get("SEPB_K3_DEFS", "")).encode())
     return h.hexdigest()
 
 

@@ -155,6 +155,7 @@ def _ptr(a):
 
 
 OPT_MATCH_KERNEL = 1
+OPT_PNP_TWO_PHASE_MIN_PAIRS = 2
 
 
 class Context:
@@ -188,6 +189,10 @@ class Context:
     def set_match_kernel(self, which: str):
         """'auto' | 'popc' (INT-pipe kernel) | 'tensor' (tcgen05 int8 GEMM kernel); identical results."""
         self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_KERNEL, {"auto": -1, "popc": 0, "tensor": 1}[which]))
+
+    def set_pnp_two_phase_min_pairs(self, n: int):
+        """Batches above n pairs run K3 as two launches (chunk 0, then the rest longest-first); 0 forces it."""
+        self.check(lib().sepb_ctx_set_option(self._h, OPT_PNP_TWO_PHASE_MIN_PAIRS, int(n)))
 
     def close(self):
         if self._h:

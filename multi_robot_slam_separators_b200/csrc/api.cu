@@ -52,6 +52,7 @@ void sepb_ctx_destroy(sepb_ctx* ctx) {
   if (ctx->scratch) cudaFree(ctx->scratch);
   if (ctx->io) cudaFree(ctx->io);
   if (ctx->table) cudaFree(ctx->table);
+  if (ctx->k3_order) cudaFree(ctx->k3_order);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -73,6 +74,11 @@ int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value) {
     ctx->opt_match_kernel = value;
     return SEPB_OK;
   }
+  if (option == SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS) {
+    SEPB_REQUIRE(ctx, value >= 0, SEPB_E_INVALID);
+    ctx->opt_two_phase_min = value;
+    return SEPB_OK;
+  }
   return sepb_fail(ctx, SEPB_E_INVALID, "unknown option", __FILE__, __LINE__);
 }
 
@@ -80,6 +86,10 @@ int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value) {
   if (!ctx || !value) return SEPB_E_INVALID;
   if (option == SEPB_OPT_MATCH_KERNEL) {
     *value = ctx->opt_match_kernel;
+    return SEPB_OK;
+  }
+  if (option == SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS) {
+    *value = ctx->opt_two_phase_min < 0 ? 4 * ctx->sm_count : ctx->opt_two_phase_min;
     return SEPB_OK;
   }
   return SEPB_E_INVALID;

@@ -27,9 +27,13 @@ struct sepb_ctx {
   // cv::RNG(-1) minimal-sample index table [count][table_h][5] (K3)
   uint16_t* table = nullptr;
   int table_m = -1, table_h = 0;
+  // K3 launch order (pairs with the fewest correspondences = longest RANSAC runs first), grow-only
+  int32_t* k3_order = nullptr;
+  size_t k3_order_cap = 0;
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
   size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_guess_smem = 0;
   int opt_match_kernel = SEPB_MATCH_AUTO;
+  int opt_two_phase_min = -1;   // -1: 4 x sm_count
   int opt_nn_mode = -1;  // reserved
   bool cfg_pnp = false, cfg_exact = false, cfg_gemm = false;
 };

@@ -40,6 +40,12 @@
 #define K3_ACC(slot, v)
 #endif
 
+#ifndef SEPB_JACOBI_ILP
+// 1: 12 x 12 sweep with two row-disjoint rotations in flight (jacobi12_sweeps_ilp).  Measured on B200 (tools/k3_ab.sh):
+// 10 % fewer cycles per warp but no shorter kernel (26.85 vs 26.57 ms verify), so the plain cyclic loop stays the default.
+#define SEPB_JACOBI_ILP 0
+#endif
+
 namespace cvm {
 
 constexpr double kDblEps = 2.220446049250313e-16;
@@ -111,6 +117,74 @@ CVM_HD inline double cv_hypot(double a, double b) {
     return b * sqrt(1 + a * a);
   }
   return 0;
+}
+
+// tail of JacobiSVDImpl_: singular values, descending sort, normalisation (random completion of zero rows)
+template <int m, int n, bool want_v>
+CVM_HD inline void jacobi_finish(Heap At, Heap W, Heap Vt) {
+  const double eps = kDblEps * 10;
+  CVM_NOUNROLL
+  for (int i = 0; i < n; ++i) {
+    double sd = 0;
+    CVM_UNROLL
+    for (int k = 0; k < m; ++k) {
+      const double t = At[i * m + k];
+      sd += t * t;
+    }
+    W[i] = sqrt(sd);
+  }
+  CVM_NOUNROLL
+  for (int i = 0; i < n - 1; ++i) {
+    int j = i;
+    for (int k = i + 1; k < n; ++k)
+      if (W[j] < W[k]) j = k;
+    if (i != j) {
+      double t = W[i]; W[i] = W[j]; W[j] = t;
+      for (int k = 0; k < m; ++k) { t = At[i * m + k]; At[i * m + k] = At[j * m + k]; At[j * m + k] = t; }
+      if (want_v)
+        for (int k = 0; k < n; ++k) { t = Vt[i * n + k]; Vt[i * n + k] = Vt[j * n + k]; Vt[j * n + k] = t; }
+    }
+  }
+  Rng rng(0x12345678);
+  CVM_NOUNROLL
+  for (int i = 0; i < n; ++i) {
+    double sd = W[i];
+    CVM_NOUNROLL
+    for (int ii = 0; ii < 100 && sd <= kDblMin; ++ii) {
+      // zero singular value: random +-1/m vector, orthogonalised against the previous rows
+      const double val0 = 1. / m;
+      CVM_NOUNROLL
+      for (int k = 0; k < m; ++k) At[i * m + k] = (rng.next() & 256) != 0 ? val0 : -val0;
+      CVM_NOUNROLL
+      for (int it = 0; it < 2; ++it)
+        CVM_NOUNROLL
+        for (int j = 0; j < i; ++j) {
+          sd = 0;
+          CVM_NOUNROLL
+          for (int k = 0; k < m; ++k) sd += At[i * m + k] * At[j * m + k];
+          double asum = 0;
+          CVM_NOUNROLL
+          for (int k = 0; k < m; ++k) {
+            const double t = At[i * m + k] - sd * At[j * m + k];
+            At[i * m + k] = t;
+            asum += fabs(t);
+          }
+          asum = asum > eps * 100 ? 1 / asum : 0;
+          CVM_NOUNROLL
+          for (int k = 0; k < m; ++k) At[i * m + k] *= asum;
+        }
+      sd = 0;
+      CVM_NOUNROLL
+      for (int k = 0; k < m; ++k) {
+        const double t = At[i * m + k];
+        sd += t * t;
+      }
+      sd = sqrt(sd);
+    }
+    const double s = sd > kDblMin ? 1 / sd : 0.;
+    CVM_UNROLL
+    for (int k = 0; k < m; ++k) At[i * m + k] *= s;
+  }
 }
 
 // JacobiSVDImpl_<double>: At is n rows of length m (row r at At[r*m + k]); on return rows of At are the
@@ -189,7 +263,40 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
       }
     if (!changed) break;
   }
-  CVM_NOUNROLL
+  jacobi_finish<m, n, want_v>(At, W, Vt);
+}
+
+#if defined(__CUDACC__)
+// 12 x 12 sweep of the M^T M Jacobi with kJacobiIlp rotations in flight per thread.  Rotation (i, j) touches rows
+// i and j (and W[i], W[j]) only, so rotations on disjoint rows commute EXACTLY: any order that keeps, for every row, the
+// cyclic order of the rotations touching it gives bit-identical results.  The table is a list schedule of the 66
+// cyclic pairs into rounds of <= 2 row-disjoint pairs ({0, 0} = empty slot); the dependent chains of a round
+// (dot product, hypot / sqrt / divide, rotated norms) interleave, which is what a lone warp per scheduler needs.
+// The sweep loop is warp-uniform: a lane that has converged only sees skipped rotations (no stores) in extra sweeps.
+constexpr int kJacobiIlp = 2;
+constexpr int kJacobiRounds = 35;
+static __device__ const unsigned char kJacobi12Sched[kJacobiRounds][kJacobiIlp][2] = {
+    {{0, 1}, {0, 0}}, {{0, 2}, {0, 0}}, {{0, 3}, {1, 2}}, {{0, 4}, {1, 3}}, {{0, 5}, {1, 4}},
+    {{2, 3}, {0, 6}}, {{1, 5}, {2, 4}}, {{0, 7}, {1, 6}}, {{2, 5}, {3, 4}}, {{0, 8}, {1, 7}},
+    {{2, 6}, {3, 5}}, {{0, 9}, {1, 8}}, {{2, 7}, {3, 6}}, {{4, 5}, {0, 10}}, {{1, 9}, {2, 8}},
+    {{3, 7}, {4, 6}}, {{0, 11}, {1, 10}}, {{2, 9}, {3, 8}}, {{4, 7}, {5, 6}}, {{1, 11}, {2, 10}},
+    {{3, 9}, {4, 8}}, {{5, 7}, {2, 11}}, {{3, 10}, {4, 9}}, {{5, 8}, {6, 7}}, {{3, 11}, {4, 10}},
+    {{5, 9}, {6, 8}}, {{4, 11}, {5, 10}}, {{6, 9}, {7, 8}}, {{5, 11}, {6, 10}}, {{7, 9}, {6, 11}},
+    {{7, 10}, {8, 9}}, {{7, 11}, {8, 10}}, {{8, 11}, {9, 10}}, {{9, 11}, {0, 0}}, {{10, 11}, {0, 0}}};
+#endif
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ double lds_f64(uint32_t a) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f64(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v)); }
+
+__device__ CVM_NOINLINE inline void jacobi12_sweeps_ilp(Heap At, Heap W) {
+  constexpr int m = 12, n = 12, G = kJacobiIlp;
+  constexpr uint32_t kEl = kHeapStride * 8, kRow = m * kEl;
+  const double eps = kDblEps * 10;
+  const unsigned mask = __activemask();
   for (int i = 0; i < n; ++i) {
     double sd = 0;
     CVM_UNROLL
@@ -197,61 +304,101 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
       const double t = At[i * m + k];
       sd += t * t;
     }
-    W[i] = sqrt(sd);
+    W[i] = sd;
   }
   CVM_NOUNROLL
-  for (int i = 0; i < n - 1; ++i) {
-    int j = i;
-    for (int k = i + 1; k < n; ++k)
-      if (W[j] < W[k]) j = k;
-    if (i != j) {
-      double t = W[i]; W[i] = W[j]; W[j] = t;
-      for (int k = 0; k < m; ++k) { t = At[i * m + k]; At[i * m + k] = At[j * m + k]; At[j * m + k] = t; }
-      if (want_v)
-        for (int k = 0; k < n; ++k) { t = Vt[i * n + k]; Vt[i * n + k] = Vt[j * n + k]; Vt[j * n + k] = t; }
-    }
-  }
-  Rng rng(0x12345678);
-  CVM_NOUNROLL
-  for (int i = 0; i < n; ++i) {
-    double sd = W[i];
+  for (int iter = 0; iter < 30; ++iter) {
+    bool changed = false;
+#if defined(SEPB_K3_PROFILE)
+    if ((threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[6], 1ull);
+#endif
     CVM_NOUNROLL
-    for (int ii = 0; ii < 100 && sd <= kDblMin; ++ii) {
-      // zero singular value: random +-1/m vector, orthogonalised against the previous rows
-      const double val0 = 1. / m;
-      CVM_NOUNROLL
-      for (int k = 0; k < m; ++k) At[i * m + k] = (rng.next() & 256) != 0 ? val0 : -val0;
-      CVM_NOUNROLL
-      for (int it = 0; it < 2; ++it)
-        CVM_NOUNROLL
-        for (int j = 0; j < i; ++j) {
-          sd = 0;
-          CVM_NOUNROLL
-          for (int k = 0; k < m; ++k) sd += At[i * m + k] * At[j * m + k];
-          double asum = 0;
-          CVM_NOUNROLL
-          for (int k = 0; k < m; ++k) {
-            const double t = At[i * m + k] - sd * At[j * m + k];
-            At[i * m + k] = t;
-            asum += fabs(t);
-          }
-          asum = asum > eps * 100 ? 1 / asum : 0;
-          CVM_NOUNROLL
-          for (int k = 0; k < m; ++k) At[i * m + k] *= asum;
-        }
-      sd = 0;
-      CVM_NOUNROLL
-      for (int k = 0; k < m; ++k) {
-        const double t = At[i * m + k];
-        sd += t * t;
+    for (int r = 0; r < kJacobiRounds; ++r) {
+      uint32_t ai[G], aj[G], wi[G], wj[G];
+      bool rot[G];
+      double a[G], b[G], p[G];
+      CVM_UNROLL
+      for (int g = 0; g < G; ++g) {
+        const int i = kJacobi12Sched[r][g][0], j = kJacobi12Sched[r][g][1];
+        rot[g] = i != j;
+        ai[g] = At.a + i * kRow;
+        aj[g] = At.a + j * kRow;
+        wi[g] = W.a + i * kEl;
+        wj[g] = W.a + j * kEl;
+        a[g] = lds_f64(wi[g]);
+        b[g] = lds_f64(wj[g]);
+        p[g] = 0;
       }
-      sd = sqrt(sd);
+      // both rows of every slot stay in registers from the dot product to the rotation: no load has to wait behind a
+      // store to a row the compiler cannot tell apart
+      double x[G][m], y[G][m];
+      CVM_UNROLL
+      for (int k = 0; k < m; ++k) {
+        CVM_UNROLL
+        for (int g = 0; g < G; ++g) {
+          x[g][k] = lds_f64(ai[g] + k * kEl);
+          y[g][k] = lds_f64(aj[g] + k * kEl);
+        }
+      }
+      CVM_UNROLL
+      for (int k = 0; k < m; ++k) {
+        CVM_UNROLL
+        for (int g = 0; g < G; ++g) p[g] += x[g][k] * y[g][k];
+      }
+      bool any = false;
+      CVM_UNROLL
+      for (int g = 0; g < G; ++g) {
+        rot[g] = rot[g] && !(fabs(p[g]) <= eps * sqrt(a[g] * b[g]));
+        any |= rot[g];
+      }
+      if (!__any_sync(mask, any)) continue;
+      double c[G], s[G];
+      CVM_UNROLL
+      for (int g = 0; g < G; ++g) {
+        // same operations as the scalar branches of jacobi_svd / cv_hypot, selected instead of branched
+        const double pp = p[g] * 2, beta = a[g] - b[g];
+        const double ha = fabs(pp), hb = fabs(beta);
+        const bool agtb = ha > hb;
+        const double big = agtb ? ha : hb, small = agtb ? hb : ha;
+        const double q = small / big;
+        const double gamma = big > 0 ? big * sqrt(1 + q * q) : 0.0;
+        const bool neg = beta < 0;
+        const double num = neg ? (gamma - beta) * 0.5 : (gamma + beta);
+        const double den = neg ? gamma : gamma * 2;
+        const double r1 = sqrt(num / den);
+        const double r2 = pp / (gamma * r1 * 2);
+        s[g] = neg ? r1 : r2;
+        c[g] = neg ? r2 : r1;
+        a[g] = 0;
+        b[g] = 0;
+      }
+      CVM_UNROLL
+      for (int k = 0; k < m; ++k) {
+        CVM_UNROLL
+        for (int g = 0; g < G; ++g) {
+          const double t0 = c[g] * x[g][k] + s[g] * y[g][k];
+          const double t1 = -s[g] * x[g][k] + c[g] * y[g][k];
+          if (rot[g]) {
+            sts_f64(ai[g] + k * kEl, t0);
+            sts_f64(aj[g] + k * kEl, t1);
+          }
+          a[g] += t0 * t0;
+          b[g] += t1 * t1;
+        }
+      }
+      CVM_UNROLL
+      for (int g = 0; g < G; ++g)
+        if (rot[g]) {
+          sts_f64(wi[g], a[g]);
+          sts_f64(wj[g], b[g]);
+          changed = true;
+        }
     }
-    const double s = sd > kDblMin ? 1 / sd : 0.;
-    CVM_UNROLL
-    for (int k = 0; k < m; ++k) At[i * m + k] *= s;
+    if (!__any_sync(mask, changed)) break;
   }
+  jacobi_finish<12, 12, false>(At, W, W);
 }
+#endif
 
 // SVBkSb, one right-hand side: x[n] = V diag(1/w) U^T b, with U^T = rows of At (n x m), Vt n x n.
 // m, n are template parameters so that b[] / x[] keep static indices (registers, not local memory).

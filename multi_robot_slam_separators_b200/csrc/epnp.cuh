@@ -290,7 +290,11 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
         At[b * 12 + a] = s;
       }
     K3_T0(t_j);
+#if defined(__CUDA_ARCH__) && SEPB_JACOBI_ILP
+    jacobi12_sweeps_ilp(At, h.at(H_W));   // same arithmetic, three row-disjoint rotations in flight (cvmath.cuh)
+#else
     jacobi_svd<12, 12, false>(At, h.at(H_W), h.at(H_W));
+#endif
     K3_ACC(5, t_j);
   }
   // ---- L_6x10 and rho

@@ -31,7 +31,10 @@ namespace {
 constexpr int kWarp = 32;
 constexpr int kSolveLanes = cvm::kHeapStride;   // hypotheses solved at once by a warp (one lane each)
 constexpr int kMaskWords = SEPB_MAX_FEATURES / 32;
-constexpr int kScoreIlp = 4;                    // correspondences per lane scored together
+#ifndef SEPB_SCORE_ILP
+#define SEPB_SCORE_ILP 1   // measured: 1 -> 26.57 ms, 2 -> 26.98 ms, 4 -> 29.8 ms per verify of 50 k pairs (staged LDS are cheap)
+#endif
+constexpr int kScoreIlp = SEPB_SCORE_ILP;                    // correspondences per lane scored together
 
 struct PnpKernelParams {
   cvm::Intrinsics K;
@@ -67,6 +70,68 @@ __global__ void sample_table_kernel(uint16_t* table, int max_count, int H) {
       idx[i] = v;
       row[h * 5 + i] = (uint16_t)v;
     }
+  }
+}
+
+// Two-phase launch of K3.  A pair's cost is its number of 32-hypothesis chunks (1..10 at 300 iterations), unknown
+// until RANSAC runs, and the hardware hands CTAs out in blockIdx order: in one launch a 7-chunk pair that happens to
+// start last keeps an SM busy for 5 ms after the rest has drained (measured: 16 ms against 11.6 ms of work).  So
+// phase 0 runs chunk 0 of every pair (uniform cost; pairs that are done after it finish there), saves
+// {niters, best count, best hypothesis, mask} of the others, and phase 1 resumes them in DESCENDING order of the
+// iteration bound left after chunk 0 (longest first).  Counting sort in one CTA; order inside a bin is arbitrary
+// because every pair writes only its own outputs.
+constexpr int kOrderThreads = 1024;
+constexpr int kStateInts = 4;   // per-pair state header: niters (0 = nothing left to do), best_good, best_h, hk
+__global__ void __launch_bounds__(kOrderThreads)
+pnp_order_kernel(const int32_t* __restrict__ state, int state_stride, int n_pairs, int32_t* __restrict__ order) {
+  __shared__ int hist[SEPB_MAX_FEATURES + 2];   // bin max(0, 4096 - niters); last bin = pairs with nothing left
+  __shared__ int warp_tot[32];
+  constexpr int kBins = SEPB_MAX_FEATURES + 2;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < kBins; i += kOrderThreads) hist[i] = 0;
+  __syncthreads();
+  auto key_of = [&](int p) {
+    const int it = state[(size_t)p * state_stride];
+    return it > 0 ? max(0, SEPB_MAX_FEATURES - it) : kBins - 1;
+  };
+  for (int p = tid; p < n_pairs; p += kOrderThreads) atomicAdd(&hist[key_of(p)], 1);
+  __syncthreads();
+  if (tid == 0) order[n_pairs] = n_pairs - hist[kBins - 1];   // pairs that resume
+  // exclusive scan of the bins: each thread owns a contiguous run of bins
+  constexpr int kPer = (kBins + kOrderThreads - 1) / kOrderThreads;
+  int local[kPer], sum = 0;
+  for (int i = 0; i < kPer; ++i) {
+    const int b = tid * kPer + i;
+    local[i] = b < kBins ? hist[b] : 0;
+    sum += local[i];
+  }
+  int incl = sum;
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if ((tid & 31) >= o) incl += v;
+  }
+  if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
+  __syncthreads();
+  if (tid < 32) {
+    int w = warp_tot[tid];
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xFFFFFFFFu, w, o);
+      if (tid >= o) w += v;
+    }
+    warp_tot[tid] = w;
+  }
+  __syncthreads();
+  int base = incl - sum + ((tid >> 5) ? warp_tot[(tid >> 5) - 1] : 0);
+  __syncthreads();
+  for (int i = 0; i < kPer; ++i) {
+    const int b = tid * kPer + i;
+    if (b < kBins) hist[b] = base;
+    base += local[i];
+  }
+  __syncthreads();
+  for (int p = tid; p < n_pairs; p += kOrderThreads) {
+    const int k = key_of(p);
+    if (k != kBins - 1) order[atomicAdd(&hist[k], 1)] = p;
   }
 }
 
@@ -207,13 +272,17 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
                   PnpKernelParams prm,
                   int32_t* __restrict__ status, int32_t* __restrict__ n_inliers, double* __restrict__ pose /*[P][6]*/,
                   float* __restrict__ transform /*[P][12]*/, uint32_t* __restrict__ inlier_mask, int mask_words,
-                  int32_t* __restrict__ best_hyp, int32_t* __restrict__ iters_run) {
+                  int32_t* __restrict__ best_hyp, int32_t* __restrict__ iters_run, const int32_t* __restrict__ order,
+                  int phase /*-1: whole run, 0: chunk 0 (+ finish if done), 1: resume*/, int32_t* __restrict__ state,
+                  int state_stride) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   double* heap_base = reinterpret_cast<double*>(smem_raw);
   uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)cvm::kEpnpHeap * kSolveLanes * 8);  // 2 * kMaskWords
   const int lane = threadIdx.x;
-  const int pair = blockIdx.x;
-  if (pair >= n_pairs) return;
+  if ((int)blockIdx.x >= (phase == 1 ? order[n_pairs] : n_pairs)) return;
+  const int pair = phase == 1 ? order[blockIdx.x] : blockIdx.x;
+  int32_t* st = state ? state + (size_t)pair * state_stride : nullptr;
+  if (phase == 0 && lane == 0) st[0] = 0;   // nothing to resume unless the chunk loop says so
   // second pass (estimate_transformation's call with guess = first result): pairs whose first pass failed keep it
   if (only_if_ok && only_if_ok[pair] != 1) return;
   const cvm::Heap heap{heap_base + lane};
@@ -233,7 +302,7 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
     g[3 + i] = guess ? guess[6 * pair + 3 + i] : prm.tvec0[i];
   }
   uint32_t* out_mask = inlier_mask ? inlier_mask + (size_t)pair * mask_words : nullptr;
-  if (out_mask)
+  if (out_mask && phase != 1)
     for (int w = lane; w < mask_words; w += 32) out_mask[w] = 0;
 
   auto finish = [&](int st, int ninl, const double* p6, int bh, int it) {
@@ -283,9 +352,18 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
   }
 
   int niters = prm.iterations > 1 ? prm.iterations : 1;
-  int best_good = 0, best_h = -1, cur = 0, hk = 0;
+  int best_good = 0, best_h = -1, cur = 0, hk = 0, chunk0 = 0;
+  if (phase == 1) {   // resume after chunk 0
+    niters = st[0];
+    best_good = st[1];
+    best_h = st[2];
+    hk = st[3];
+    chunk0 = kSolveLanes;
+    for (int w = lane; w < (M + 31) / 32; w += 32) s_mask[w] = (uint32_t)st[kStateInts + w];
+    __syncwarp();
+  }
   cr.stage(stage_buf, M);
-  for (int chunk = 0; chunk < niters; chunk += kSolveLanes) {
+  for (int chunk = chunk0; chunk < niters; chunk += kSolveLanes) {
     // ---- solve: lane <-> hypothesis (the first kSolveLanes lanes; more resident warps hide the f64 latency
     //      better than wider warps, and shorter chunks waste fewer hypotheses past the adaptive stop)
     int h = chunk + lane;
@@ -354,6 +432,18 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
 #ifdef SEPB_K3_PROFILE
     if (lane == 0) atomicAdd(&g_k3_prof[4], 1ull);
 #endif
+    if (phase == 0 && chunk + kSolveLanes < niters) {   // more chunks to run: hand the pair over to phase 1
+      __syncwarp();
+      if (lane == 0) {
+        st[0] = niters;
+        st[1] = best_good;
+        st[2] = best_h;
+        st[3] = hk;
+      }
+      const uint32_t* bm = s_mask + cur * kMaskWords;
+      for (int w = lane; w < (M + 31) / 32; w += 32) st[kStateInts + w] = (int32_t)bm[w];
+      return;
+    }
   }
   __syncwarp();
   K3_T0(t_lm);
@@ -456,11 +546,40 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
     SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  pnp_ransac_kernel<<<n_pairs, kWarp, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, d_n_matches, d_match_from,
-                                                          d_match_to, d_n_unique_to, d_table, d_custom_samples, custom_h,
-                                                          d_guess, d_only_if_ok, k, d_status, d_n_inliers, d_pose, d_transform,
-                                                          d_inlier_mask, mask_words, d_best_hyp, d_iters_run);
+  auto launch = [&](int phase, const int32_t* d_order, int32_t* d_state, int stride) {
+    pnp_ransac_kernel<<<n_pairs, kWarp, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, d_n_matches, d_match_from,
+                                                            d_match_to, d_n_unique_to, d_table, d_custom_samples, custom_h,
+                                                            d_guess, d_only_if_ok, k, d_status, d_n_inliers, d_pose,
+                                                            d_transform, d_inlier_mask, mask_words, d_best_hyp, d_iters_run,
+                                                            d_order, phase, d_state, stride);
+    ctx->launches++;
+  };
+  // below a few waves of CTAs there is no tail to trim: one launch.  Otherwise chunk 0, sort, resume (pnp_order_kernel)
+  const int two_phase_min = ctx->opt_two_phase_min < 0 ? 4 * ctx->sm_count : ctx->opt_two_phase_min;
+  if (n_pairs <= two_phase_min || p->iterations <= kSolveLanes) {
+    launch(-1, nullptr, nullptr, 0);
+    SEPB_CUDA(ctx, cudaGetLastError());
+    return SEPB_OK;
+  }
+  const int stride = kStateInts + (from.max_feat + 31) / 32;
+  const size_t want = (size_t)n_pairs * (stride + 1) + 1;   // state + order + resume count
+  if (want > ctx->k3_order_cap) {
+    if (ctx->k3_order) {
+      cudaStreamSynchronize(ctx->stream);
+      cudaFree(ctx->k3_order);
+      ctx->k3_order = nullptr;
+      ctx->k3_order_cap = 0;
+    }
+    const size_t cap = want + want / 2;
+    SEPB_CUDA(ctx, cudaMalloc(&ctx->k3_order, cap * sizeof(int32_t)));
+    ctx->k3_order_cap = cap;
+  }
+  int32_t* d_state = ctx->k3_order;
+  int32_t* d_order = ctx->k3_order + (size_t)n_pairs * stride;
+  launch(0, nullptr, d_state, stride);
+  pnp_order_kernel<<<1, kOrderThreads, 0, ctx->stream>>>(d_state, stride, n_pairs, d_order);
   ctx->launches++;
+  launch(1, d_order, d_state, stride);
   SEPB_CUDA(ctx, cudaGetLastError());
   return SEPB_OK;
 }

@@ -103,3 +103,30 @@ def test_synthetic_pairs_vs_cv2(ctx):
             G = synth.relative_pose_gt(A, a, B, b)
             assert np.abs(T - G).max() < 0.05
     assert n_ok >= len(same) - 2
+
+
+def test_two_phase_launch_identical(ctx, golden):
+    """Large batches run K3 as chunk 0 + longest-first resume (pnp_order_kernel): every output must equal the
+    single-launch run, including pairs that finish in chunk 0, degenerate pairs and injected sample indices."""
+    A, B = synth.make_robots(2, 40, n_feat=1000, dim=128, seed=1003)
+    A.count[3] = 700
+    B.count[5] = 300
+    A.count[7] = 4
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    rng = np.random.default_rng(6)
+    same = [(a, b) for a in range(40) for b in range(40) if A.place[a] == B.place[b]]
+    pairs = same + [(int(rng.integers(40)), int(rng.integers(40))) for _ in range(30)] + [(7, 1), (3, 5)]
+    for iters in (300, 40, 1000):
+        prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY, iterations=iters)
+        ctx.set_pnp_two_phase_min_pairs(1 << 30)
+        one = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+        ctx.set_pnp_two_phase_min_pairs(0)
+        try:
+            two = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+        finally:
+            ctx.set_pnp_two_phase_min_pairs(4 * 148)
+        assert int((one["status"] == 1).sum()) >= len(same) - 2
+        assert int((one["iters_run"] > 32).sum()) > 0 or iters <= 32
+        for k in ("status", "n_matches", "n_inliers", "inlier_mask", "pose", "transform", "best_hyp", "iters_run", "covariance"):
+            if k in one:
+                assert np.array_equal(one[k], two[k], equal_nan=True), (iters, k)
