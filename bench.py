@@ -47,7 +47,7 @@ def clocks_sampler_start(gpu_index):
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     try:
         p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + q, "--format=csv,noheader,nounits",
-                              "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+                              "-lms", "50"], stdout=f, stderr=subprocess.DEVNULL)
     except Exception:
         return None, f.name
     return p, f.name
@@ -242,6 +242,7 @@ def run_ours(args):
     n_ok = int((res["status"] == 1).sum().item())
     n_ransac = int((res["n_matches"] >= 5).sum().item())
     iters_mean = float(res["iters_run"][res["n_matches"] >= 5].float().mean().item()) if n_ransac else 0.0
+    m_mean = float(res["n_matches"][res["n_matches"] >= 5].float().mean().item()) if n_ransac else 0.0
 
     # ---- per-kernel durations (CUDA events on the launching stream) ---------------------------
     def timed(fn, reps):
@@ -345,6 +346,16 @@ def run_ours(args):
         bf16_burst = float(peaks.get("bf16_tflops", 1590.0))
         bf16_sust = float(peaks.get("bf16_tflops_sustained", 1400.0))
         peak_src = "MEASURED_PEAKS.json" if peaks else "fallback"
+        # DRAM traffic per launch from the committed ncu --set full captures (only valid for the workload they were taken on)
+        traffic = {}
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+            w = tj["workload"]
+            if (w["keyframes_per_robot"], w["features_per_frame"], w["netvlad_dim"], w["top_k"]) == \
+                    (args.frames, args.feat, args.dim, args.topk):
+                traffic = {k: v["bytes_per_launch"] for k, v in tj.items() if isinstance(v, dict) and "bytes_per_launch" in v}
+        except Exception:
+            pass
         k2_bytes = P * ((args.feat + args.feat) * 32 + args.feat * 12)        # algorithmic bytes per launch
         k2_gbs = k2_bytes / (ms_k2 * 1e-3) / 1e9
         k2_popc = P * 8.0 * args.feat * args.feat / (ms_k2 * 1e-3)
@@ -352,7 +363,8 @@ def run_ours(args):
         rooflines = {}
         if match_kernel == "tensor":
             rooflines["K2"] = {"kernel": "hamming_mma_kernel (K2T, tcgen05 kind::i8)", "bound": "tensor", "achieved": k2_tops,
-                               "peak": 2 * bf16_burst, "unit": "TOP/s", "frac": k2_tops / (2 * bf16_burst), "traffic": None,
+                               "peak": 2 * bf16_burst, "unit": "TOP/s", "frac": k2_tops / (2 * bf16_burst), "traffic": traffic.get("K2"),
+                               "algorithmic_bytes": k2_bytes,
                                "peak_source": peak_src + ": 2 x measured bf16 burst (int8 dense issues at twice the bf16 rate; "
                                                          "kernel timed alone)",
                                "hbm_gbs": k2_gbs, "popc_equivalent_per_s": k2_popc}
@@ -364,12 +376,14 @@ def run_ours(args):
                                             "peak_source": "sepb_measure_peak microbenchmark, same run"}}
         k1_tflops = 2.0 * args.frames * args.frames * args.dim / (ms_k1 * 1e-3) / 1e12
         rooflines["K1"] = {"kernel": "netvlad %s top-%d" % (args.nn, args.topk), "bound": "tensor", "achieved": k1_tflops,
-                           "peak": bf16_burst, "unit": "TFLOP/s", "frac": k1_tflops / bf16_burst, "traffic": None,
+                           "peak": bf16_burst, "unit": "TFLOP/s", "frac": k1_tflops / bf16_burst, "traffic": traffic.get("K1"),
                            "peak_source": peak_src + " (bf16 burst)", "algorithmic_flop": "2*Q*N*D"}
-        k3_ops = n_ransac * iters_mean * (1.1e5 + 30.0 * 100)   # H_eff * (C_epnp + 30*M)
+        k3_ops = n_ransac * iters_mean * (1.1e5 + 30.0 * m_mean)   # H_eff * (C_epnp + 30*M)
         rooflines["K3"] = {"kernel": "pnp_ransac_kernel (K3)", "bound": "fp64 issue", "achieved": k3_ops / max(ms_k3, 1e-9) / 1e-3,
                            "peak": dfma_peak, "unit": "f64 op/s", "frac": k3_ops / max(ms_k3, 1e-9) / 1e-3 / dfma_peak,
-                           "peak_source": "sepb_measure_peak FP64 FMA microbenchmark, same run"}
+                           "peak_source": "sepb_measure_peak FP64 FMA microbenchmark, same run", "traffic": traffic.get("K3"),
+                           "launches_per_step": 2, "note": "latency-bound by construction: OpenCV's serial f64 operation order is "
+                           "replayed per hypothesis (bit-exact inlier sets); two launches (chunk 0, longest-first resume)"}
         dominant = max((("K1", ms_k1), ("K2", ms_k2), ("K3", ms_k3)), key=lambda kv: kv[1])[0]
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_total_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -387,7 +401,7 @@ def run_ours(args):
                              "note": "whole estimate_transformation service call: K2 + K3, then K2G + K3 seeded with the first result "
                                      "(R/src/stereoCamGeometricTools.cpp:141-164); rank-0 timing x n_gpus"},
                 "nn_queries_per_s": args.frames / (ms_k1 * 1e-3), "nn_mode": args.nn, "match_kernel": match_kernel,
-                "verified_ok_per_step": n_ok, "pairs_with_ransac_per_step": n_ransac, "ransac_iters_mean": iters_mean,
+                "verified_ok_per_step": n_ok, "pairs_with_ransac_per_step": n_ransac, "ransac_iters_mean": iters_mean, "matches_per_ransac_pair_mean": m_mean,
                 "synth_seconds": t_gen}
         if not args.no_cpu_baseline and world == 1:
             sample = make_cpu_sample(args, 2000, args.cpu_queries)
@@ -405,7 +419,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=10000)

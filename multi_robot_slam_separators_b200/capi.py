@@ -6,6 +6,7 @@ fallback: if the library is missing or no sm_100 device is present, calls raise.
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 import os
 
 import numpy as np
@@ -164,6 +165,8 @@ class Context:
         rc = lib().sepb_ctx_create(device, C.byref(self._h))
         if rc != 0:
             raise SepbError(f"sepb_ctx_create(device={device}) failed with code {rc} (CUDA device required)")
+        # stores / databases created on this context: they hold a raw pointer to it, so close() destroys them first
+        self._children = weakref.WeakSet()
 
     def check(self, rc: int):
         if rc != 0:
@@ -196,6 +199,8 @@ class Context:
 
     def close(self):
         if self._h:
+            for child in list(getattr(self, "_children", ())):
+                child.close()
             lib().sepb_ctx_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -213,6 +218,7 @@ class Frames:
         self.ctx, self.capacity, self.max_feat = ctx, capacity, max_feat
         self._h = C.c_void_p()
         ctx.check(lib().sepb_frames_create(ctx._h, capacity, max_feat, C.byref(self._h)))
+        ctx._children.add(self)
 
     def upload(self, first, desc, kp2d, kp3d, count, octave=None, async_=False):
         """async_=True: enqueue on the copy stream and return (arrays must stay alive, ideally pinned, until
@@ -365,6 +371,7 @@ class NetvladDB:
         self.ctx, self.dim, self.capacity = ctx, dim, capacity
         self._h = C.c_void_p()
         ctx.check(lib().sepb_db_create(ctx._h, dim, capacity, C.byref(self._h)))
+        ctx._children.add(self)
         if base:
             ctx.check(lib().sepb_db_set_base(self._h, base))
 

@@ -135,7 +135,7 @@ def make_frames(place_ids, robot, seed, n_feat=1000, dim=128, n_landmarks=700, f
         u = lm_jc[..., 0] / z * FX + CX
         v = lm_jc[..., 1] / z * FY + CY
         vis = (z > 1.0) & (u >= 0) & (u < WIDTH) & (v >= 0) & (v < HEIGHT)
-        n_true_max = int(true_frac * F)
+        n_true_max = min(int(true_frac * F), L)   # a place has L landmarks: larger frames get more clutter
         score = r.random((B, L))
         score[~vis] = 2.0
         order = np.argsort(score, axis=1)[:, :n_true_max]             # random visible subset first
