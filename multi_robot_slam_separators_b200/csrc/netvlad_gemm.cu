@@ -50,6 +50,7 @@ constexpr int kBBlockBytes = BN * 128;   // 32 KB
 constexpr int KP = 12;             // per-list capacity (k <= 8)
 constexpr int kMaxK = 8;
 constexpr int kEpiWarps = 8;
+constexpr int kSeedTiles = 0;                      // database tiles of the threshold seed pass
 constexpr int kThreads = (2 + kEpiWarps) * 32;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 constexpr int kQueue = 256;        // candidates per row the re-rank kernel handles before falling back
 constexpr int kMaxLists = 1024 / KP;
@@ -742,6 +743,28 @@ int sepb_netvlad_tensor_topk(sepb_ctx* ctx, const sepb_db* cdb, const double* d_
   if (!ctx->cfg_gemm) {
     SEPB_CUDA(ctx, cudaFuncSetAttribute(netvlad_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ctx->cfg_gemm = true;
+  }
+  // Seed pass: the same kernel over the first kSeedTiles database tiles only (one split, its lists are overwritten by
+  // the main pass).  It leaves row_thr = (k-th smallest of a 512-column sample) + 2E, a valid bound like every value
+  // written there, so the 2 * splits lists of the main pass start inside a window instead of at +inf and take a
+  // fraction of the list inserts (437 -> 99 per row at 10 k x 10 k, k = 5).  Off by default: the out-of-line hit loop is
+  // warp-uniform over 32 rows, so 4.4x fewer inserts only removed a third of its iterations and the extra launch cost
+  // more than that (0.362 -> 0.400 ms measured).  Kept as the first half of a per-lane candidate queue.
+  int seed_tiles = (kSeedTiles > 0 && tiles_n >= 4 * kSeedTiles) ? kSeedTiles : 0;
+  if (const char* e = getenv("SEPB_K1_SEED")) seed_tiles = std::max(0, std::min(atoi(e), tiles_n));   // developer override
+  if (seed_tiles > 0) {
+    GemmParams sp = gp;
+    sp.tiles_n = seed_tiles;
+    sp.n = std::min(n, seed_tiles * BN);
+    sp.splits = 1;
+    sp.n_items = row_blocks;
+    sp.lists = 2;
+    sp.dbg_v = nullptr;
+    sp.stats = nullptr;
+    netvlad_gemm_kernel<<<std::min(ctx->sm_count, row_blocks), kThreads, smem, ctx->stream>>>(
+        tmQ, *reinterpret_cast<const CUtensorMap*>(db->tmap), sp);
+    ctx->launches++;
+    SEPB_CUDA(ctx, cudaGetLastError());
   }
   netvlad_gemm_kernel<<<grid, kThreads, smem, ctx->stream>>>(tmQ, *reinterpret_cast<const CUtensorMap*>(db->tmap), gp);
   ctx->launches++;
