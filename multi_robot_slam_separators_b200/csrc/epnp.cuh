@@ -1,21 +1,21 @@
 // 5-point EPnP minimal solver: operation-for-operation replay of cv::solvePnP(SOLVEPNP_EPNP) as
 // PnPRansacCallback::runKernel reaches it (undistortPoints -> epnp::compute_pose), see cvmath.cuh.
-// Per-thread scratch lives in a `cvm::Heap` of kEpnpHeap doubles:
+// Per-thread scratch lives in a `cvm::Heap` of kEpnpHeap doubles (174: five one-warp CTAs of K3 fit one SM):
 //   [0,144)   12x12 M^T M / its Jacobi sweep; afterwards rows 8..11 ([96,144)) are the null-space
 //             vectors, [0,60) holds L_6x10 and [60,96) is small-SVD scratch
-//   [144,164) barycentric alphas (5x4)      [164,176) control points cws (4x3)
-//   [176,208) W of the big SVD, afterwards W / Vt of the small SVDs
+//   [144,174) control points cws (4x3) until rho is formed, then W of the big SVD, then W / Vt of the small SVDs
+// The barycentric alphas (5x4) live in the caller's local memory: they are read once per point while M^T M
+// is accumulated and once per candidate pose.
 #pragma once
 #include "cvmath.cuh"
 
 namespace cvm {
 
-constexpr int kEpnpHeap = 208;
+constexpr int kEpnpHeap = 174;
 constexpr int kN = 5;  // model points
 
 namespace detail {
-constexpr int H_AT = 0, H_L = 0, H_SAT = 60, H_UT = 96, H_ALPHA = 144, H_CWS = 164, H_W = 176, H_SW = 176,
-              H_SVT = 181;
+constexpr int H_AT = 0, H_L = 0, H_SAT = 60, H_UT = 96, H_CWS = 144, H_W = 144, H_SW = 144, H_SVT = 149;
 
 CVM_HD inline double dot3(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
 
@@ -140,7 +140,7 @@ CVM_HD CVM_NOINLINE inline void gauss_newton(Heap h, const double* rho, double* 
 }
 
 // compute_ccs / compute_pcs / solve_for_sign / estimate_R_and_t / reprojection_error
-CVM_HD CVM_NOINLINE inline double compute_R_and_t(Heap h, const float* o, const double* us, const Intrinsics& K, const double* betas,
+CVM_HD CVM_NOINLINE inline double compute_R_and_t(Heap h, const double* alpha, const float* o, const double* us, const Intrinsics& K, const double* betas,
                                      double* R, double* t) {
   double ccs[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
   for (int i = 0; i < 4; ++i) {
@@ -150,8 +150,7 @@ CVM_HD CVM_NOINLINE inline double compute_R_and_t(Heap h, const float* o, const 
   }
   double pcs[kN][3];
   for (int i = 0; i < kN; ++i) {
-    const double a0 = h[H_ALPHA + 4 * i], a1 = h[H_ALPHA + 4 * i + 1], a2 = h[H_ALPHA + 4 * i + 2],
-                 a3 = h[H_ALPHA + 4 * i + 3];
+    const double a0 = alpha[4 * i], a1 = alpha[4 * i + 1], a2 = alpha[4 * i + 2], a3 = alpha[4 * i + 3];
     for (int j = 0; j < 3; ++j) pcs[i][j] = a0 * ccs[0][j] + a1 * ccs[1][j] + a2 * ccs[2][j] + a3 * ccs[3][j];
   }
   if (pcs[0][2] < 0.0) {
@@ -246,6 +245,7 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
     }
   }
   // ---- compute_barycentric_coordinates: cvInvert(CC, CV_SVD)
+  double alpha[4 * kN];
   {
     Heap At = h.at(0), W = h.at(9), Vt = h.at(12);
     // CC[i][j-1] = cws[j][i] - cws[0][i]; Jacobi runs on rows of CC^T: At[c][r] = CC[r][c]
@@ -265,30 +265,51 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
       for (int j = 0; j < 3; ++j)
         a[1 + j] = ci[3 * j] * (px - h[H_CWS]) + ci[3 * j + 1] * (py - h[H_CWS + 1]) + ci[3 * j + 2] * (pz - h[H_CWS + 2]);
       a[0] = 1.0 - a[1] - a[2] - a[3];
-      for (int j = 0; j < 4; ++j) h[H_ALPHA + 4 * i + j] = a[j];
+      for (int j = 0; j < 4; ++j) alpha[4 * i + j] = a[j];
+    }
+  }
+  // rho (squared control-point distances) first: the control points share their slots with W of the big SVD
+  double rho[6];
+  {
+    double c[4][3];
+    for (int i = 0; i < 4; ++i)
+      for (int j = 0; j < 3; ++j) c[i][j] = h[H_CWS + 3 * i + j];
+    const int pa[6] = {0, 0, 0, 1, 1, 2}, pb[6] = {1, 2, 3, 2, 3, 3};
+    for (int i = 0; i < 6; ++i) {
+      const double d0 = c[pa[i]][0] - c[pb[i]][0], d1 = c[pa[i]][1] - c[pb[i]][1], d2 = c[pa[i]][2] - c[pb[i]][2];
+      rho[i] = d0 * d0 + d1 * d1 + d2 * d2;
     }
   }
   // ---- M^T M (mulTransposed over the 10 x 12 M of fill_M, rows in order u0,v0,u1,v1,...)
   {
+    // Every entry is s = 0; for each point: s += m1[a] * m1[b]; s += m2[a] * m2[b] -- accumulated here point by point
+    // (same additions in the same order per entry), so that the alphas are read once per point and stay in registers.
     Heap At = h.at(H_AT);
     for (int a = 0; a < 12; ++a)
-      for (int b = a; b < 12; ++b) {
-        double s = 0;
-        const int ka = a / 3, ca = a % 3, kb = b / 3, cb = b % 3;
-        for (int i = 0; i < kN; ++i) {
-          const double aa = h[H_ALPHA + 4 * i + ka], ab = h[H_ALPHA + 4 * i + kb];
-          const double u = us[2 * i], v = us[2 * i + 1];
-          // row 2i: [a*fu, 0, a*(uc-u)], row 2i+1: [0, a*fv, a*(vc-v)]
-          const double m1a = ca == 0 ? aa * K.fx : (ca == 1 ? 0.0 : aa * (K.cx - u));
-          const double m1b = cb == 0 ? ab * K.fx : (cb == 1 ? 0.0 : ab * (K.cx - u));
-          const double m2a = ca == 0 ? 0.0 : (ca == 1 ? aa * K.fy : aa * (K.cy - v));
-          const double m2b = cb == 0 ? 0.0 : (cb == 1 ? ab * K.fy : ab * (K.cy - v));
-          s += m1a * m1b;
-          s += m2a * m2b;
-        }
-        At[a * 12 + b] = s;  // symmetric: row a of MtM^T == row a of MtM
-        At[b * 12 + a] = s;
+      for (int b = a; b < 12; ++b) At[a * 12 + b] = 0;
+    CVM_NOUNROLL
+    for (int i = 0; i < kN; ++i) {
+      const double u = us[2 * i], v = us[2 * i + 1];
+      double m1[12], m2[12];   // row 2i: [a*fu, 0, a*(uc-u)] x 4, row 2i+1: [0, a*fv, a*(vc-v)] x 4
+      CVM_UNROLL
+      for (int k4 = 0; k4 < 4; ++k4) {
+        const double aa = alpha[4 * i + k4];
+        m1[3 * k4] = aa * K.fx; m1[3 * k4 + 1] = 0.0; m1[3 * k4 + 2] = aa * (K.cx - u);
+        m2[3 * k4] = 0.0; m2[3 * k4 + 1] = aa * K.fy; m2[3 * k4 + 2] = aa * (K.cy - v);
       }
+      CVM_UNROLL
+      for (int a = 0; a < 12; ++a) {
+        CVM_UNROLL
+        for (int b = a; b < 12; ++b) {
+          double s = At[a * 12 + b];
+          s += m1[a] * m1[b];
+          s += m2[a] * m2[b];
+          At[a * 12 + b] = s;
+        }
+      }
+    }
+    for (int a = 0; a < 12; ++a)
+      for (int b = a + 1; b < 12; ++b) At[b * 12 + a] = At[a * 12 + b];  // symmetric: row a of MtM^T == row a of MtM
     K3_T0(t_j);
 #if defined(__CUDA_ARCH__) && SEPB_JACOBI_ILP
     jacobi12_sweeps_ilp(At, h.at(H_W));   // same arithmetic, three row-disjoint rotations in flight (cvmath.cuh)
@@ -322,17 +343,6 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
     }
     for (int i = 0; i < 60; ++i) h[H_L + i] = L[i];  // rows 0..4 of the swept matrix are dead by now
   }
-  double rho[6];
-  {
-    double c[4][3];
-    for (int i = 0; i < 4; ++i)
-      for (int j = 0; j < 3; ++j) c[i][j] = h[H_CWS + 3 * i + j];
-    const int pa[6] = {0, 0, 0, 1, 1, 2}, pb[6] = {1, 2, 3, 2, 3, 3};
-    for (int i = 0; i < 6; ++i) {
-      const double d0 = c[pa[i]][0] - c[pb[i]][0], d1 = c[pa[i]][1] - c[pb[i]][1], d2 = c[pa[i]][2] - c[pb[i]][2];
-      rho[i] = d0 * d0 + d1 * d1 + d2 * d2;
-    }
-  }
   double Rs[3][9], ts[3][3], errs[3];
   // ---- approx 1: [B11 B12 B13 B14]
   {
@@ -351,7 +361,7 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
       betas[3] = b4[3] / betas[0];
     }
     gauss_newton(h, rho, betas);
-    errs[0] = compute_R_and_t(h, o, us, K, betas, Rs[0], ts[0]);
+    errs[0] = compute_R_and_t(h, alpha, o, us, K, betas, Rs[0], ts[0]);
   }
   // ---- approx 2: [B11 B12 B22]
   {
@@ -369,7 +379,7 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
     betas[2] = 0.0;
     betas[3] = 0.0;
     gauss_newton(h, rho, betas);
-    errs[1] = compute_R_and_t(h, o, us, K, betas, Rs[1], ts[1]);
+    errs[1] = compute_R_and_t(h, alpha, o, us, K, betas, Rs[1], ts[1]);
   }
   // ---- approx 3: [B11 B12 B22 B13 B23]
   {
@@ -387,7 +397,7 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
     betas[2] = b5[3] / betas[0];
     betas[3] = 0.0;
     gauss_newton(h, rho, betas);
-    errs[2] = compute_R_and_t(h, o, us, K, betas, Rs[2], ts[2]);
+    errs[2] = compute_R_and_t(h, alpha, o, us, K, betas, Rs[2], ts[2]);
   }
   int N = 0;
   if (errs[1] < errs[0]) N = 1;

@@ -11,6 +11,8 @@
 // hypothesis), applying OpenCV's `goodCount > max(best, 4)` rule and RANSACUpdateNumIters after each
 // one, which reproduces the sequential result exactly and keeps most of its early exit.
 // Compiled with -fmad=false (see build.py): no multiply-add contraction, like the cv2 build.
+#include <cstdlib>
+
 #include "common.cuh"
 
 // developer build (SEPB_K3_PROFILE=1 python -m ...build): cycle counters per phase, read by sepb_debug_k3_prof
@@ -540,7 +542,8 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   }
   for (int i = 0; i < 9; ++i) k.local_R[i] = p->local_R[i];
   k.table_h = table_h;
-  const size_t smem = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
+  size_t smem = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
+  if (const char* e = getenv("SEPB_K3_PAD_SMEM")) smem += (size_t)atoi(e);   // developer switch: fewer resident CTAs per SM
   bool& configured = ctx->cfg_pnp;
   if (!configured) {
     SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
