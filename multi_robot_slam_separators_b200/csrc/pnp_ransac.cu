@@ -85,7 +85,8 @@ __global__ void sample_table_kernel(uint16_t* table, int max_count, int H) {
 constexpr int kOrderThreads = 1024;
 constexpr int kStateInts = 4;   // per-pair state header: niters (0 = nothing left to do), best_good, best_h, hk
 __global__ void __launch_bounds__(kOrderThreads)
-pnp_order_kernel(const int32_t* __restrict__ state, int state_stride, int n_pairs, int32_t* __restrict__ order) {
+pnp_order_kernel(const int32_t* __restrict__ state, int state_stride, int n_pairs, int32_t* __restrict__ order,
+                 const int32_t* __restrict__ n_matches, const int32_t* __restrict__ only_if_ok) {
   __shared__ int hist[SEPB_MAX_FEATURES + 2];   // bin max(0, 4096 - niters); last bin = pairs with nothing left
   __shared__ int warp_tot[32];
   constexpr int kBins = SEPB_MAX_FEATURES + 2;
@@ -93,12 +94,16 @@ pnp_order_kernel(const int32_t* __restrict__ state, int state_stride, int n_pair
   for (int i = tid; i < kBins; i += kOrderThreads) hist[i] = 0;
   __syncthreads();
   auto key_of = [&](int p) {
+    if (n_matches) {   // before phase 0: pairs that will run RANSAC first (so that they share CTAs), every pair listed
+      const bool run = n_matches[p] >= 5 && (!only_if_ok || only_if_ok[p] == 1);
+      return run ? 0 : kBins - 1;
+    }
     const int it = state[(size_t)p * state_stride];
     return it > 0 ? max(0, SEPB_MAX_FEATURES - it) : kBins - 1;
   };
   for (int p = tid; p < n_pairs; p += kOrderThreads) atomicAdd(&hist[key_of(p)], 1);
   __syncthreads();
-  if (tid == 0) order[n_pairs] = n_pairs - hist[kBins - 1];   // pairs that resume
+  if (tid == 0) order[n_pairs] = n_matches ? n_pairs : n_pairs - hist[kBins - 1];   // pairs listed
   // exclusive scan of the bins: each thread owns a contiguous run of bins
   constexpr int kPer = (kBins + kOrderThreads - 1) / kOrderThreads;
   int local[kPer], sum = 0;
@@ -133,7 +138,7 @@ pnp_order_kernel(const int32_t* __restrict__ state, int state_stride, int n_pair
   __syncthreads();
   for (int p = tid; p < n_pairs; p += kOrderThreads) {
     const int k = key_of(p);
-    if (k != kBins - 1) order[atomicAdd(&hist[k], 1)] = p;
+    if (k != kBins - 1 || n_matches) order[atomicAdd(&hist[k], 1)] = p;
   }
 }
 
@@ -265,7 +270,11 @@ __device__ __forceinline__ void lm_step_warp(cvm::Heap h, const double* JtJ, con
   for (int i = 0; i < 6; ++i) param[i] = __shfl_sync(0xFFFFFFFFu, param[i], 0);
 }
 
-__global__ void __launch_bounds__(kWarp)
+// One warp per keyframe pair.  WPC warps (pairs) share a CTA: the warps of a CTA start together and, as long as their
+// work is alike (phase 0: chunk 0 of every pair), run the same code at about the same time, which is what the
+// instruction caches want -- ncu shows the GPC-level cache at 40-50 % of its request rate for this 330 KB kernel.
+template <int WPC>
+__global__ void __launch_bounds__(kWarp * WPC)
 pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs,
                   const int32_t* __restrict__ n_matches, const uint16_t* __restrict__ match_from,
                   const uint16_t* __restrict__ match_to, const int32_t* __restrict__ n_unique_to,
@@ -278,11 +287,14 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
                   int phase /*-1: whole run, 0: chunk 0 (+ finish if done), 1: resume*/, int32_t* __restrict__ state,
                   int state_stride) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  double* heap_base = reinterpret_cast<double*>(smem_raw);
-  uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)cvm::kEpnpHeap * kSolveLanes * 8);  // 2 * kMaskWords
-  const int lane = threadIdx.x;
-  if ((int)blockIdx.x >= (phase == 1 ? order[n_pairs] : n_pairs)) return;
-  const int pair = phase == 1 ? order[blockIdx.x] : blockIdx.x;
+  constexpr size_t kWarpBytes = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
+  uint8_t* wsm = smem_raw + (threadIdx.x >> 5) * kWarpBytes;   // this warp's heap + masks
+  double* heap_base = reinterpret_cast<double*>(wsm);
+  uint32_t* s_mask = reinterpret_cast<uint32_t*>(wsm + (size_t)cvm::kEpnpHeap * kSolveLanes * 8);  // 2 * kMaskWords
+  const int lane = threadIdx.x & 31;
+  const int slot = blockIdx.x * WPC + (threadIdx.x >> 5);
+  if (slot >= (order ? order[n_pairs] : n_pairs)) return;
+  const int pair = order ? order[slot] : slot;
   int32_t* st = state ? state + (size_t)pair * state_stride : nullptr;
   if (phase == 0 && lane == 0) st[0] = 0;   // nothing to resume unless the chunk loop says so
   // second pass (estimate_transformation's call with guess = first result): pairs whose first pass failed keep it
@@ -294,7 +306,7 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
   const int M = valid_pair ? n_matches[pair] : 0;
   const int nf = valid_pair ? from.count[fi] : 0;
   const int nu = n_unique_to ? n_unique_to[pair] : M;
-  float* stage_buf = reinterpret_cast<float*>(smem_raw + kStageOffBytes);
+  float* stage_buf = reinterpret_cast<float*>(wsm + kStageOffBytes);
   Corr cr{from.kp3d + (size_t)fi * from.max_feat * 3, to.kp2d + (size_t)ti * to.max_feat * 2,
           match_from + (size_t)pair * from.max_feat, match_to + (size_t)pair * from.max_feat,
           M <= kStageCap ? stage_buf : nullptr};
@@ -546,15 +558,30 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   if (const char* e = getenv("SEPB_K3_PAD_SMEM")) smem += (size_t)atoi(e);   // developer switch: fewer resident CTAs per SM
   bool& configured = ctx->cfg_pnp;
   if (!configured) {
-    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem + 200000 > 232448 ? 232448 : smem + 200000)));
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem)));
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(5 * smem)));
     configured = true;
   }
+  int wpc0 = 5;   // warps (pairs) per CTA in phase 0; the other launches use one-warp CTAs (variable work per pair)
+  if (const char* e = getenv("SEPB_K3_WPC")) wpc0 = atoi(e);
+  int wpc1 = 1;
+  if (const char* e = getenv("SEPB_K3_WPC1")) wpc1 = atoi(e);
   auto launch = [&](int phase, const int32_t* d_order, int32_t* d_state, int stride) {
-    pnp_ransac_kernel<<<n_pairs, kWarp, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, d_n_matches, d_match_from,
-                                                            d_match_to, d_n_unique_to, d_table, d_custom_samples, custom_h,
-                                                            d_guess, d_only_if_ok, k, d_status, d_n_inliers, d_pose,
-                                                            d_transform, d_inlier_mask, mask_words, d_best_hyp, d_iters_run,
-                                                            d_order, phase, d_state, stride);
+#define SEPB_K3_LAUNCH(W)                                                                                              \
+  pnp_ransac_kernel<W><<<(n_pairs + W - 1) / W, kWarp * W, smem * W, ctx->stream>>>(                                   \
+      from, to, d_pairs, n_pairs, d_n_matches, d_match_from, d_match_to, d_n_unique_to, d_table, d_custom_samples,     \
+      custom_h, d_guess, d_only_if_ok, k, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words,      \
+      d_best_hyp, d_iters_run, d_order, phase, d_state, stride)
+    const int w = phase == 0 ? wpc0 : phase == 1 ? wpc1 : 1;
+    if (w == 5) {
+      SEPB_K3_LAUNCH(5);
+    } else if (w == 2) {
+      SEPB_K3_LAUNCH(2);
+    } else {
+      SEPB_K3_LAUNCH(1);
+    }
+#undef SEPB_K3_LAUNCH
     ctx->launches++;
   };
   // below a few waves of CTAs there is no tail to trim: one launch.  Otherwise chunk 0, sort, resume (pnp_order_kernel)
@@ -579,8 +606,14 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   }
   int32_t* d_state = ctx->k3_order;
   int32_t* d_order = ctx->k3_order + (size_t)n_pairs * stride;
-  launch(0, nullptr, d_state, stride);
-  pnp_order_kernel<<<1, kOrderThreads, 0, ctx->stream>>>(d_state, stride, n_pairs, d_order);
+  if (wpc0 > 1) {   // group the pairs that will run RANSAC into the same CTAs
+    pnp_order_kernel<<<1, kOrderThreads, 0, ctx->stream>>>(nullptr, 0, n_pairs, d_order, d_n_matches, d_only_if_ok);
+    ctx->launches++;
+    launch(0, d_order, d_state, stride);
+  } else {
+    launch(0, nullptr, d_state, stride);
+  }
+  pnp_order_kernel<<<1, kOrderThreads, 0, ctx->stream>>>(d_state, stride, n_pairs, d_order, nullptr, nullptr);
   ctx->launches++;
   launch(1, d_order, d_state, stride);
   SEPB_CUDA(ctx, cudaGetLastError());
