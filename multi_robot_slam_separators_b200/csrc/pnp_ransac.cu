@@ -559,7 +559,6 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   bool& configured = ctx->cfg_pnp;
   if (!configured) {
     SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem + 200000 > 232448 ? 232448 : smem + 200000)));
-    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem)));
     SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(5 * smem)));
     configured = true;
   }
@@ -576,8 +575,6 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
     const int w = phase == 0 ? wpc0 : phase == 1 ? wpc1 : 1;
     if (w == 5) {
       SEPB_K3_LAUNCH(5);
-    } else if (w == 2) {
-      SEPB_K3_LAUNCH(2);
     } else {
       SEPB_K3_LAUNCH(1);
     }
