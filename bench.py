@@ -384,7 +384,8 @@ def run_ours(args):
                            "peak_source": "sepb_measure_peak FP64 FMA microbenchmark, same run", "traffic": traffic.get("K3"),
                            "launches_per_step": 2, "note": "latency-bound by construction: OpenCV's serial f64 operation order is "
                            "replayed per hypothesis (bit-exact inlier sets); two launches (chunk 0, longest-first resume)"}
-        dominant = max((("K1", ms_k1), ("K2", ms_k2), ("K3", ms_k3)), key=lambda kv: kv[1])[0]
+        # dominant kernel = longest single launch (K3 runs as two launches per step: chunk 0, then the resume)
+        dominant = max((("K1", ms_k1), ("K2", ms_k2), ("K3", ms_k3 / 2.0)), key=lambda kv: kv[1])[0]
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_total_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "s8/s32 (Hamming GEMM) + f64 (PnP, NetVLAD)" if match_kernel == "tensor" else "u32+f64",
@@ -392,7 +393,8 @@ def run_ours(args):
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
                         "steps": e2e_steps, "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified"},
                 "gpu_launches": int(launches),
-                "roofline": dict(rooflines[dominant], dominant=dominant),
+                "roofline": dict(rooflines[dominant], dominant=dominant, dominant_rule="longest single kernel launch of the step; "
+                                 "every kernel of the step is in `rooflines`"),
                 "rooflines": rooflines,
                 "kernels_ms": {"K1_netvlad_topk": ms_k1, "K2_hamming_match": ms_k2, "K3_pnp_ransac": ms_k3,
                                "step_share_K2": ms_k2 / (ms_total / args.steps)},
