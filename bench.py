@@ -367,13 +367,21 @@ def run_ours(args):
                                "algorithmic_bytes": k2_bytes,
                                "peak_source": peak_src + ": 2 x measured bf16 burst (int8 dense issues at twice the bf16 rate; "
                                                          "kernel timed alone)",
-                               "hbm_gbs": k2_gbs, "popc_equivalent_per_s": k2_popc}
+                               "hbm_gbs": k2_gbs, "popc_equivalent_per_s": k2_popc,
+                               # every s32 accumulator is read back once (tcgen05.ld): F_to x F_from x 4 B per pair against the
+                               # measured TMEM read rate -- informational: the accumulator read-back is NOT what bounds K2T
+                               "tmem_read": {"achieved_tbs": P * 4.0 * args.feat * args.feat / (ms_k2 * 1e-3) / 1e12,
+                                             "peak_tbs": eng.ctx.measure_peak("tmem_pack16") / 1e12,
+                                             "peak_source": "sepb_measure_peak: tcgen05.ld 32x32b.x16.pack::16b microbenchmark, same run"}}
         else:
             rooflines["K2"] = {"kernel": "hamming_match_kernel (K2, POPC pipe)", "bound": "hbm", "achieved": k2_gbs,
                                "peak": hbm_peak, "unit": "GB/s", "frac": k2_gbs / hbm_peak, "traffic": None,
                                "peak_source": peak_src, "note": "POPC-issue bound, not HBM bound",
                                "int_pipe": {"achieved": k2_popc, "peak": popc_peak, "unit": "popc32/s", "frac": k2_popc / popc_peak,
                                             "peak_source": "sepb_measure_peak microbenchmark, same run"}}
+        if "tmem_read" in rooflines["K2"]:
+            tr = rooflines["K2"]["tmem_read"]
+            tr["frac"] = tr["achieved_tbs"] / tr["peak_tbs"]
         k1_tflops = 2.0 * args.frames * args.frames * args.dim / (ms_k1 * 1e-3) / 1e12
         rooflines["K1"] = {"kernel": "netvlad %s top-%d" % (args.nn, args.topk), "bound": "tensor", "achieved": k1_tflops,
                            "peak": bf16_burst, "unit": "TFLOP/s", "frac": k1_tflops / bf16_burst, "traffic": traffic.get("K1"),

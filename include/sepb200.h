@@ -270,6 +270,7 @@ SEPB_API int sepb_estimate_transformations_dev(sepb_ctx* ctx, const sepb_frames*
 
 /* ---- measurement support (roofline denominators not in MEASURED_PEAKS.json) ----------------
  * kind 0: POPC instructions/s (K2's bounding pipe), kind 1: FP64 FMA/s (K3's).  Best of reps. */
+/* kind 0: POPC/s, 1: FP64 FMA/s, 2 / 3: TMEM bytes/s read by tcgen05.ld (plain / .pack::16b) */
 SEPB_API int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s);
 /* developer hook (K3): cycle counters {EPnP solve, Rodrigues, scoring, refit, chunk-solves, 12x12 Jacobi, Jacobi
  * sweeps, 0} summed over warps; all zero and return 0 unless the library was built with SEPB_K3_PROFILE=1. */

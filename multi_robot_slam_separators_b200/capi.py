@@ -184,9 +184,10 @@ class Context:
         return int(lib().sepb_ctx_launch_count(self._h))
 
     def measure_peak(self, kind: str, reps: int = 5) -> float:
-        """'popc' -> POPC/s, 'dfma' -> FP64 FMA/s (measured microbenchmarks)."""
+        """'popc' -> POPC/s, 'dfma' -> FP64 FMA/s, 'tmem' / 'tmem_pack16' -> TMEM bytes/s read by tcgen05.ld
+        (measured microbenchmarks)."""
         v = C.c_double()
-        self.check(lib().sepb_measure_peak(self._h, {"popc": 0, "dfma": 1}[kind], reps, C.byref(v)))
+        self.check(lib().sepb_measure_peak(self._h, {"popc": 0, "dfma": 1, "tmem": 2, "tmem_pack16": 3}[kind], reps, C.byref(v)))
         return v.value
 
     def set_match_kernel(self, which: str):

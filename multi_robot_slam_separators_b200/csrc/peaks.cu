@@ -1,6 +1,7 @@
 // Roofline denominators that MEASURED_PEAKS.json does not carry: POPC (K2) and FP64 FMA (K3)
 // issue-rate microbenchmarks.  Measurement support only; not on the data path.
 #include "common.cuh"
+#include "umma.cuh"
 
 namespace {
 
@@ -25,15 +26,56 @@ __global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters, 
   out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
 
+// TMEM -> register read rate (tcgen05.ld 32x32b.x32, and the .pack::16b form K2T uses): 8 warps of one CTA per SM, two
+// per lane quarter, sweep the 512 columns `iters` times.  Uninitialised TMEM content is fine: only the rate matters.
+__global__ void __launch_bounds__(256, 1) tmem_read_peak_kernel(uint32_t* out, int iters, int packed) {
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) umma::tmem_alloc(&slot, 512);
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t base = slot + ((uint32_t)((warp & 3) * 32) << 16);
+  uint32_t acc = 0;
+  for (int i = 0; i < iters; ++i) {
+    for (int c = 0; c < 512; c += 64) {
+      if (packed) {
+        uint32_t a[16], b[16];
+        umma::tmem_ld32_pack16(base + c, a);
+        umma::tmem_ld32_pack16(base + c + 32, b);
+        umma::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc ^= a[j] + b[j];
+      } else {
+        uint32_t a[32], b[32];
+        umma::tmem_ld32(base + c, a);
+        umma::tmem_ld32(base + c + 32, b);
+        umma::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc ^= a[j] + b[j];
+      }
+    }
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    umma::tc_fence_after();
+    umma::tmem_dealloc(slot, 512);
+  }
+}
+
 }  // namespace
 
 extern "C" {
 
-// kind 0: POPC ops/s; kind 1: FP64 FMA/s (one FMA = 2 FLOP).  Best of `reps` launches.
+// kind 0: POPC ops/s; kind 1: FP64 FMA/s (one FMA = 2 FLOP); kind 2 / 3: TMEM bytes/s read by tcgen05.ld (32-bit cells,
+// plain / .pack::16b).  Best of `reps` launches.
 int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s) {
   if (!ctx || !ops_per_s) return SEPB_E_INVALID;
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
-  const int blocks = ctx->sm_count * 8, threads = 256, iters = kind == 0 ? 4096 : 2048;
+  const bool tm = kind == 2 || kind == 3;
+  const int blocks = tm ? ctx->sm_count : ctx->sm_count * 8, threads = 256, iters = kind == 0 ? 4096 : tm ? 512 : 2048;
   void* buf = sepb_scratch(ctx, (size_t)blocks * threads * 8);
   if (!buf) return (int)cudaErrorMemoryAllocation;
   cudaEvent_t e0, e1;
@@ -43,13 +85,16 @@ int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s) {
   for (int r = 0; r < reps + 1; ++r) {
     SEPB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     if (kind == 0) popc_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((uint32_t*)buf, iters, 12345u + r);
-    else dfma_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((double*)buf, iters, 1.0 + r);
+    else if (kind == 1) dfma_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((double*)buf, iters, 1.0 + r);
+    else tmem_read_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((uint32_t*)buf, iters, kind == 3);
     ctx->launches++;
     SEPB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
     SEPB_CUDA(ctx, cudaEventSynchronize(e1));
     float ms = 0;
     SEPB_CUDA(ctx, cudaEventElapsedTime(&ms, e0, e1));
-    const double ops = (double)blocks * threads * iters * 8.0 / (ms * 1e-3);
+    // TMEM: every warp reads 32 lanes x 512 columns x 4 B per sweep (the packed form returns half the registers)
+    const double ops = tm ? (double)blocks * 8 * iters * (32.0 * 512 * 4) / (ms * 1e-3)
+                          : (double)blocks * threads * iters * 8.0 / (ms * 1e-3);
     if (r > 0 && ops > best) best = ops;
   }
   cudaEventDestroy(e0);

@@ -11,6 +11,8 @@ print("popc/s %.3e  dfma/s %.3e" % (ctx.measure_peak("popc"), ctx.measure_peak("
 nF = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 P = int(sys.argv[2]) if len(sys.argv) > 2 else 20000
 A, B = synth.make_robots(2, nF, n_feat=1000, dim=128, seed=1002)
+if os.environ.get("SEPB_K2_COUNT"):      # developer: shorter frames -> fixed cost per pair of the matcher kernels
+    A.count[:] = int(os.environ["SEPB_K2_COUNT"]); B.count[:] = int(os.environ["SEPB_K2_COUNT"])
 fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
 rng = np.random.default_rng(0)
 pairs = torch.from_numpy(rng.integers(0, nF, (P, 2)).astype(np.int32)).cuda()
