@@ -340,10 +340,16 @@ netvlad_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
               const float4 w = *reinterpret_cast<const float4*>(nd + ch * 32 + g * 4);
               const float vs[4] = {fmaf(-2.f, __uint_as_float(x[0]), w.x), fmaf(-2.f, __uint_as_float(x[1]), w.y),
                                    fmaf(-2.f, __uint_as_float(x[2]), w.z), fmaf(-2.f, __uint_as_float(x[3]), w.w)};
+              // lane-private loop over THIS lane's hits of the group: the warp pays for the largest number of hits one
+              // of its rows has here (usually 1), not for one pass per column position (0.362 -> 0.301 ms at 10k x 10k)
+              uint32_t hm = (vs[0] <= thr && vs[0] < INFINITY ? 1u : 0u) | (vs[1] <= thr && vs[1] < INFINITY ? 2u : 0u) |
+                            (vs[2] <= thr && vs[2] < INFINITY ? 4u : 0u) | (vs[3] <= thr && vs[3] < INFINITY ? 8u : 0u);
 #pragma unroll 1
-              for (int u = 0; u < 4; ++u) {
+              while (hm) {
+                const int u = __ffs(hm) - 1;
+                hm &= hm - 1;
                 const float v = u == 0 ? vs[0] : u == 1 ? vs[1] : u == 2 ? vs[2] : vs[3];
-                if (v <= thr && v < INFINITY) {
+                if (v <= thr) {   // an earlier hit of this group may have tightened the threshold
                   const int c = t * BN + ch * 32 + g * 4 + u;
                   bool ign = false;
                   for (int q = ig0; q < ig1; ++q) ign |= p.ign_col[q] == (int32_t)(p.base + c);
