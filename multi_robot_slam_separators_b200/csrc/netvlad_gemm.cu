@@ -329,27 +329,36 @@ netvlad_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             gm |= (m <= thr) ? (1u << (j >> 2)) : 0u;
           }
           uint32_t wm = __reduce_or_sync(0xFFFFFFFFu, gm);
+          // trips over PAIRS of adjacent 4-column groups (8 columns re-read per TMEM round trip): while the lists warm
+          // up every group of the warp is flagged and this halves the trips; afterwards the extra group costs little
+          uint32_t wm2 = (wm | (wm >> 1)) & 0x55u;
 #pragma unroll 1
-          while (wm) {
-            const int g = __ffs(wm) - 1;
-            wm &= wm - 1;
-            uint32_t x[4];
-            umma::tmem_ld4(taddr + (uint32_t)(ch * 32 + g * 4), x);
+          while (wm2) {
+            const int g = __ffs(wm2) - 1;   // even group index
+            wm2 &= wm2 - 1;
+            uint32_t x[8];
+            umma::tmem_ld8(taddr + (uint32_t)(ch * 32 + g * 4), x);
             umma::tmem_ld_wait();
-            if (gm & (1u << g)) {
-              const float4 w = *reinterpret_cast<const float4*>(nd + ch * 32 + g * 4);
-              const float vs[4] = {fmaf(-2.f, __uint_as_float(x[0]), w.x), fmaf(-2.f, __uint_as_float(x[1]), w.y),
-                                   fmaf(-2.f, __uint_as_float(x[2]), w.z), fmaf(-2.f, __uint_as_float(x[3]), w.w)};
-              // lane-private loop over THIS lane's hits of the group: the warp pays for the largest number of hits one
-              // of its rows has here (usually 1), not for one pass per column position (0.362 -> 0.301 ms at 10k x 10k)
-              uint32_t hm = (vs[0] <= thr && vs[0] < INFINITY ? 1u : 0u) | (vs[1] <= thr && vs[1] < INFINITY ? 2u : 0u) |
-                            (vs[2] <= thr && vs[2] < INFINITY ? 4u : 0u) | (vs[3] <= thr && vs[3] < INFINITY ? 8u : 0u);
+            if ((gm >> g) & 3u) {
+              const float4 w0 = *reinterpret_cast<const float4*>(nd + ch * 32 + g * 4);
+              const float4 w1 = *reinterpret_cast<const float4*>(nd + ch * 32 + g * 4 + 4);
+              const float vs[8] = {fmaf(-2.f, __uint_as_float(x[0]), w0.x), fmaf(-2.f, __uint_as_float(x[1]), w0.y),
+                                   fmaf(-2.f, __uint_as_float(x[2]), w0.z), fmaf(-2.f, __uint_as_float(x[3]), w0.w),
+                                   fmaf(-2.f, __uint_as_float(x[4]), w1.x), fmaf(-2.f, __uint_as_float(x[5]), w1.y),
+                                   fmaf(-2.f, __uint_as_float(x[6]), w1.z), fmaf(-2.f, __uint_as_float(x[7]), w1.w)};
+              // lane-private loop over THIS lane's hits: the warp pays for the largest number of hits one of its rows
+              // has in these 8 columns (usually 1), not for one pass per column position
+              uint32_t hm = 0;
+#pragma unroll
+              for (int u = 0; u < 8; ++u) hm |= (vs[u] <= thr && vs[u] < INFINITY) ? (1u << u) : 0u;
 #pragma unroll 1
               while (hm) {
                 const int u = __ffs(hm) - 1;
                 hm &= hm - 1;
-                const float v = u == 0 ? vs[0] : u == 1 ? vs[1] : u == 2 ? vs[2] : vs[3];
-                if (v <= thr) {   // an earlier hit of this group may have tightened the threshold
+                const float va = (u & 2) ? ((u & 1) ? vs[3] : vs[2]) : ((u & 1) ? vs[1] : vs[0]);
+                const float vb = (u & 2) ? ((u & 1) ? vs[7] : vs[6]) : ((u & 1) ? vs[5] : vs[4]);
+                const float v = (u & 4) ? vb : va;
+                if (v <= thr) {   // an earlier hit may have tightened the threshold
                   const int c = t * BN + ch * 32 + g * 4 + u;
                   bool ign = false;
                   for (int q = ig0; q < ig1; ++q) ign |= p.ign_col[q] == (int32_t)(p.base + c);

@@ -84,6 +84,13 @@ __device__ __forceinline__ void tmem_ld4(uint32_t addr, uint32_t (&r)[4]) {
                : "r"(addr)
                : "memory");
 }
+// 8 consecutive columns
+__device__ __forceinline__ void tmem_ld8(uint32_t addr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(addr)
+               : "memory");
+}
 // same lanes, 32 consecutive columns delivered as 16 registers: the low 16 bits of two adjacent columns
 // per register (column 2i in bits [15:0], column 2i+1 in bits [31:16])
 __device__ __forceinline__ void tmem_ld32_pack16(uint32_t addr, uint32_t (&r)[16]) {
