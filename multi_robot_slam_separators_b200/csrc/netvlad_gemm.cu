@@ -328,46 +328,41 @@ netvlad_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             const float m = fminf(fminf(v0, v1), fminf(v2, v3));
             gm |= (m <= thr) ? (1u << (j >> 2)) : 0u;
           }
-          uint32_t wm = __reduce_or_sync(0xFFFFFFFFu, gm);
-          // trips over PAIRS of adjacent 4-column groups (8 columns re-read per TMEM round trip): while the lists warm
-          // up every group of the warp is flagged and this halves the trips; afterwards the extra group costs little
-          uint32_t wm2 = (wm | (wm >> 1)) & 0x55u;
+          // Slow path, lane-private: a lane walks its OWN flagged groups and picks the group's four accumulators out of
+          // the registers of the branch-free pass with a select tree on the group index (no TMEM re-read, which is a
+          // collective load and forced a warp-uniform loop over the flagged groups of any of the 32 rows).
 #pragma unroll 1
-          while (wm2) {
-            const int g = __ffs(wm2) - 1;   // even group index
-            wm2 &= wm2 - 1;
-            uint32_t x[8];
-            umma::tmem_ld8(taddr + (uint32_t)(ch * 32 + g * 4), x);
-            umma::tmem_ld_wait();
-            if ((gm >> g) & 3u) {
-              const float4 w0 = *reinterpret_cast<const float4*>(nd + ch * 32 + g * 4);
-              const float4 w1 = *reinterpret_cast<const float4*>(nd + ch * 32 + g * 4 + 4);
-              const float vs[8] = {fmaf(-2.f, __uint_as_float(x[0]), w0.x), fmaf(-2.f, __uint_as_float(x[1]), w0.y),
-                                   fmaf(-2.f, __uint_as_float(x[2]), w0.z), fmaf(-2.f, __uint_as_float(x[3]), w0.w),
-                                   fmaf(-2.f, __uint_as_float(x[4]), w1.x), fmaf(-2.f, __uint_as_float(x[5]), w1.y),
-                                   fmaf(-2.f, __uint_as_float(x[6]), w1.z), fmaf(-2.f, __uint_as_float(x[7]), w1.w)};
-              // lane-private loop over THIS lane's hits: the warp pays for the largest number of hits one of its rows
-              // has in these 8 columns (usually 1), not for one pass per column position
-              uint32_t hm = 0;
+          while (gm) {
+            const int g = __ffs(gm) - 1;
+            gm &= gm - 1;
+            const bool b0 = g & 1, b1 = g & 2, b2 = g & 4;
+            uint32_t x[4];
 #pragma unroll
-              for (int u = 0; u < 8; ++u) hm |= (vs[u] <= thr && vs[u] < INFINITY) ? (1u << u) : 0u;
+            for (int u = 0; u < 4; ++u) {
+              const uint32_t s0 = b0 ? r[4 + u] : r[u], s1 = b0 ? r[12 + u] : r[8 + u];
+              const uint32_t s2 = b0 ? r[20 + u] : r[16 + u], s3 = b0 ? r[28 + u] : r[24 + u];
+              const uint32_t t0 = b1 ? s1 : s0, t1 = b1 ? s3 : s2;
+              x[u] = b2 ? t1 : t0;
+            }
+            const float4 w = *reinterpret_cast<const float4*>(nd + ch * 32 + g * 4);
+            const float vs[4] = {fmaf(-2.f, __uint_as_float(x[0]), w.x), fmaf(-2.f, __uint_as_float(x[1]), w.y),
+                                 fmaf(-2.f, __uint_as_float(x[2]), w.z), fmaf(-2.f, __uint_as_float(x[3]), w.w)};
+            uint32_t hm = (vs[0] <= thr && vs[0] < INFINITY ? 1u : 0u) | (vs[1] <= thr && vs[1] < INFINITY ? 2u : 0u) |
+                          (vs[2] <= thr && vs[2] < INFINITY ? 4u : 0u) | (vs[3] <= thr && vs[3] < INFINITY ? 8u : 0u);
 #pragma unroll 1
-              while (hm) {
-                const int u = __ffs(hm) - 1;
-                hm &= hm - 1;
-                const float va = (u & 2) ? ((u & 1) ? vs[3] : vs[2]) : ((u & 1) ? vs[1] : vs[0]);
-                const float vb = (u & 2) ? ((u & 1) ? vs[7] : vs[6]) : ((u & 1) ? vs[5] : vs[4]);
-                const float v = (u & 4) ? vb : va;
-                if (v <= thr) {   // an earlier hit may have tightened the threshold
-                  const int c = t * BN + ch * 32 + g * 4 + u;
-                  bool ign = false;
-                  for (int q = ig0; q < ig1; ++q) ign |= p.ign_col[q] == (int32_t)(p.base + c);
-                  if (!ign) hit(v, c);
-                }
+            while (hm) {
+              const int u = __ffs(hm) - 1;
+              hm &= hm - 1;
+              const float v = u == 0 ? vs[0] : u == 1 ? vs[1] : u == 2 ? vs[2] : vs[3];
+              if (v <= thr) {   // an earlier hit may have tightened the threshold
+                const int c = t * BN + ch * 32 + g * 4 + u;
+                bool ign = false;
+                for (int q = ig0; q < ig1; ++q) ign |= p.ign_col[q] == (int32_t)(p.base + c);
+                if (!ign) hit(v, c);
               }
             }
-            __syncwarp();
           }
+          __syncwarp();
           if (p.dbg_v && row < p.nq) {
             float* o = p.dbg_v + (size_t)row * p.n;
 #pragma unroll
