@@ -194,7 +194,7 @@ CVM_HD inline void jacobi_finish(Heap At, Heap W, Heap Vt) {
 // issued together and the independent element updates overlap; the ORDER of the arithmetic on every
 // accumulator is unchanged (sequential in k), which is what bit-exactness against cv2 needs.
 template <int m, int n, bool want_v>
-CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
+CVM_HD CVM_NOINLINE inline void jacobi_svd_fixed(Heap At, Heap W, Heap Vt) {
   const double eps = kDblEps * 10;
   for (int i = 0; i < n; ++i) {
     double sd = 0;
@@ -264,6 +264,154 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
     if (!changed) break;
   }
   jacobi_finish<m, n, want_v>(At, W, Vt);
+}
+
+// run-time n (one body for every 6 x n solve of the path: fewer instructions to fetch; same operations) -- tail: singular values, descending sort, normalisation (random completion of zero rows)
+template <int m, bool want_v>
+CVM_HD inline void jacobi_finish_rt(Heap At, Heap W, Heap Vt, const int n) {
+  const double eps = kDblEps * 10;
+  CVM_NOUNROLL
+  for (int i = 0; i < n; ++i) {
+    double sd = 0;
+    CVM_UNROLL
+    for (int k = 0; k < m; ++k) {
+      const double t = At[i * m + k];
+      sd += t * t;
+    }
+    W[i] = sqrt(sd);
+  }
+  CVM_NOUNROLL
+  for (int i = 0; i < n - 1; ++i) {
+    int j = i;
+    for (int k = i + 1; k < n; ++k)
+      if (W[j] < W[k]) j = k;
+    if (i != j) {
+      double t = W[i]; W[i] = W[j]; W[j] = t;
+      for (int k = 0; k < m; ++k) { t = At[i * m + k]; At[i * m + k] = At[j * m + k]; At[j * m + k] = t; }
+      if (want_v)
+        for (int k = 0; k < n; ++k) { t = Vt[i * n + k]; Vt[i * n + k] = Vt[j * n + k]; Vt[j * n + k] = t; }
+    }
+  }
+  Rng rng(0x12345678);
+  CVM_NOUNROLL
+  for (int i = 0; i < n; ++i) {
+    double sd = W[i];
+    CVM_NOUNROLL
+    for (int ii = 0; ii < 100 && sd <= kDblMin; ++ii) {
+      // zero singular value: random +-1/m vector, orthogonalised against the previous rows
+      const double val0 = 1. / m;
+      CVM_NOUNROLL
+      for (int k = 0; k < m; ++k) At[i * m + k] = (rng.next() & 256) != 0 ? val0 : -val0;
+      CVM_NOUNROLL
+      for (int it = 0; it < 2; ++it)
+        CVM_NOUNROLL
+        for (int j = 0; j < i; ++j) {
+          sd = 0;
+          CVM_NOUNROLL
+          for (int k = 0; k < m; ++k) sd += At[i * m + k] * At[j * m + k];
+          double asum = 0;
+          CVM_NOUNROLL
+          for (int k = 0; k < m; ++k) {
+            const double t = At[i * m + k] - sd * At[j * m + k];
+            At[i * m + k] = t;
+            asum += fabs(t);
+          }
+          asum = asum > eps * 100 ? 1 / asum : 0;
+          CVM_NOUNROLL
+          for (int k = 0; k < m; ++k) At[i * m + k] *= asum;
+        }
+      sd = 0;
+      CVM_NOUNROLL
+      for (int k = 0; k < m; ++k) {
+        const double t = At[i * m + k];
+        sd += t * t;
+      }
+      sd = sqrt(sd);
+    }
+    const double s = sd > kDblMin ? 1 / sd : 0.;
+    CVM_UNROLL
+    for (int k = 0; k < m; ++k) At[i * m + k] *= s;
+  }
+}
+
+template <int m, bool want_v>
+CVM_HD CVM_NOINLINE inline void jacobi_svd_rt(Heap At, Heap W, Heap Vt, const int n) {
+  const double eps = kDblEps * 10;
+  for (int i = 0; i < n; ++i) {
+    double sd = 0;
+    CVM_UNROLL
+    for (int k = 0; k < m; ++k) {
+      const double t = At[i * m + k];
+      sd += t * t;
+    }
+    W[i] = sd;
+    if (want_v) {
+      for (int k = 0; k < n; ++k) Vt[i * n + k] = 0;
+      Vt[i * n + i] = 1;
+    }
+  }
+  const int max_iter = m > 30 ? m : 30;
+  CVM_NOUNROLL
+  for (int iter = 0; iter < max_iter; ++iter) {
+    bool changed = false;
+#if defined(SEPB_K3_PROFILE) && defined(__CUDA_ARCH__)
+    if (m == 12 && (threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[6], 1ull);
+#endif
+    CVM_NOUNROLL
+    for (int i = 0; i < n - 1; ++i)
+      CVM_NOUNROLL
+      for (int j = i + 1; j < n; ++j) {
+        const Heap Ai = At.at(i * m), Aj = At.at(j * m);
+        double a = W[i], p = 0, b = W[j];
+        CVM_UNROLL
+        for (int k = 0; k < m; ++k) p += Ai[k] * Aj[k];
+        if (fabs(p) <= eps * sqrt(a * b)) continue;
+        p *= 2;
+        const double beta = a - b, gamma = cv_hypot(p, beta);
+        double c, s;
+        if (beta < 0) {
+          const double delta = (gamma - beta) * 0.5;
+          s = sqrt(delta / gamma);
+          c = p / (gamma * s * 2);
+        } else {
+          c = sqrt((gamma + beta) / (gamma * 2));
+          s = p / (gamma * c * 2);
+        }
+        a = b = 0;
+        CVM_UNROLL
+        for (int k = 0; k < m; ++k) {
+          const double x = Ai[k], y = Aj[k];
+          const double t0 = c * x + s * y;
+          const double t1 = -s * x + c * y;
+          Ai[k] = t0;
+          Aj[k] = t1;
+          a += t0 * t0;
+          b += t1 * t1;
+        }
+        W[i] = a;
+        W[j] = b;
+        changed = true;
+        if (want_v) {
+          const Heap Vi = Vt.at(i * n), Vj = Vt.at(j * n);
+          for (int k = 0; k < n; ++k) {
+            const double x = Vi[k], y = Vj[k];
+            Vi[k] = c * x + s * y;
+            Vj[k] = -s * x + c * y;
+          }
+        }
+      }
+    if (!changed) break;
+  }
+  jacobi_finish_rt<m, want_v>(At, W, Vt, n);
+}
+
+template <int m, int n, bool want_v>
+CVM_HD inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
+  if constexpr (m == 6 && want_v) {
+    jacobi_svd_rt<6, true>(At, W, Vt, n);   // 6 x {3, 4, 5, 6}: one shared body
+  } else {
+    jacobi_svd_fixed<m, n, want_v>(At, W, Vt);
+  }
 }
 
 #if defined(__CUDACC__)

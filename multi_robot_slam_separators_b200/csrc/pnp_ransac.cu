@@ -274,7 +274,7 @@ __device__ __forceinline__ void lm_step_warp(cvm::Heap h, const double* JtJ, con
 // work is alike (phase 0: chunk 0 of every pair), run the same code at about the same time, which is what the
 // instruction caches want -- ncu shows the GPC-level cache at 40-50 % of its request rate for this 330 KB kernel.
 template <int WPC>
-__global__ void __launch_bounds__(kWarp * WPC)
+__global__ void __launch_bounds__(kWarp * WPC, 5 / WPC)
 pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs,
                   const int32_t* __restrict__ n_matches, const uint16_t* __restrict__ match_from,
                   const uint16_t* __restrict__ match_to, const int32_t* __restrict__ n_unique_to,
