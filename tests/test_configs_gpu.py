@@ -91,3 +91,43 @@ def test_config5_sweep_batch_is_order_independent():
             assert np.array_equal(big[k][sel], small[k][rows[sel]], equal_nan=True), k
     finally:
         ctx.close()
+
+
+def test_more_correspondences_than_the_staging_area_holds():
+    """K3 stages a pair's correspondences in shared memory when they fit (1203 of them); beyond that it reads them from
+    global memory.  Two 2000-feature frames with the same descriptors give 2000 correspondences: inliers and pose must
+    still equal cv2.solvePnPRansac."""
+    import cv2
+    F = 2000
+    rng = np.random.default_rng(99)
+    desc = rng.integers(0, 256, (F, 32), dtype=np.uint8)
+    K = pnp.K_matrix(synth.FX, synth.FY, synth.CX, synth.CY)
+    pc = np.stack([rng.uniform(-8, 8, F), rng.uniform(-2, 2, F), rng.uniform(4, 40, F)], axis=1)     # camera frame
+    kp3d = (pc @ synth.R_LOCAL.T).astype(np.float32)                                                   # base frame
+    rv_true, tv_true = np.array([0.02, -0.05, 0.01]), np.array([0.3, -0.1, 0.5])
+    Rt, _ = cv2.Rodrigues(rv_true)
+    q = pc @ Rt.T + tv_true
+    uv = np.stack([q[:, 0] / q[:, 2] * synth.FX + synth.CX, q[:, 1] / q[:, 2] * synth.FY + synth.CY], axis=1)
+    uv += rng.normal(0, 0.4, uv.shape)
+    out = rng.random(F) < 0.35
+    uv[out] = np.stack([rng.uniform(0, 1241, out.sum()), rng.uniform(0, 376, out.sum())], axis=1)
+    kp2d = uv.astype(np.float32)
+    ctx = capi.Context(0)
+    try:
+        fr, to = capi.Frames(ctx, 1, F), capi.Frames(ctx, 1, F)
+        cnt = np.array([F], np.int32)
+        fr.upload(0, desc[None], np.zeros((1, F, 2), np.float32), kp3d[None], cnt)
+        to.upload(0, desc[None], kp2d[None], np.ones((1, F, 3), np.float32), cnt)
+        prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY)
+        res = capi.verify_pairs(ctx, fr, to, [[0, 0]], prm)
+        assert res["n_matches"][0] == F
+        pairs = matching.global_match(desc, desc, 0.8)
+        obj, img, fi, ti = matching.pnp_correspondences(pairs, kp3d, kp2d)
+        assert len(obj) == F
+        rv0, tv0 = np.array(prm.guess_rvec), np.array(prm.guess_tvec)
+        ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, K, rv0, tv0)
+        assert ok and res["status"][0] == 1
+        assert np.array_equal(capi.inlier_indices(res["inlier_mask"][0], F), inl)
+        assert np.abs(res["pose"][0, 3:] - tv).max() < TRANS_TOL and np.abs(res["pose"][0, :3] - rv).max() < ROT_TOL
+    finally:
+        ctx.close()
