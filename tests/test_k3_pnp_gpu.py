@@ -130,3 +130,25 @@ def test_two_phase_launch_identical(ctx, golden):
         for k in ("status", "n_matches", "n_inliers", "inlier_mask", "pose", "transform", "best_hyp", "iters_run", "covariance"):
             if k in one:
                 assert np.array_equal(one[k], two[k], equal_nan=True), (iters, k)
+
+
+def test_two_phase_launch_identical_in_the_second_call(ctx):
+    """The second call of estimate_transformation (guess = first result, only pairs whose first call succeeded) through
+    the two-phase launch: every output equals the single-launch run."""
+    A, B = synth.make_robots(2, 40, n_feat=1000, dim=128, seed=1003)
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    rng = np.random.default_rng(8)
+    same = [(a, b) for a in range(40) for b in range(40) if A.place[a] == B.place[b]]
+    pairs = same + [(int(rng.integers(40)), int(rng.integers(40))) for _ in range(30)]
+    prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY)
+    gprm = capi.guess_params(1241, 376, 20.0)
+    ctx.set_pnp_two_phase_min_pairs(1 << 30)
+    one = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gprm)
+    ctx.set_pnp_two_phase_min_pairs(0)
+    try:
+        two = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gprm)
+    finally:
+        ctx.set_pnp_two_phase_min_pairs(4 * 148)
+    assert int((one["status"] == 1).sum()) >= len(same) - 3
+    for k in one:
+        assert np.array_equal(one[k], two[k], equal_nan=True), k
