@@ -88,10 +88,13 @@ __device__ __forceinline__ bool row_filterable(float nq2, float maxnd2) {
 // ---- 1. split conversion ---------------------------------------------------------------------
 __global__ void netvlad_split_kernel(const double* __restrict__ src, int r0, int r1, int D, int Dp,
                                      __nv_bfloat16* __restrict__ dst, float* __restrict__ norm2,
-                                     float* __restrict__ maxnorm2) {
+                                     float* __restrict__ maxnorm2, float* __restrict__ row_thr = nullptr,
+                                     int32_t* __restrict__ zero_me = nullptr) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   const int r = r0 + warp;
+  if (zero_me && blockIdx.x == 0 && threadIdx.x == 0) *zero_me = 0;   // query pass: fallback-row counter
   if (r >= r1) return;
+  if (row_thr && lane == 0) row_thr[r] = __uint_as_float(0x7f7f7f7fu);   // query pass: 3.39e38, no threshold known yet
   const double* x = src + (size_t)r * D;
   __nv_bfloat16* o = dst + (size_t)r * 2 * Dp;
   double s = 0.0;
@@ -724,9 +727,9 @@ int sepb_netvlad_tensor_topk(sepb_ctx* ctx, const sepb_db* cdb, const double* d_
   float* q_norm2 = reinterpret_cast<float*>(s + o_qn);
   int32_t* fb_rows = reinterpret_cast<int32_t*>(s + o_fb);
   int32_t* fb_count = reinterpret_cast<int32_t*>(s + o_cnt);
-  SEPB_CUDA(ctx, cudaMemsetAsync(fb_count, 0, 4, ctx->stream));
-  SEPB_CUDA(ctx, cudaMemsetAsync(s + o_u, 0x7f, (size_t)nq * 4, ctx->stream));   // 3.39e38: no threshold known yet
-  netvlad_split_kernel<<<(nq + 7) / 8, 256, 0, ctx->stream>>>(d_q, 0, nq, D, Dp, q_split, q_norm2, nullptr);
+  // the query pass of the split kernel also resets the fallback counter and the shared row thresholds
+  netvlad_split_kernel<<<(nq + 7) / 8, 256, 0, ctx->stream>>>(d_q, 0, nq, D, Dp, q_split, q_norm2, nullptr,
+                                                             reinterpret_cast<float*>(s + o_u), fb_count);
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());
   CUtensorMap tmQ;
