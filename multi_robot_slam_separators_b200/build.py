@@ -21,7 +21,9 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 # SEPB_K3_DEFS: developer A/B switches for the K3 translation unit (e.g. "-DSEPB_JACOBI_ILP=0 -DSEPB_SCORE_ILP=2")
 EXTRA = {"guess_match.cu": ["-fmad=false"],
          "pnp_ransac.cu": ["-fmad=false"] + (["-DSEPB_K3_PROFILE"] if os.environ.get("SEPB_K3_PROFILE") else [])
-                          + os.environ.get("SEPB_K3_DEFS", "").split()}
+                          + os.environ.get("SEPB_K3_DEFS", "").split(),
+         # SEPB_K2T_DEFS: same for the tensor matcher (e.g. "-DSEPB_K2T_TRACE=1000": clock64 timeline of that pair's CTA)
+         "hamming_mma.cu": os.environ.get("SEPB_K2T_DEFS", "").split()}
 
 
 def nvcc() -> str:
@@ -40,7 +42,8 @@ def _stamp():
     for f in sorted(os.listdir(CSRC)) + ["../../include/sepb200.h", "../build.py"]:
         with open(os.path.join(CSRC, f), "rb") as fh:
             h.update(fh.read())
-    h.update((os.environ.get("SEPB_K3_PROFILE", "") + "|" + os.environ.get("SEPB_K3_DEFS", "")).encode())
+    h.update((os.environ.get("SEPB_K3_PROFILE", "") + "|" + os.environ.get("SEPB_K3_DEFS", "") + "|"
+              + os.environ.get("SEPB_K2T_DEFS", "")).encode())
     return h.hexdigest()
 
 

@@ -185,9 +185,12 @@ class Context:
 
     def measure_peak(self, kind: str, reps: int = 5) -> float:
         """'popc' -> POPC/s, 'dfma' -> FP64 FMA/s, 'tmem' / 'tmem_pack16' -> TMEM bytes/s read by tcgen05.ld
-        (measured microbenchmarks)."""
+        (measured microbenchmarks); 'mma_i8_n128' | 'mma_i8_n256' | 'mma_bf16_n256' | 'mma_i8_n128_sts' -> tensor-pipe
+        ops/s of a bare tcgen05.mma issue loop (M128, SWIZZLE_128B shared-memory operands; _sts: with producer-like
+        shared-memory stores running beside it)."""
         v = C.c_double()
-        self.check(lib().sepb_measure_peak(self._h, {"popc": 0, "dfma": 1, "tmem": 2, "tmem_pack16": 3}[kind], reps, C.byref(v)))
+        self.check(lib().sepb_measure_peak(self._h, {"popc": 0, "dfma": 1, "tmem": 2, "tmem_pack16": 3, "mma_i8_n128": 4, "mma_i8_n256": 5,
+                                                         "mma_bf16_n256": 6, "mma_i8_n128_sts": 7}[kind], reps, C.byref(v)))
         return v.value
 
     def set_match_kernel(self, which: str):

@@ -31,7 +31,7 @@ struct sepb_ctx {
   int32_t* k3_order = nullptr;
   size_t k3_order_cap = 0;
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
-  size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_guess_smem = 0;
+  size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_hamming_mma_smem_wide = 0, cfg_guess_smem = 0;
   int opt_match_kernel = SEPB_MATCH_AUTO;
   int opt_two_phase_min = -1;   // -1: 4 x sm_count
   int opt_nn_mode = -1;  // reserved

@@ -40,13 +40,33 @@ constexpr int kProdWarps = 4;
 constexpr int kProdThreads = kProdWarps * 32;
 constexpr int kThreadsT = (kEpiWarps + 1 + kProdWarps) * 32;  // 416
 constexpr int TM = 128;             // To rows per A tile (= TMEM lanes)
-constexpr int TN = 128;             // From rows per accumulator tile (= one TMEM stage)
-constexpr int kBStages = 3;         // From-row stages resident in shared memory
-constexpr int CH = kBStages * TN;   // From rows per resident chunk
-constexpr int kTStages = 4;         // TMEM accumulator stages of TN columns
-constexpr int kBBytes = CH * 256;   // main K-blocks of the resident chunk
+constexpr int kHalf = 128;          // columns one epilogue group drains; the column code of the index K-block is
+                                    // relative to this (242 > 127)
+// Geometry for an accumulator tile of TN From rows (= one TMEM stage).  TN = 256 halves the To-tile operand reads per
+// multiply-add (the tensor pipe of one SM is operand-fetch limited at M128 x N128: a bare issue loop measures
+// 2.79 POP/s per GPU for N = 128 against 3.43 for N = 256, tools/mma_peak.py) and both epilogue groups then drain one
+// half of every tile; TN = 128 (tiles alternate between the groups) needs 32 KB less shared memory and takes the
+// frames the wide geometry cannot hold.
+template <int TN_>
+struct Geo {
+  static_assert(TN_ == 128 || TN_ == 256, "accumulator tile width");
+  static constexpr int TN = TN_;
+  static constexpr int kGroupsPerTile = TN / kHalf;
+  static constexpr int kBStages = TN == 128 ? 3 : 2;  // From-row stages resident in shared memory
+  static constexpr int CH = kBStages * TN;            // From rows per resident chunk
+  static constexpr int kTStages = 512 / TN;           // TMEM accumulator stages of TN columns (all 512 columns)
+  static constexpr int kTShift = TN == 128 ? 2 : 1;
+  static constexpr int kBBytes = CH * 256;            // main K-blocks of the resident chunk
+  // index K-block, interleaved (no-swizzle) layout.  Only the first 16 of its 32 K bytes carry anything and the To
+  // side (A_x) is zero in the other 16, so the From side keeps ONE 8-row x 16-byte core matrix per 8 rows
+  // (LBO = SBO = 128: the "second" core matrix of a group is the first of the next one, whatever it holds is
+  // multiplied by zero; the last group's runs into A_x, which follows it in shared memory).
+  static constexpr int kBxBytes = CH * 16;
+  static constexpr size_t smem(int max_feat_to) {
+    return (size_t)kBBytes + 2 * (TM * 256) + kBxBytes + TM * 32 + (size_t)max_feat_to * 16 + 1024;
+  }
+};
 constexpr int kABytes = TM * 256;
-constexpr int kBxBytes = CH * 32;   // index K-block (interleaved layout)
 constexpr int kAxBytes = TM * 32;
 constexpr uint32_t kNoneKey = 0xFFFFFFFFu;
 
@@ -128,11 +148,30 @@ __device__ __forceinline__ void scan32(const uint32_t (&r)[16], uint32_t (&m1)[2
   }
 }
 
+// Developer timeline (-DSEPB_K2T_TRACE=<pair>): the CTA of that pair stamps clock64 at every pipeline hand-off.
+// Slots: 0 start, 1 setup done, 2 main loop done, 3 tail done; per accumulator tile g (< 64): 16+g MMA warp starts
+// waiting for the TMEM stage, 80+g MMAs issued, 144+g epilogue (lane quarter 0) starts waiting, 208+g accumulator
+// ready, 272+g stage released; per To tile `it` (< 32): 336 producer waits, 368 buffer free, 400 expanded;
+// 432 + 4 * chunk + j: From stage j expanded; 464 + it: MMA warp starts waiting for To tile `it`.  tools/k2t_trace.py prints it.
+#ifdef SEPB_K2T_TRACE
+__device__ long long g_k2t_trace[512];
+#define K2T_STAMP(cond, slot)                                              \
+  do {                                                                     \
+    if (blockIdx.x == (SEPB_K2T_TRACE) && (cond) && (slot) < 512) g_k2t_trace[(slot)] = clock64(); \
+  } while (0)
+#else
+#define K2T_STAMP(cond, slot) do { } while (0)
+#endif
+
+template <int TN>
 __global__ void __launch_bounds__(kThreadsT, 1)
 hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs, float nndr, int strict,
                    int32_t* __restrict__ knn_idx, int32_t* __restrict__ knn_dist, int32_t* __restrict__ n_matches,
                    uint16_t* __restrict__ match_from, uint16_t* __restrict__ match_to,
                    int32_t* __restrict__ n_unique_to) {
+  using G = Geo<TN>;
+  constexpr int kGroupsPerTile = G::kGroupsPerTile, kBStages = G::kBStages, CH = G::CH, kTStages = G::kTStages,
+                kTShift = G::kTShift, kBBytes = G::kBBytes, kBxBytes = G::kBxBytes;
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment by pointer arithmetic on the shared array (keeps the shared address space: LDS/STS, not LD.E)
   uint8_t* smem = smem_raw + ((1024u - (umma::smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -153,6 +192,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
 
   const int pair = blockIdx.x;
   if (pair >= n_pairs) return;
+  K2T_STAMP(threadIdx.x == 0, 0);
   const int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool valid_pair = fi >= 0 && fi < from.size && ti >= 0 && ti < to.size;
@@ -180,8 +220,8 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     reinterpret_cast<uint4*>(sBx)[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
   for (int r = tid; r < CH; r += kThreadsT) {
-    const int col = r & (TN - 1);
-    uint8_t* p = sBx + (r >> 3) * 256 + (r & 7) * 16;
+    const int col = r & (kHalf - 1);
+    uint8_t* p = sBx + (r >> 3) * 128 + (r & 7) * 16;
     p[0] = (uint8_t)(col >> 6);
     p[1] = (uint8_t)(col & 63);
   }
@@ -199,7 +239,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     }
     for (int s = 0; s < kTStages; ++s) {
       umma::mbar_init(&bar_t_full[s], 1);
-      umma::mbar_init(&bar_t_empty[s], 4);  // one arrive per epilogue warp of the group that drains the stage
+      umma::mbar_init(&bar_t_empty[s], 4 * kGroupsPerTile);  // one arrive per epilogue warp that drains the stage
     }
     umma::fence_mbar_init();
     s_dropped = 0;
@@ -210,6 +250,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   __syncthreads();
   umma::tc_fence_after();
   const uint32_t tmem = tmem_slot;
+  K2T_STAMP(tid == 0, 1);
   const int n_chunks = (nf + CH - 1) / CH, n_mt = (nt + TM - 1) / TM;
 
   if (warp >= kProdWarp0) {
@@ -222,26 +263,33 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
       const int rows_pad = (rows + 31) & ~31;  // the last tile is padded to 32 columns with "no neighbour" rows
       for (int m = 0; m < n_mt; ++m, ++it) {
         const int s = it & 1;
+        K2T_STAMP(p == 0 && it < 32, 336 + it);
         umma::mbar_wait(&bar_a_empty[s], (uint32_t)(((it >> 1) & 1) ^ 1));
+        K2T_STAMP(p == 0 && it < 32, 368 + it);
         const int row = m * TM + p;
         if (row < nt) expand_row(sA_a + (uint32_t)(s * kABytes), TM, p, g_query + 2 * (size_t)row);
         umma::fence_proxy_async();
         umma::mbar_arrive(&bar_a_full[s]);
+        K2T_STAMP(p == 0 && it < 32, 400 + it);
         if (m == 0) {
           // resident From stages of this chunk, each as soon as the previous chunk's last tile on it retired
           for (int j = 0; j * TN < rows; ++j) {
             umma::mbar_wait(&bar_b_empty[j], (uint32_t)((c & 1) ^ 1));
-            const int r = j * TN + p;
-            if (r < rows) {
-              expand_row(sB_a, CH, r, g_train + 2 * (size_t)(c * CH + r));
-            } else if (r < rows_pad) {
-              zero_row(sB_a, CH, r);
-              uint8_t* px = sBx + (r >> 3) * 256 + (r & 7) * 16;
-              px[2] = 127;
-              px[3] = 127;
+#pragma unroll
+            for (int h = 0; h < kGroupsPerTile; ++h) {
+              const int r = j * TN + h * kHalf + p;
+              if (r < rows) {
+                expand_row(sB_a, CH, r, g_train + 2 * (size_t)(c * CH + r));
+              } else if (r < rows_pad) {
+                zero_row(sB_a, CH, r);
+                uint8_t* px = sBx + (r >> 3) * 128 + (r & 7) * 16;
+                px[2] = 127;
+                px[3] = 127;
+              }
             }
             umma::fence_proxy_async();
             umma::mbar_arrive(&bar_b_full[j]);
+            K2T_STAMP(p == 0 && c < 4, 432 + 4 * c + j);
           }
         }
       }
@@ -253,6 +301,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     const uint32_t b_lo = ((umma::smem_u32(sB) & 0x3FFFFu) >> 4) | (1u << 16);
     const uint32_t sw_hi = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);         // SBO, version, SWIZZLE_128B
     const uint32_t il_hi = (uint32_t)(256 >> 4) | (1u << 14);                        // SBO, version, no swizzle
+    const uint32_t ilb_hi = (uint32_t)(128 >> 4) | (1u << 14);                       // From side: one core matrix per group
     const uint32_t ax_lo = ((umma::smem_u32(sAx) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
     const uint32_t bx_lo = ((umma::smem_u32(sBx) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
     auto desc = [](uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; };
@@ -262,6 +311,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
       const int rows = min(CH, nf - c * CH);
       for (int m = 0; m < n_mt; ++m, ++it) {
         const int s = it & 1;
+        K2T_STAMP(lane == 0 && it < 32, 464 + it);
         umma::mbar_wait(&bar_a_full[s], (uint32_t)((it >> 1) & 1));
         const uint32_t a_s = a_lo + (uint32_t)((s * kABytes) >> 4);
 #pragma unroll
@@ -270,7 +320,8 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
           if (ncols <= 0) break;
           if (m == 0) umma::mbar_wait(&bar_b_full[j], (uint32_t)(c & 1));
           const uint32_t st = g & (kTStages - 1);
-          umma::mbar_wait(&bar_t_empty[st], ((g >> 2) & 1) ^ 1);
+          K2T_STAMP(lane == 0 && g < 64, 16 + g);
+          umma::mbar_wait(&bar_t_empty[st], ((g >> kTShift) & 1) ^ 1);
           umma::tc_fence_after();
           if (umma::elect_one()) {
             const uint32_t idesc = umma::instr_desc(2, 1, 1, TM, (uint32_t)((ncols + 31) & ~31));
@@ -282,11 +333,12 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
                 umma::mma_i8(d, desc(a_s + (uint32_t)((kb * TM * 128 + k * 32) >> 4), sw_hi),
                              desc(b_lo + (uint32_t)((kb * CH * 128 + j * TN * 128 + k * 32) >> 4), sw_hi), idesc,
                              (kb | k) != 0);
-            umma::mma_i8(d, desc(ax_lo, il_hi), desc(bx_lo + (uint32_t)((j * TN * 32) >> 4), il_hi), idesc, true);
+            umma::mma_i8(d, desc(ax_lo, il_hi), desc(bx_lo + (uint32_t)((j * TN * 16) >> 4), ilb_hi), idesc, true);
             umma::mma_commit(&bar_t_full[st]);
             if (m == n_mt - 1) umma::mma_commit(&bar_b_empty[j]);  // last To tile against this From stage
           }
           __syncwarp();
+          K2T_STAMP(lane == 0 && g < 64, 80 + g);
           ++g;
         }
         if (umma::elect_one()) umma::mma_commit(&bar_a_empty[s]);
@@ -301,16 +353,20 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
       const int rows = min(CH, nf - c * CH);
       for (int m = 0; m < n_mt; ++m) {
         for (int j = 0; j * TN < rows; ++j, ++g) {
-          if ((int)(g & 1) != grp) continue;  // warp-uniform: the other group drains this tile
-          const int ncols = min(TN, rows - j * TN);
-          const int nch = (ncols + 31) >> 5;  // the producers padded the tile to nch * 32 columns
+          // warp-uniform: 128-column tiles alternate between the groups, 256-column tiles are split between them
+          if (kGroupsPerTile == 1 && (int)(g & 1) != grp) continue;
+          const int off = kGroupsPerTile == 1 ? 0 : grp * kHalf;
+          const int ncols = max(0, min(kHalf, rows - j * TN - off));
+          const int nch = (ncols + 31) >> 5;  // the producers padded the tile to a multiple of 32 columns
           const uint32_t st = g & (kTStages - 1);
-          const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + st * TN;
-          umma::mbar_wait(&bar_t_full[st], (g >> 2) & 1);
+          const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + st * TN + off;
+          K2T_STAMP(lq == 0 && lane == 0 && g < 64, 144 + g);
+          umma::mbar_wait(&bar_t_full[st], (g >> kTShift) & 1);
+          K2T_STAMP(lq == 0 && lane == 0 && g < 64, 208 + g);
           umma::tc_fence_after();
           uint32_t m1[2] = {kNone2, kNone2}, m2[2] = {kNone2, kNone2};
           uint32_t ra[16], rb[16];
-          umma::tmem_ld32_pack16(taddr, ra);
+          if (nch > 0) umma::tmem_ld32_pack16(taddr, ra);
           for (int ch = 0; ch < nch; ch += 2) {
             umma::tmem_ld_wait();
             if (ch + 1 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 1) * 32), rb);
@@ -324,6 +380,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
           umma::tc_fence_before();
           __syncwarp();
           if (lane == 0) umma::mbar_arrive(&bar_t_empty[st]);
+          K2T_STAMP(lq == 0 && lane == 0 && g < 64, 272 + g);
           merge2(m1[0], m2[0], m1[1], m2[1]);
           // unpack: even columns in the low halves, odd columns in the high halves
           int v1 = (int)(int16_t)(m1[0] & 0xFFFFu), v2 = (int)(int16_t)(m2[0] & 0xFFFFu);
@@ -337,7 +394,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
           if (row < nt) {
             uint32_t* slot = s_top + ((size_t)grp * to.max_feat + row) * 2;
             uint32_t k1 = slot[0], k2 = slot[1];
-            merge_min(k1, k2, acc_to_key(v1, c * CH + j * TN), acc_to_key(v2, c * CH + j * TN));
+            merge_min(k1, k2, acc_to_key(v1, c * CH + j * TN + off), acc_to_key(v2, c * CH + j * TN + off));
             slot[0] = k1;
             slot[1] = k2;
           }
@@ -349,6 +406,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   // ---- tail: NNDR, uniqueness, correspondence list (all warps) --------------------------------------
   umma::tc_fence_before();
   __syncthreads();
+  K2T_STAMP(tid == 0, 2);
   if (warp == kMmaWarp) {
     umma::tc_fence_after();
     umma::tmem_dealloc(tmem, 512);
@@ -374,19 +432,27 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   const float* p3 = from.kp3d + (size_t)fi * from.max_feat * 3;
   mtail::unique_and_compact<kThreadsT>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
                                        (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to, n_unique_to);
+  K2T_STAMP(tid == 0, 3);
 }
 
 }  // namespace
 
-size_t sepb_hamming_mma_smem(int max_feat_to) {
-  return (size_t)kBBytes + 2 * kABytes + kBxBytes + kAxBytes + (size_t)max_feat_to * 16 + 1024;
+#ifdef SEPB_K2T_TRACE
+// developer build only (not in include/sepb200.h): copy the timeline out
+extern "C" __attribute__((visibility("default"))) int sepb_debug_k2t_trace(long long* out, int n) {
+  if (n > 512) n = 512;
+  return (int)cudaMemcpyFromSymbol(out, g_k2t_trace, (size_t)n * sizeof(long long));
+}
+#endif
+
+// shared-memory budget of one CTA decides the geometry: wide tiles when the To frames are short enough
+template <int TN>
+static bool geo_fits(const FramesView& from, const FramesView& to) {
+  const size_t tail = (size_t)to.max_feat * 4 + (size_t)from.max_feat * 6;
+  return Geo<TN>::smem(to.max_feat) + 256 <= 232448 && tail <= (size_t)Geo<TN>::kBBytes && from.max_feat <= 65535;
 }
 
-// largest To-frame feature count the tensor kernel supports (shared-memory budget of one CTA)
-bool sepb_hamming_mma_supported(const FramesView& from, const FramesView& to) {
-  const size_t tail = (size_t)to.max_feat * 4 + (size_t)from.max_feat * 6;
-  return sepb_hamming_mma_smem(to.max_feat) + 256 <= 232448 && tail <= (size_t)kBBytes && from.max_feat <= 65535;
-}
+bool sepb_hamming_mma_supported(const FramesView& from, const FramesView& to) { return geo_fits<128>(from, to); }
 
 int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                             float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
@@ -394,14 +460,23 @@ int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const
   if (n_pairs == 0) return SEPB_OK;
   if (!sepb_hamming_mma_supported(from, to))
     return sepb_fail(ctx, SEPB_E_SHAPE, "hamming_mma: frame too large for the tensor kernel", __FILE__, __LINE__);
-  const size_t smem = sepb_hamming_mma_smem(to.max_feat);
-  if (smem > ctx->cfg_hamming_mma_smem) {
-    SEPB_CUDA(ctx, cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ctx->cfg_hamming_mma_smem = smem;
+  bool wide = geo_fits<256>(from, to);
+  if (const char* e = getenv("SEPB_K2T_TN")) wide = wide && atoi(e) == 256;  // developer A/B
+  const size_t smem = wide ? Geo<256>::smem(to.max_feat) : Geo<128>::smem(to.max_feat);
+  size_t& cfg = wide ? ctx->cfg_hamming_mma_smem_wide : ctx->cfg_hamming_mma_smem;
+  if (smem > cfg) {
+    SEPB_CUDA(ctx, wide ? cudaFuncSetAttribute(hamming_mma_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                        : cudaFuncSetAttribute(hamming_mma_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cfg = smem;
   }
-  hamming_mma_kernel<<<n_pairs, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
-                                                               d_knn_dist, d_n_matches, d_match_from, d_match_to,
-                                                               d_n_unique_to);
+  if (wide)
+    hamming_mma_kernel<256><<<n_pairs, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
+                                                                      d_knn_dist, d_n_matches, d_match_from, d_match_to,
+                                                                      d_n_unique_to);
+  else
+    hamming_mma_kernel<128><<<n_pairs, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
+                                                                      d_knn_dist, d_n_matches, d_match_from, d_match_to,
+                                                                      d_n_unique_to);
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());
   return SEPB_OK;

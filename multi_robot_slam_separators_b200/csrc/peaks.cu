@@ -65,17 +65,82 @@ __global__ void __launch_bounds__(256, 1) tmem_read_peak_kernel(uint32_t* out, i
   }
 }
 
+// Tensor-pipe issue rate of the MMA shapes the matchers use: one CTA per SM, one elected thread issues `tiles`
+// accumulator tiles of 8 K-steps each (SWIZZLE_128B operands, 2 K-blocks of 128 B like K2T / K1) round-robin over
+// the TMEM stages, nothing drains them.  mode 0: kind::i8 M128 N128 K32; 1: kind::i8 M128 N256 K32;
+// 2: kind::f16 (bf16) M128 N256 K16; 3: mode 0 while four more warps store into shared memory the way K2T's
+// producers do (operand-fetch contention).  Operand content is whatever shared memory holds: only the rate matters.
+__global__ void __launch_bounds__(160, 1) mma_peak_kernel(uint32_t* out, int tiles, int mode) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (umma::smem_u32(smem_raw) & 1023u)) & 1023u);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  __shared__ volatile int done;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int N = (mode == 1 || mode == 2) ? 256 : 128;
+  const uint32_t sA = umma::smem_u32(smem), sB = sA + 2 * 128 * 128, sScratch = sB + 2 * 256 * 128;
+  if (threadIdx.x == 0) {
+    umma::mbar_init(&bar, 1);
+    umma::fence_mbar_init();
+    done = 0;
+  }
+  if (warp == 0) umma::tmem_alloc(&slot, 512);
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tmem = slot;
+  if (warp == 0) {
+    if (umma::elect_one()) {
+      const uint32_t idesc = mode == 2 ? umma::instr_desc(1, 1, 1, 128, 256) : umma::instr_desc(2, 1, 1, 128, (uint32_t)N);
+      for (int t = 0; t < tiles; ++t) {
+        const uint32_t d = tmem + (uint32_t)((t * N) & 511);
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t a = umma::smem_desc_sw128(sA + (uint32_t)(kb * 128 * 128 + k * 32));
+            const uint64_t b = umma::smem_desc_sw128(sB + (uint32_t)(kb * N * 128 + k * 32));
+            if (mode == 2) umma::mma_f16(d, a, b, idesc, (kb | k) != 0);
+            else umma::mma_i8(d, a, b, idesc, (kb | k) != 0);
+          }
+      }
+      umma::mma_commit(&bar);
+    }
+    __syncwarp();
+    umma::mbar_wait(&bar, 0);
+    done = 1;
+  } else if (mode == 3) {
+    uint32_t i = 0;
+    while (!done) {  // 128 threads x 16 B, rows of 128 B: the store pattern of expand_row
+      umma::sts128(sScratch + (uint32_t)(((threadIdx.x - 32) * 128 + (i & 7) * 16)), i, i, i, i);
+      ++i;
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = i;
+  }
+  (void)lane;
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    umma::tc_fence_after();
+    umma::tmem_dealloc(tmem, 512);
+  }
+}
+
 }  // namespace
 
 extern "C" {
 
 // kind 0: POPC ops/s; kind 1: FP64 FMA/s (one FMA = 2 FLOP); kind 2 / 3: TMEM bytes/s read by tcgen05.ld (32-bit cells,
-// plain / .pack::16b).  Best of `reps` launches.
+// plain / .pack::16b); kind 4..7: tensor-pipe ops/s (2 per multiply-add) of mma_peak_kernel modes 0..3.
+// Best of `reps` launches.
 int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s) {
   if (!ctx || !ops_per_s) return SEPB_E_INVALID;
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
-  const bool tm = kind == 2 || kind == 3;
-  const int blocks = tm ? ctx->sm_count : ctx->sm_count * 8, threads = 256, iters = kind == 0 ? 4096 : tm ? 512 : 2048;
+  const bool tm = kind == 2 || kind == 3, mm = kind >= 4 && kind <= 7;
+  const int mma_tiles = 4096;
+  const size_t mma_smem = 2 * 128 * 128 + 2 * 256 * 128 + 128 * 128 + 1024;
+  if (mm) SEPB_CUDA(ctx, cudaFuncSetAttribute(mma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mma_smem));
+  const int blocks = (tm || mm) ? ctx->sm_count : ctx->sm_count * 8, threads = 256, iters = kind == 0 ? 4096 : tm ? 512 : 2048;
   void* buf = sepb_scratch(ctx, (size_t)blocks * threads * 8);
   if (!buf) return (int)cudaErrorMemoryAllocation;
   cudaEvent_t e0, e1;
@@ -86,6 +151,7 @@ int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s) {
     SEPB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     if (kind == 0) popc_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((uint32_t*)buf, iters, 12345u + r);
     else if (kind == 1) dfma_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((double*)buf, iters, 1.0 + r);
+    else if (mm) mma_peak_kernel<<<blocks, 160, mma_smem, ctx->stream>>>((uint32_t*)buf, mma_tiles, kind - 4);
     else tmem_read_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((uint32_t*)buf, iters, kind == 3);
     ctx->launches++;
     SEPB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
@@ -93,7 +159,8 @@ int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s) {
     float ms = 0;
     SEPB_CUDA(ctx, cudaEventElapsedTime(&ms, e0, e1));
     // TMEM: every warp reads 32 lanes x 512 columns x 4 B per sweep (the packed form returns half the registers)
-    const double ops = tm ? (double)blocks * 8 * iters * (32.0 * 512 * 4) / (ms * 1e-3)
+    const double mma_k = kind == 6 ? 16.0 : 32.0, mma_n = (kind == 5 || kind == 6) ? 256.0 : 128.0;
+    const double ops = mm ? (double)blocks * mma_tiles * 8 * (2.0 * 128 * mma_n * mma_k) / (ms * 1e-3) : tm ? (double)blocks * 8 * iters * (32.0 * 512 * 4) / (ms * 1e-3)
                           : (double)blocks * threads * iters * 8.0 / (ms * 1e-3);
     if (r > 0 && ops > best) best = ops;
   }
