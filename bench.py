@@ -379,6 +379,14 @@ def run_ours(args):
                                "peak_source": peak_src, "note": "POPC-issue bound, not HBM bound",
                                "int_pipe": {"achieved": k2_popc, "peak": popc_peak, "unit": "popc32/s", "frac": k2_popc / popc_peak,
                                             "peak_source": "sepb_measure_peak microbenchmark, same run"}}
+        if match_kernel == "tensor":
+            # what one SM's tensor pipe sustains for K2T's instruction shape (cta_group::1, M128 x N256 x K32 int8, both
+            # operands in shared memory): a bare tcgen05.mma issue loop, measured in the same run.  K2T issues 9 K-steps
+            # per tile (8 descriptor + 1 train-index step) for 8 K-steps of algorithmic work.
+            issue_peak = eng.ctx.measure_peak("mma_i8_n256") / 1e12
+            rooflines["K2"]["tensor_issue"] = {"peak_tops": issue_peak, "achieved_tops_issued": k2_tops * 9.0 / 8.0,
+                                               "frac_issued": k2_tops * 9.0 / 8.0 / issue_peak, "frac_algorithmic": k2_tops / issue_peak,
+                                               "peak_source": "sepb_measure_peak mma_i8_n256 microbenchmark, same run"}
         if "tmem_read" in rooflines["K2"]:
             tr = rooflines["K2"]["tmem_read"]
             tr["frac"] = tr["achieved_tbs"] / tr["peak_tbs"]

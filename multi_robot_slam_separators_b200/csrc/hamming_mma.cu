@@ -365,22 +365,22 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
           K2T_STAMP(lq == 0 && lane == 0 && g < 64, 208 + g);
           umma::tc_fence_after();
           uint32_t m1[2] = {kNone2, kNone2}, m2[2] = {kNone2, kNone2};
-          uint32_t ra[16], rb[16];
-          if (nch > 0) umma::tmem_ld32_pack16(taddr, ra);
-          for (int ch = 0; ch < nch; ch += 2) {
-            umma::tmem_ld_wait();
-            if (ch + 1 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 1) * 32), rb);
-            scan32(ra, m1, m2);
-            if (ch + 1 < nch) {
-              umma::tmem_ld_wait();
-              if (ch + 2 < nch) umma::tmem_ld32_pack16(taddr + (uint32_t)((ch + 2) * 32), ra);
-              scan32(rb, m1, m2);
-            }
-          }
+          // the group's whole half tile goes to registers at once (one TMEM round trip instead of four) and the
+          // stage returns to the MMA warp before the scan, not after it
+          uint32_t r0[16], r1[16], r2[16], r3[16];
+          if (nch > 0) umma::tmem_ld32_pack16(taddr, r0);
+          if (nch > 1) umma::tmem_ld32_pack16(taddr + 32u, r1);
+          if (nch > 2) umma::tmem_ld32_pack16(taddr + 64u, r2);
+          if (nch > 3) umma::tmem_ld32_pack16(taddr + 96u, r3);
+          umma::tmem_ld_wait();
           umma::tc_fence_before();
           __syncwarp();
           if (lane == 0) umma::mbar_arrive(&bar_t_empty[st]);
           K2T_STAMP(lq == 0 && lane == 0 && g < 64, 272 + g);
+          if (nch > 0) scan32(r0, m1, m2);
+          if (nch > 1) scan32(r1, m1, m2);
+          if (nch > 2) scan32(r2, m1, m2);
+          if (nch > 3) scan32(r3, m1, m2);
           merge2(m1[0], m2[0], m1[1], m2[1]);
           // unpack: even columns in the low halves, odd columns in the high halves
           int v1 = (int)(int16_t)(m1[0] & 0xFFFFu), v2 = (int)(int16_t)(m2[0] & 0xFFFFu);

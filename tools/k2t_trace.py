@@ -36,14 +36,15 @@ t = np.array(tr[:], dtype=np.int64)
 t0 = t[0]
 rel = lambda a: (np.asarray(a) - t0).astype(np.int64)
 print("setup done %d, main loop done %d, tail done %d (clocks from CTA start)" % tuple(rel(t[1:4])))
-G = 64
+wide = os.environ.get("SEPB_K2T_TN", "256") == "256"      # geometry the launch picks for 1000-feature frames
+G = 32 if wide else 64
 mw, mi, ew, er, ed = (rel(t[16:16 + G]), rel(t[80:80 + G]), rel(t[144:144 + G]), rel(t[208:208 + G]),
                       rel(t[272:272 + G]))
 print("  g  mma_wait mma_issued  epi_wait acc_ready released | issue-wait ready-issued drain")
 for g in range(G):
     print("%3d %9d %10d %9d %9d %8d | %10d %12d %5d" % (g, mw[g], mi[g], ew[g], er[g], ed[g], mi[g] - mw[g],
                                                         er[g] - mi[g], ed[g] - er[g]))
-n_it = 24
+n_it = 16 if wide else 24
 pw, pf, pd, aw = rel(t[336:336 + n_it]), rel(t[368:368 + n_it]), rel(t[400:400 + n_it]), rel(t[464:464 + n_it])
 print(" it prod_wait buf_free expanded mma_waits_A | wait expand  mma_stall_on_A")
 for i in range(n_it):
@@ -51,7 +52,7 @@ for i in range(n_it):
                                                  max(0, pd[i] - aw[i])))
 print("From stages expanded (chunk, j):", {(c, j): int(rel(t[432 + 4 * c + j])) for c in range(3) for j in range(3)
                                            if t[432 + 4 * c + j]})
-steady = slice(8, 56)
+steady = slice(4, G - 4)
 summary = {
     "main_loop_clocks": int(rel(t[2]) - rel(t[1])), "setup_clocks": int(rel(t[1])), "tail_clocks": int(t[3] - t[2]),
     "per_tile_clocks": float((rel(t[2]) - rel(t[1])) / G),
