@@ -17,14 +17,17 @@
 //   no key building, no masking, and everything stays exact.
 //
 // One CTA per keyframe pair, warp-specialised:
-//   warps 0-7   epilogue: TMEM -> registers (tcgen05.ld), running top-2 per To row; two groups of four
-//               warps (TMEM lane quarter = warp & 3) take the accumulator tiles alternately
+//   warps 0-7   epilogue: TMEM -> registers (tcgen05.ld, a whole 128-column half tile per round trip; the stage goes
+//               back to the MMA warp before the scan), running top-2 per To row; two groups of four warps (TMEM
+//               lane quarter = warp & 3): each drains one half of every 256-column tile (128-column geometry: the
+//               tiles alternate between the groups)
 //   warp  8     MMA issuer (one elected lane): per (To tile, From tile) 8 SWIZZLE_128B K-steps + 1 index K-step
-//               of M=128 x N=128 into one of FOUR 128-column TMEM stages (all 512 columns)
+//               of M=128 x N=256 into one of TWO 256-column TMEM stages (N=128: four stages; all 512 columns)
 //   warps 9-12  producers: expand descriptor bits into the +-11 operand tiles in shared memory (PRMT lookups)
-// A resident chunk of 384 From rows (three 128-row stages, each with its own full/empty barrier so the next
-// chunk is expanded while the last To tiles still run) is expanded once per chunk; the 128-row To tiles
-// stream through a 2-deep ring against it.
+// A resident chunk of 512 From rows (two 256-row stages, each with its own full/empty barrier so the next
+// chunk is expanded while the last To tiles still run; N=128: three 128-row stages) is expanded once per chunk; the
+// 128-row To tiles stream through a 2-deep ring against it.  struct Geo holds both geometries; the launch takes the
+// wide one whenever its shared memory fits (To frames up to ~1400 features).
 #include <limits.h>
 
 #include "common.cuh"
