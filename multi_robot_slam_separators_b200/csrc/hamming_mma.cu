@@ -81,8 +81,7 @@ constexpr uint32_t kNone2 = 0x80008000u;
 // expand one 256-bit descriptor into 256 int8 (+11 / -11) at row r of a SWIZZLE_128B tile of `rows` rows
 // (shared-memory address `tile`).  Any fixed permutation of the 256 bit positions along K is fine as long
 // as both operands use the same one; the one used here costs 13 instructions per 32 bits.
-__device__ __forceinline__ void expand_row(uint32_t tile, int rows, int r, const uint4* __restrict__ g) {
-  const uint4 a = __ldg(g), b = __ldg(g + 1);
+__device__ __forceinline__ void expand_row(uint32_t tile, int rows, int r, const uint4 a, const uint4 b) {
   const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
   // byte lookups through PRMT: a selector nibble v (3 bits of the descriptor) picks byte v of an 8-byte table
   // holding +11 where the wanted bit of v is 0 and -11 (0xF5) where it is 1
@@ -217,6 +216,26 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     return;
   }
 
+  // producers: the rows of the first To tile and of the first From chunk are requested before the setup, so their L2
+  // latency hides behind it and the first MMA does not wait for three dependent round trips
+  constexpr int kRowsB = CH / kHalf;  // From rows of a chunk per producer thread
+  uint4 pre_a[2], pre_b[kRowsB][2];
+  if (warp >= kProdWarp0) {
+    const int p = tid - kProdWarp0 * 32;
+    if (p < nt) {
+      pre_a[0] = __ldg(g_query + 2 * (size_t)p);
+      pre_a[1] = __ldg(g_query + 2 * (size_t)p + 1);
+    }
+#pragma unroll
+    for (int i = 0; i < kRowsB; ++i) {
+      const int r = i * kHalf + p;
+      if (r < nf) {
+        pre_b[i][0] = __ldg(g_train + 2 * (size_t)r);
+        pre_b[i][1] = __ldg(g_train + 2 * (size_t)r + 1);
+      }
+    }
+  }
+
   // ---- setup -----------------------------------------------------------------------------------
   for (int i = tid; i < 4 * to.max_feat; i += kThreadsT) s_top[i] = kNoneKey;
   for (int i = tid; i < (kBxBytes + kAxBytes) / 16; i += kThreadsT)
@@ -267,22 +286,45 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
       for (int m = 0; m < n_mt; ++m, ++it) {
         const int s = it & 1;
         K2T_STAMP(p == 0 && it < 32, 336 + it);
+        // every row is requested before the wait for its buffer (the first ones before the setup)
+        const int row = m * TM + p;
+        uint4 qa, qb;
+        if (it == 0) {
+          qa = pre_a[0];
+          qb = pre_a[1];
+        } else if (row < nt) {
+          qa = __ldg(g_query + 2 * (size_t)row);
+          qb = __ldg(g_query + 2 * (size_t)row + 1);
+        }
         umma::mbar_wait(&bar_a_empty[s], (uint32_t)(((it >> 1) & 1) ^ 1));
         K2T_STAMP(p == 0 && it < 32, 368 + it);
-        const int row = m * TM + p;
-        if (row < nt) expand_row(sA_a + (uint32_t)(s * kABytes), TM, p, g_query + 2 * (size_t)row);
+        if (row < nt) expand_row(sA_a + (uint32_t)(s * kABytes), TM, p, qa, qb);
         umma::fence_proxy_async();
         umma::mbar_arrive(&bar_a_full[s]);
         K2T_STAMP(p == 0 && it < 32, 400 + it);
         if (m == 0) {
           // resident From stages of this chunk, each as soon as the previous chunk's last tile on it retired
-          for (int j = 0; j * TN < rows; ++j) {
+#pragma unroll
+          for (int j = 0; j < kBStages; ++j) {
+            if (j * TN >= rows) break;
+            uint4 ta[kGroupsPerTile], tb[kGroupsPerTile];
+#pragma unroll
+            for (int h = 0; h < kGroupsPerTile; ++h) {
+              const int r = j * TN + h * kHalf + p;
+              if (c == 0) {
+                ta[h] = pre_b[j * kGroupsPerTile + h][0];
+                tb[h] = pre_b[j * kGroupsPerTile + h][1];
+              } else if (r < rows) {
+                ta[h] = __ldg(g_train + 2 * (size_t)(c * CH + r));
+                tb[h] = __ldg(g_train + 2 * (size_t)(c * CH + r) + 1);
+              }
+            }
             umma::mbar_wait(&bar_b_empty[j], (uint32_t)((c & 1) ^ 1));
 #pragma unroll
             for (int h = 0; h < kGroupsPerTile; ++h) {
               const int r = j * TN + h * kHalf + p;
               if (r < rows) {
-                expand_row(sB_a, CH, r, g_train + 2 * (size_t)(c * CH + r));
+                expand_row(sB_a, CH, r, ta[h], tb[h]);
               } else if (r < rows_pad) {
                 zero_row(sB_a, CH, r);
                 uint8_t* px = sBx + (r >> 3) * 128 + (r & 7) * 16;
