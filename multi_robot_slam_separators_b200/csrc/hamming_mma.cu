@@ -203,6 +203,26 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   const uint4* g_train = reinterpret_cast<const uint4*>(from.desc + (size_t)(valid_pair ? fi : 0) * from.max_feat * 32);
   const uint4* g_query = reinterpret_cast<const uint4*>(to.desc + (size_t)(valid_pair ? ti : 0) * to.max_feat * 32);
 
+  // producers: the rows of the first To tile and of the first From chunk are requested before the setup (and
+  // before the feature counts arrive: any row below max_feat is readable), so their L2 latency hides behind it
+  constexpr int kRowsB = CH / kHalf;  // From rows of a chunk per producer thread
+  uint4 pre_a[2], pre_b[kRowsB][2];
+  if (warp >= kProdWarp0) {
+    const int p = tid - kProdWarp0 * 32;
+    if (p < to.max_feat) {
+      pre_a[0] = __ldg(g_query + 2 * (size_t)p);
+      pre_a[1] = __ldg(g_query + 2 * (size_t)p + 1);
+    }
+#pragma unroll
+    for (int i = 0; i < kRowsB; ++i) {
+      const int r = i * kHalf + p;
+      if (r < from.max_feat) {
+        pre_b[i][0] = __ldg(g_train + 2 * (size_t)r);
+        pre_b[i][1] = __ldg(g_train + 2 * (size_t)r + 1);
+      }
+    }
+  }
+
   if (nt == 0 || nf == 0) {  // block-uniform: nothing to multiply
     for (int qi = tid; qi < nt; qi += kThreadsT) {
       const size_t o = ((size_t)pair * to.max_feat + qi) * 2;
@@ -214,26 +234,6 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
       if (n_unique_to) n_unique_to[pair] = nt;
     }
     return;
-  }
-
-  // producers: the rows of the first To tile and of the first From chunk are requested before the setup, so their L2
-  // latency hides behind it and the first MMA does not wait for three dependent round trips
-  constexpr int kRowsB = CH / kHalf;  // From rows of a chunk per producer thread
-  uint4 pre_a[2], pre_b[kRowsB][2];
-  if (warp >= kProdWarp0) {
-    const int p = tid - kProdWarp0 * 32;
-    if (p < nt) {
-      pre_a[0] = __ldg(g_query + 2 * (size_t)p);
-      pre_a[1] = __ldg(g_query + 2 * (size_t)p + 1);
-    }
-#pragma unroll
-    for (int i = 0; i < kRowsB; ++i) {
-      const int r = i * kHalf + p;
-      if (r < nf) {
-        pre_b[i][0] = __ldg(g_train + 2 * (size_t)r);
-        pre_b[i][1] = __ldg(g_train + 2 * (size_t)r + 1);
-      }
-    }
   }
 
   // ---- setup -----------------------------------------------------------------------------------
@@ -457,6 +457,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     umma::tmem_dealloc(tmem, 512);
   }
   for (int i = tid; i < nf; i += kThreadsT) s_count[i] = 0;
+  int any_assigned = 0;
   for (int qi = tid; qi < nt; qi += kThreadsT) {
     uint32_t k1 = s_top[(size_t)qi * 2], k2 = s_top[(size_t)qi * 2 + 1];
     merge_min(k1, k2, s_top[((size_t)to.max_feat + qi) * 2], s_top[((size_t)to.max_feat + qi) * 2 + 1]);
@@ -471,9 +472,18 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
       knn_dist[o] = d1;
       knn_dist[o + 1] = d2;
     }
-    s_assigned[qi] = mtail::nndr_assign(i1, d1, i2, d2, nndr, strict);
+    const int as = mtail::nndr_assign(i1, d1, i2, d2, nndr, strict);
+    s_assigned[qi] = as;
+    any_assigned |= as >= 0;
   }
-  __syncthreads();
+  if (!__syncthreads_or(any_assigned)) {  // no To row passed the ratio test (most non-matching pairs): empty list
+    if (tid == 0) {
+      n_matches[pair] = 0;
+      if (n_unique_to) n_unique_to[pair] = nt;
+    }
+    K2T_STAMP(tid == 0, 3);
+    return;
+  }
   const float* p3 = from.kp3d + (size_t)fi * from.max_feat * 3;
   mtail::unique_and_compact<kThreadsT>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
                                        (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to, n_unique_to);
