@@ -223,19 +223,6 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     }
   }
 
-  if (nt == 0 || nf == 0) {  // block-uniform: nothing to multiply
-    for (int qi = tid; qi < nt; qi += kThreadsT) {
-      const size_t o = ((size_t)pair * to.max_feat + qi) * 2;
-      if (knn_idx) knn_idx[o] = knn_idx[o + 1] = -1;
-      if (knn_dist) knn_dist[o] = knn_dist[o + 1] = -1;
-    }
-    if (tid == 0) {
-      n_matches[pair] = 0;
-      if (n_unique_to) n_unique_to[pair] = nt;
-    }
-    return;
-  }
-
   // ---- setup -----------------------------------------------------------------------------------
   for (int i = tid; i < 4 * to.max_feat; i += kThreadsT) s_top[i] = kNoneKey;
   for (int i = tid; i < (kBxBytes + kAxBytes) / 16; i += kThreadsT)
@@ -273,6 +260,20 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   umma::tc_fence_after();
   const uint32_t tmem = tmem_slot;
   K2T_STAMP(tid == 0, 1);
+  if (nt == 0 || nf == 0) {  // block-uniform: nothing to multiply (checked after the setup, which does not need the
+                             // feature counts and so overlaps the pairs -> counts round trips)
+    for (int qi = tid; qi < nt; qi += kThreadsT) {
+      const size_t o = ((size_t)pair * to.max_feat + qi) * 2;
+      if (knn_idx) knn_idx[o] = knn_idx[o + 1] = -1;
+      if (knn_dist) knn_dist[o] = knn_dist[o + 1] = -1;
+    }
+    if (tid == 0) {
+      n_matches[pair] = 0;
+      if (n_unique_to) n_unique_to[pair] = nt;
+    }
+    if (warp == kMmaWarp) umma::tmem_dealloc(tmem, 512);  // nothing was issued against it
+    return;
+  }
   const int n_chunks = (nf + CH - 1) / CH, n_mt = (nt + TM - 1) / TM;
 
   if (warp >= kProdWarp0) {
