@@ -123,15 +123,24 @@ def test_tensor_kernel_equals_popc_kernel_full_size():
     rng = np.random.default_rng(11)
     pairs = rng.integers(0, 48, (256, 2)).astype(np.int32)
     outs = []
-    for which in ("popc", "tensor"):
+    # the tensor kernel in both accumulator-tile geometries (the launch takes the 256-column one for these frames;
+    # SEPB_K2T_TN=128 is the developer switch that forces the geometry used for longer To frames)
+    import os
+    for which, tn in (("popc", None), ("tensor", None), ("tensor", "128")):
         c = capi.Context(0)
         c.set_match_kernel(which)
         fa, fb = capi.frames_from_robot(c, A), capi.frames_from_robot(c, B)
-        outs.append(capi.match_pairs(c, fa, fb, pairs, nndr=0.8))
+        if tn:
+            os.environ["SEPB_K2T_TN"] = tn
+        try:
+            outs.append(capi.match_pairs(c, fa, fb, pairs, nndr=0.8))
+        finally:
+            os.environ.pop("SEPB_K2T_TN", None)
         fa.close(); fb.close(); c.close()
-    for k in ("knn_idx", "knn_dist", "n_matches", "n_unique_to"):
-        assert np.array_equal(outs[0][k], outs[1][k]), k
-    for p in range(len(pairs)):
-        m = outs[0]["n_matches"][p]
-        assert np.array_equal(outs[0]["match_from"][p, :m], outs[1]["match_from"][p, :m])
-        assert np.array_equal(outs[0]["match_to"][p, :m], outs[1]["match_to"][p, :m])
+    for other in outs[1:]:
+        for k in ("knn_idx", "knn_dist", "n_matches", "n_unique_to"):
+            assert np.array_equal(outs[0][k], other[k]), k
+        for p in range(len(pairs)):
+            m = outs[0]["n_matches"][p]
+            assert np.array_equal(outs[0]["match_from"][p, :m], other["match_from"][p, :m])
+            assert np.array_equal(outs[0]["match_to"][p, :m], other["match_to"][p, :m])
