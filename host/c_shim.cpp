@@ -72,6 +72,8 @@ void sh_pr_add_keyframe(void* p, const double* netvlad, int n_values, const uint
   fill(d, k, k3, desc, n, kp2, oct, kp3);
   static_cast<PlaceRecognition*>(p)->addKeyframe(std::vector<double>(netvlad, netvlad + n_values), d, k3, k, (int16_t)kf_id);
 }
+int sh_pr_dropped_int16(void* p) { return static_cast<PlaceRecognition*>(p)->droppedForInt16(); }
+const char* sh_pr_last_error(void* p) { return static_cast<PlaceRecognition*>(p)->lastError().c_str(); }
 
 // returns the number of matches; ids into the three int16 arrays (capacity max_out); feature rows of the first match
 int sh_pr_find_matches_compute(void* p, const double* new_desc, int n_values, int16_t* kf_ids, int16_t* local_ids,

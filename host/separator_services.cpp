@@ -138,14 +138,21 @@ PlaceRecognition::PlaceRecognition(Device& dev, int dim, double distance, int ma
 PlaceRecognition::~PlaceRecognition() { sepb_db_destroy(db_); }
 int PlaceRecognition::receivedCount() const { return sepb_db_size(db_); }
 
-void PlaceRecognition::addKeyframe(const std::vector<double>& netvlad, const msgs::Descriptors& d,
+static constexpr int kInt16Max = 32767;   // int16[] ids of FindMatches.srv:3-5, ReceiveSeparators.srv:3-6
+
+bool PlaceRecognition::addKeyframe(const std::vector<double>& netvlad, const msgs::Descriptors& d,
                                    const msgs::KeyPoint3DVec& k3, const msgs::KeyPointVec& k, int16_t kf_id) {
+  if (localCount() > kInt16Max) {
+    err_ = "addKeyframe: frames-kept index exceeds the int16 ids of FindMatches.srv";
+    return false;
+  }
   // data_handler.py:157-158: the first netvlad_dimensions values, no re-normalisation
   for (int i = 0; i < dim_; ++i) local_descriptors_.push_back(i < (int)netvlad.size() ? netvlad[i] : 0.0);
   feats_desc_.push_back(d);
   feats_k3_.push_back(k3);
   feats_k_.push_back(k);
   kf_ids_of_frames_kept_.push_back(kf_id);
+  return true;
 }
 
 std::vector<std::pair<int, int>> PlaceRecognition::findMatches() {
@@ -189,6 +196,12 @@ bool PlaceRecognition::findMatchesCompute(const msgs::FindMatches::Request& req,
   for (auto& m : matches) {
     const int local = m.first;
     if (local < 0 || local >= (int)feats_desc_.size()) continue;        // `if not resp_feats_and_descs: continue` (:319-320)
+    if (local > kInt16Max || m.second > kInt16Max) {   // not representable on the wire: absent from the response
+      ++dropped_int16_;
+      err_ = "find_matches_compute: match (" + std::to_string(local) + ", " + std::to_string(m.second) +
+             ") dropped, id exceeds int16 (FindMatches.srv:3-5)";
+      continue;
+    }
     res.frames_kept_ids_computing_robot.push_back((int16_t)local);
     res.frames_kept_ids_querying_robot.push_back((int16_t)m.second);
     res.descriptors_vec.push_back(feats_desc_[local]);

@@ -84,8 +84,10 @@ class PlaceRecognition {
                    int capacity = 65536);
   ~PlaceRecognition();
 
-  // one kept keyframe of the local robot: NetVLAD descriptor (first netvlad_dimensions values), features, kf id
-  void addKeyframe(const std::vector<double>& netvlad, const msgs::Descriptors& d, const msgs::KeyPoint3DVec& k3,
+  // one kept keyframe of the local robot: NetVLAD descriptor (first netvlad_dimensions values), features, kf id.
+  // false (nothing stored, lastError() set) once the frames-kept index would no longer fit the int16 ids of
+  // FindMatches.srv:3-5 / ReceiveSeparators.srv:3-6 (rospy refuses to serialise such a response).
+  bool addKeyframe(const std::vector<double>& netvlad, const msgs::Descriptors& d, const msgs::KeyPoint3DVec& k3,
                    const msgs::KeyPointVec& k, int16_t kf_id);
 
   bool findMatchesCompute(const msgs::FindMatches::Request& req, msgs::FindMatches::Response& res);
@@ -94,6 +96,11 @@ class PlaceRecognition {
   // DataHandler.find_matches (data_handler.py:166-209): [(idx_local, idx_other)]
   std::vector<std::pair<int, int>> findMatches();
   int receivedCount() const;
+  int localCount() const { return (int)kf_ids_of_frames_kept_.size(); }
+  // matches left out of responses because an id exceeded the int16 wire types (in-band: the match is simply absent,
+  // like "no match"); lastError() says why
+  int droppedForInt16() const { return dropped_int16_; }
+  const std::string& lastError() const { return err_; }
 
  private:
   Device& dev_;
@@ -107,6 +114,8 @@ class PlaceRecognition {
   std::vector<int16_t> kf_ids_of_frames_kept_;
   std::vector<int> local_kf_already_used_, other_kf_already_used_;
   std::vector<std::pair<int, int>> frames_kept_pairs_ignored_;
+  int dropped_int16_ = 0;
+  std::string err_;
 };
 
 // rtabmap::Transform (f32 3x4, row-major) -> geometry_msgs/Pose like tf::poseEigenToMsg(transform.toEigen3d())

@@ -61,6 +61,9 @@ SEPB_API int64_t sepb_ctx_launch_count(const sepb_ctx* ctx);
 /* batches of more than this many pairs run PnP-RANSAC as two launches (first 32 hypotheses of every pair, then the
  * rest longest-first; same results, shorter tail).  Default 4 x SM count; 0 forces it, INT_MAX disables it. */
 #define SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS 2
+/* accumulator tile width of the tensor matcher: 0 (default) = 256 columns whenever the To frames fit its shared-memory
+ * budget (up to ~1400 features), else 128; 128 forces the narrow geometry.  Identical results. */
+#define SEPB_OPT_MATCH_TILE 3
 SEPB_API int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value);
 SEPB_API int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value);
 
@@ -269,8 +272,11 @@ SEPB_API int sepb_estimate_transformations_dev(sepb_ctx* ctx, const sepb_frames*
                                                const sepb_verify_out* d_out, int32_t* d_status_pass1);
 
 /* ---- measurement support (roofline denominators not in MEASURED_PEAKS.json) ----------------
- * kind 0: POPC instructions/s (K2's bounding pipe), kind 1: FP64 FMA/s (K3's).  Best of reps. */
-/* kind 0: POPC/s, 1: FP64 FMA/s, 2 / 3: TMEM bytes/s read by tcgen05.ld (plain / .pack::16b) */
+ * Microbenchmarks, best of `reps`.  kind 0: POPC instructions/s (K2's bounding pipe); 1: FP64 FMA/s (K3's);
+ * 2 / 3: TMEM bytes/s read by tcgen05.ld (plain / .pack::16b); 4 / 5: int8 op/s of a bare tcgen05.mma kind::i8 issue
+ * loop, M128 x N128 / N256 x K32, both operands in shared memory (what K2T's instruction shape sustains per GPU);
+ * 6: bf16 FLOP/s of the same loop with kind::f16 M128 x N256 x K16; 7: kind 4 with producer-like shared-memory
+ * stores running beside it. */
 SEPB_API int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s);
 /* developer hook (K3): cycle counters {EPnP solve, Rodrigues, scoring, refit, chunk-solves, 12x12 Jacobi, Jacobi
  * sweeps, 0} summed over warps; all zero and return 0 unless the library was built with SEPB_K3_PROFILE=1. */

@@ -16,6 +16,10 @@ OBJ = os.path.join(HERE, "build")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
           "-I", os.path.join(ROOT, "include")]
+# SEPB_DEVELOPER=1: the library reads its A/B switches (SEPB_K1_SPLITS, SEPB_K3_WPC, ...) from the environment;
+# a normal build compiles every getenv out of the launch paths
+if os.environ.get("SEPB_DEVELOPER"):
+    COMMON.append("-DSEPB_DEVELOPER")
 # per-file extra flags.  pnp_ransac.cu replays OpenCV's double-precision operation order bit for
 # bit (x86-64 baseline build of cv2 has no FMA contraction), hence -fmad=false there.
 # SEPB_K3_DEFS: developer A/B switches for the K3 translation unit (e.g. "-DSEPB_JACOBI_ILP=0 -DSEPB_SCORE_ILP=2")
@@ -43,7 +47,7 @@ def _stamp():
         with open(os.path.join(CSRC, f), "rb") as fh:
             h.update(fh.read())
     h.update((os.environ.get("SEPB_K3_PROFILE", "") + "|" + os.environ.get("SEPB_K3_DEFS", "") + "|"
-              + os.environ.get("SEPB_K2T_DEFS", "")).encode())
+              + os.environ.get("SEPB_K2T_DEFS", "") + "|" + os.environ.get("SEPB_DEVELOPER", "")).encode())
     return h.hexdigest()
 
 

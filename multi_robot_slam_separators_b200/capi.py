@@ -157,6 +157,7 @@ def _ptr(a):
 
 OPT_MATCH_KERNEL = 1
 OPT_PNP_TWO_PHASE_MIN_PAIRS = 2
+OPT_MATCH_TILE = 3
 
 
 class Context:
@@ -196,6 +197,10 @@ class Context:
     def set_match_kernel(self, which: str):
         """'auto' | 'popc' (INT-pipe kernel) | 'tensor' (tcgen05 int8 GEMM kernel); identical results."""
         self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_KERNEL, {"auto": -1, "popc": 0, "tensor": 1}[which]))
+
+    def set_match_tile(self, width: int):
+        """Accumulator tile of the tensor matcher: 0 = widest that fits (256 columns up to ~1400 features), 128 = narrow."""
+        self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_TILE, int(width)))
 
     def set_pnp_two_phase_min_pairs(self, n: int):
         """Batches above n pairs run K3 as two launches (chunk 0, then the rest longest-first); 0 forces it."""

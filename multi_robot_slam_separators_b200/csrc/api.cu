@@ -79,6 +79,11 @@ int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value) {
     ctx->opt_two_phase_min = value;
     return SEPB_OK;
   }
+  if (option == SEPB_OPT_MATCH_TILE) {
+    SEPB_REQUIRE(ctx, value == 0 || value == 128 || value == 256, SEPB_E_INVALID);
+    ctx->opt_match_tile = value == 256 ? 0 : value;
+    return SEPB_OK;
+  }
   return sepb_fail(ctx, SEPB_E_INVALID, "unknown option", __FILE__, __LINE__);
 }
 
@@ -90,6 +95,10 @@ int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value) {
   }
   if (option == SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS) {
     *value = ctx->opt_two_phase_min < 0 ? 4 * ctx->sm_count : ctx->opt_two_phase_min;
+    return SEPB_OK;
+  }
+  if (option == SEPB_OPT_MATCH_TILE) {
+    *value = ctx->opt_match_tile;
     return SEPB_OK;
   }
   return SEPB_E_INVALID;

@@ -89,13 +89,11 @@ static int pnp_ransac_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
     rc = ensure_table(ctx, from->max_feat, prm->iterations);
     if (rc) return rc;
   }
-  sepb_frames_acquire(ctx, from, to);
-  rc = sepb_launch_pnp_ransac(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from,
-                              d_match_to, d_n_unique_to, ctx->table, ctx->table_h, d_custom_samples, custom_h, d_guess,
-                              d_only_if_ok, prm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words,
-                              d_best_hyp, d_iters_run);
-  sepb_frames_release(ctx, from, to);
-  return rc;
+  FramesUse use(ctx, from, to);
+  return sepb_launch_pnp_ransac(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from,
+                                d_match_to, d_n_unique_to, ctx->table, ctx->table_h, d_custom_samples, custom_h, d_guess,
+                                d_only_if_ok, prm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words,
+                                d_best_hyp, d_iters_run);
 }
 
 int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
@@ -128,7 +126,8 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   int32_t* d_nu = (int32_t*)s0;
   double* d_guess = (double*)(s0 + b_nu);
   const int mw = (from->max_feat + 31) / 32;
-  sepb_frames_acquire(ctx, from, to);
+  // released when this function returns, i.e. after the last kernel that reads the stores (covariance, K2G) was enqueued
+  FramesUse use(ctx, from, to);
   int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, mprm->nndr, mprm->nndr_strict,
                                      nullptr, nullptr, o->n_matches, o->match_from, o->match_to, d_nu);
   if (rc) return rc;
@@ -281,10 +280,12 @@ int sepb_guess_match_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   double* d_g = (double*)s;
   SEPB_CUDA(ctx, cudaMemcpyAsync(d_pairs, pairs, P * 8, cudaMemcpyHostToDevice, ctx->stream));
   SEPB_CUDA(ctx, cudaMemcpyAsync(d_T, transforms, P * 48, cudaMemcpyHostToDevice, ctx->stream));
-  sepb_frames_acquire(ctx, from, to);
-  int rc = sepb_launch_guess_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, nullptr, d_T, pprm, gprm->image_width,
-                                   gprm->image_height, gprm->win_size, nndr, d_nm, d_mf, d_mt, d_nu, d_g);
-  sepb_frames_release(ctx, from, to);
+  int rc;
+  {
+    FramesUse use(ctx, from, to);
+    rc = sepb_launch_guess_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, nullptr, d_T, pprm, gprm->image_width,
+                                 gprm->image_height, gprm->win_size, nndr, d_nm, d_mf, d_mt, d_nu, d_g);
+  }
   if (rc) return rc;
   SEPB_CUDA(ctx, cudaMemcpyAsync(n_matches, d_nm, P * 4, cudaMemcpyDeviceToHost, ctx->stream));
   SEPB_CUDA(ctx, cudaMemcpyAsync(match_from, d_mf, P * F * 2, cudaMemcpyDeviceToHost, ctx->stream));

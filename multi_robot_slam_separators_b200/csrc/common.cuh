@@ -33,6 +33,7 @@ struct sepb_ctx {
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
   size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_hamming_mma_smem_wide = 0, cfg_guess_smem = 0;
   int opt_match_kernel = SEPB_MATCH_AUTO;
+  int opt_match_tile = 0;       // 0: widest K2T accumulator tile that fits, 128: force the narrow geometry
   int opt_two_phase_min = -1;   // -1: 4 x sm_count
   int opt_nn_mode = -1;  // reserved
   bool cfg_pnp = false, cfg_exact = false, cfg_gemm = false;
@@ -99,6 +100,26 @@ static inline void sepb_frames_release(sepb_ctx* ctx, const sepb_frames* a, cons
     b->has_use = true;
   }
 }
+
+// scope guard: one acquire when a call starts enqueuing readers of the stores, one release after the LAST of them on
+// every return path (a release recorded too early lets a following sepb_frames_upload_async overwrite data in use)
+struct FramesUse {
+  sepb_ctx* ctx;
+  const sepb_frames *a, *b;
+  FramesUse(sepb_ctx* c, const sepb_frames* a_, const sepb_frames* b_) : ctx(c), a(a_), b(b_) { sepb_frames_acquire(ctx, a, b); }
+  ~FramesUse() { sepb_frames_release(ctx, a, b); }
+  FramesUse(const FramesUse&) = delete;
+  FramesUse& operator=(const FramesUse&) = delete;
+};
+
+// developer A/B switches read from the environment exist only in -DSEPB_DEVELOPER builds (SEPB_DEVELOPER=1 python -m
+// ...build); a production library never calls getenv on a launch path
+#ifdef SEPB_DEVELOPER
+#include <stdlib.h>
+static inline const char* sepb_dev_env(const char* name) { return getenv(name); }
+#else
+static inline const char* sepb_dev_env(const char*) { return nullptr; }
+#endif
 
 static inline int sepb_fail(sepb_ctx* ctx, int code, const char* what, const char* file, int line) {
   char buf[512];

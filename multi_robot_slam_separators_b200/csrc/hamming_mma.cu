@@ -517,7 +517,7 @@ int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const
   if (!sepb_hamming_mma_supported(from, to))
     return sepb_fail(ctx, SEPB_E_SHAPE, "hamming_mma: frame too large for the tensor kernel", __FILE__, __LINE__);
   bool wide = geo_fits<256>(from, to);
-  if (const char* e = getenv("SEPB_K2T_TN")) wide = wide && atoi(e) == 256;  // developer A/B
+  if (ctx->opt_match_tile == 128) wide = false;   // SEPB_OPT_MATCH_TILE: the narrow geometry on request (tests, A/B)
   const size_t smem = wide ? Geo<256>::smem(to.max_feat) : Geo<128>::smem(to.max_feat);
   size_t& cfg = wide ? ctx->cfg_hamming_mma_smem_wide : ctx->cfg_hamming_mma_smem;
   if (smem > cfg) {

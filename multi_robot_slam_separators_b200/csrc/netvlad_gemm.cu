@@ -706,7 +706,7 @@ int sepb_netvlad_tensor_topk(sepb_ctx* ctx, const sepb_db* cdb, const double* d_
   const int row_blocks = (nq + BM - 1) / BM, tiles_n = (n + BN - 1) / BN;
   int splits, grid;
   choose_splits(ctx->sm_count, row_blocks, tiles_n, &splits, &grid);
-  if (const char* e = getenv("SEPB_K1_SPLITS")) {   // developer override
+  if (const char* e = sepb_dev_env("SEPB_K1_SPLITS")) {   // developer override
     splits = std::max(1, std::min(atoi(e), std::min(tiles_n, kMaxLists / 2)));
     grid = std::min(ctx->sm_count, row_blocks * splits);
   }
@@ -749,7 +749,7 @@ int sepb_netvlad_tensor_topk(sepb_ctx* ctx, const sepb_db* cdb, const double* d_
   gp.list_v = reinterpret_cast<float*>(s + o_lv); gp.list_i = reinterpret_cast<int32_t*>(s + o_li);
   gp.list_drop = reinterpret_cast<float*>(s + o_ld); gp.dbg_v = d_dbg_v; gp.stats = d_stats;
   {
-    const char* e = getenv("SEPB_K1_DBG");
+    const char* e = sepb_dev_env("SEPB_K1_DBG");
     gp.dbg_flags = e ? atoi(e) : 0;
   }
   const size_t smem = gemm_smem_bytes();
@@ -764,7 +764,7 @@ int sepb_netvlad_tensor_topk(sepb_ctx* ctx, const sepb_db* cdb, const double* d_
   // warp-uniform over 32 rows, so 4.4x fewer inserts only removed a third of its iterations and the extra launch cost
   // more than that (0.362 -> 0.400 ms measured).  Kept as the first half of a per-lane candidate queue.
   int seed_tiles = (kSeedTiles > 0 && tiles_n >= 4 * kSeedTiles) ? kSeedTiles : 0;
-  if (const char* e = getenv("SEPB_K1_SEED")) seed_tiles = std::max(0, std::min(atoi(e), tiles_n));   // developer override
+  if (const char* e = sepb_dev_env("SEPB_K1_SEED")) seed_tiles = std::max(0, std::min(atoi(e), tiles_n));   // developer override
   if (seed_tiles > 0) {
     GemmParams sp = gp;
     sp.tiles_n = seed_tiles;

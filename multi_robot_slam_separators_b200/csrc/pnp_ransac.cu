@@ -555,7 +555,7 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   for (int i = 0; i < 9; ++i) k.local_R[i] = p->local_R[i];
   k.table_h = table_h;
   size_t smem = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
-  if (const char* e = getenv("SEPB_K3_PAD_SMEM")) smem += (size_t)atoi(e);   // developer switch: fewer resident CTAs per SM
+  if (const char* e = sepb_dev_env("SEPB_K3_PAD_SMEM")) smem += (size_t)atoi(e);   // developer switch: fewer resident CTAs per SM
   bool& configured = ctx->cfg_pnp;
   if (!configured) {
     SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem + 200000 > 232448 ? 232448 : smem + 200000)));
@@ -563,9 +563,9 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
     configured = true;
   }
   int wpc0 = 5;   // warps (pairs) per CTA in phase 0; the other launches use one-warp CTAs (variable work per pair)
-  if (const char* e = getenv("SEPB_K3_WPC")) wpc0 = atoi(e);
+  if (const char* e = sepb_dev_env("SEPB_K3_WPC")) wpc0 = atoi(e);
   int wpc1 = 1;
-  if (const char* e = getenv("SEPB_K3_WPC1")) wpc1 = atoi(e);
+  if (const char* e = sepb_dev_env("SEPB_K3_WPC1")) wpc1 = atoi(e);
   auto launch = [&](int phase, const int32_t* d_order, int32_t* d_state, int stride) {
 #define SEPB_K3_LAUNCH(W)                                                                                              \
   pnp_ransac_kernel<W><<<(n_pairs + W - 1) / W, kWarp * W, smem * W, ctx->stream>>>(                                   \

@@ -46,6 +46,7 @@ class SeparatorEngine:
         self.local = capi.Frames(self.ctx, local_capacity, max_feat)
         self.peer = capi.Frames(self.ctx, peer_capacity, max_feat)
         self.db = capi.NetvladDB(self.ctx, dim, peer_capacity, base=db_base)
+        self.db_base = db_base
         self.pnp = capi.pnp_params(cam.fx, cam.fy, cam.cx, cam.cy, iterations=iterations, min_inliers=min_inliers,
                                    reproj_error=reproj_error)
         self.mp = capi.MatchParams(nndr, 0)
@@ -91,12 +92,19 @@ class SeparatorEngine:
                                                         C.c_void_p(dist.data_ptr())))
         return idx, dist
 
-    def pairs_from_candidates(self, idx: torch.Tensor):
-        """(from = peer frame = database column, to = local frame = query row); -1 = no candidate."""
+    def pairs_from_candidates(self, idx: torch.Tensor, base: int | None = None):
+        """(from = peer frame slot = database row - base, to = local frame = query row); -1 = no candidate.
+        Database rows are GLOBAL ids (`sepb_db_set_base`): the frame store of this engine holds the rows of its own
+        shard, so the shard's base is subtracted; rows of other shards (after a merge) map to -1 here."""
         Q, k = idx.shape
+        base = self.db_base if base is None else base
         with torch.cuda.stream(self.stream):
             rows = torch.arange(Q, dtype=torch.int32, device=idx.device).repeat_interleave(k)
-            pairs = torch.stack([idx.reshape(-1), rows], dim=1).contiguous()
+            col = idx.reshape(-1)
+            if base:
+                local = col - base
+                col = torch.where((col >= 0) & (local >= 0) & (local < self.peer.capacity), local, torch.full_like(col, -1))
+            pairs = torch.stack([col, rows], dim=1).contiguous()
         return pairs
 
     def verify_dev(self, d_pairs: torch.Tensor, two_pass: bool = False):

@@ -47,27 +47,48 @@ def gather_topk(idx: torch.Tensor, dist_: torch.Tensor, group=None) -> Tuple[tor
     return all_idx, all_dist
 
 
+def _order(after: "torch.cuda.Stream", before: "torch.cuda.Stream"):
+    """Work enqueued on `after` from now on waits for everything enqueued on `before` so far (device-side)."""
+    if after.cuda_stream != before.cuda_stream:
+        ev = torch.cuda.Event()
+        ev.record(before)
+        after.wait_event(ev)
+
+
 def merge_on_device(ctx) -> Callable[[torch.Tensor, torch.Tensor], Tuple[torch.Tensor, torch.Tensor]]:
-    """The product merge: sepb_topk_merge_dev on the context's stream (fails loudly without the library)."""
+    """The product merge: sepb_topk_merge_dev on the context's stream (fails loudly without the library).
+
+    The library's stream is non-blocking and the collective runs on torch's current stream, so the two are ordered
+    explicitly, both ways: the merge waits for the gather, and torch's current stream then waits for the merge --
+    the returned tensors are safe to use on the current stream like any torch result."""
     from . import capi
 
     def merge(all_idx: torch.Tensor, all_dist: torch.Tensor):
         lists, Q, k = all_idx.shape
         out_i = torch.empty((Q, k), dtype=torch.int32, device=all_idx.device)
         out_d = torch.empty((Q, k), dtype=torch.float64, device=all_idx.device)
+        lib_stream = torch.cuda.ExternalStream(ctx.stream, device=all_idx.device)
+        cur = torch.cuda.current_stream(all_idx.device)
+        _order(lib_stream, cur)
         ctx.check(capi.lib().sepb_topk_merge_dev(ctx._h, C.c_void_p(all_idx.data_ptr()), C.c_void_p(all_dist.data_ptr()),
                                                  lists, Q, k, C.c_void_p(out_i.data_ptr()), C.c_void_p(out_d.data_ptr())))
+        _order(cur, lib_stream)
+        for t in (all_idx, all_dist, out_i, out_d):
+            t.record_stream(lib_stream)
         return out_i, out_d
 
     return merge
 
 
-def sharded_topk(local_topk: Callable[[], Tuple[torch.Tensor, torch.Tensor]], merge, group=None, sync=None):
+def sharded_topk(local_topk: Callable[[], Tuple[torch.Tensor, torch.Tensor]], merge, group=None, sync=None, ctx=None):
     """One sharded NetVLAD search: local exact top-k with global ids -> all-gather -> merge.
 
-    local_topk() returns this rank's (idx [Q,k] i32, dist [Q,k] f64) with GLOBAL row ids; `sync`
-    (optional) orders the library's stream before the collective reads the tensors."""
+    local_topk() returns this rank's (idx [Q,k] i32, dist [Q,k] f64) with GLOBAL row ids.  ctx: the library context
+    local_topk enqueued on -- the collective (torch's current stream) is then ordered behind it on the device;
+    `sync` (optional, legacy) is a host-side alternative."""
     idx, d = local_topk()
+    if ctx is not None and idx.is_cuda:
+        _order(torch.cuda.current_stream(idx.device), torch.cuda.ExternalStream(ctx.stream, device=idx.device))
     if sync is not None:
         sync()
     all_idx, all_d = gather_topk(idx, d, group)

@@ -33,6 +33,9 @@ def load():
     L.sh_pr_add_keyframe.argtypes = [vp, vp, i32, vp, i32, vp, vp, vp, i32]
     L.sh_pr_find_matches_compute.argtypes = [vp, vp, i32, vp, vp, vp, i32, vp]
     L.sh_pr_receive_separators.argtypes = [vp, i32, vp, vp, vp]
+    L.sh_pr_dropped_int16.argtypes = [vp]
+    L.sh_pr_last_error.argtypes = [vp]
+    L.sh_pr_last_error.restype = C.c_char_p
     return L
 
 
@@ -137,4 +140,27 @@ def test_find_matches_compute_and_receive_separators():
     want = fm.find_matches(nv_b, nv_a, 0.13, 20, local_used=to[:3].tolist(), other_used=fr[:3].tolist(),
                            pairs_ignored=[(int(to[3]), int(fr[3])), (int(to[4]), int(fr[4]))])
     assert [(int(a), int(b)) for a, b in zip(lo[:n3], ot[:n3])] == want
+    L.sh_pr_destroy(pr); L.sh_device_destroy(dev)
+
+
+@pytest.mark.gpu
+def test_find_matches_compute_int16_wire_cap():
+    """FindMatches.srv:3-5 carries int16 ids: a match whose database row does not fit is left out of the response
+    (in-band, like "no match") and reported, never wrapped to a negative id."""
+    L = load()
+    rng = np.random.default_rng(5)
+    n_db, D = 33000, 16
+    db = rng.normal(size=(n_db, D)) * 0.3
+    local = np.stack([db[32900] + 1e-3, db[100] + 1e-3, db[32767] + 1e-3])       # nearest rows: 32900 (too big), 100, 32767 (last that fits)
+    feats = synth.make_frames(np.zeros(1, np.int64), 1, 1000, n_feat=32, dim=8)
+    dev = L.sh_device_create(0)
+    pr = L.sh_pr_create(dev, D, 0.13, 20, n_db)
+    for i in range(3):
+        L.sh_pr_add_keyframe(pr, p(np.ascontiguousarray(local[i])), D, p(feats.desc[0]), 32, p(feats.kp2d[0]), p(feats.octave[0]),
+                             p(feats.kp3d[0]), 7 + i)
+    kf, lo, ot = np.zeros(8, np.int16), np.zeros(8, np.int16), np.zeros(8, np.int16)
+    n = L.sh_pr_find_matches_compute(pr, p(np.ascontiguousarray(db)), db.size, p(kf), p(lo), p(ot), 8, None)
+    got = sorted((int(a), int(b)) for a, b in zip(lo[:n], ot[:n]))
+    assert got == [(1, 100), (2, 32767)]
+    assert L.sh_pr_dropped_int16(pr) == 1 and b"int16" in L.sh_pr_last_error(pr)
     L.sh_pr_destroy(pr); L.sh_device_destroy(dev)

@@ -124,18 +124,13 @@ def test_tensor_kernel_equals_popc_kernel_full_size():
     pairs = rng.integers(0, 48, (256, 2)).astype(np.int32)
     outs = []
     # the tensor kernel in both accumulator-tile geometries (the launch takes the 256-column one for these frames;
-    # SEPB_K2T_TN=128 is the developer switch that forces the geometry used for longer To frames)
-    import os
-    for which, tn in (("popc", None), ("tensor", None), ("tensor", "128")):
+    # SEPB_OPT_MATCH_TILE = 128 forces the geometry used for longer To frames)
+    for which, tn in (("popc", 0), ("tensor", 0), ("tensor", 128)):
         c = capi.Context(0)
         c.set_match_kernel(which)
+        c.set_match_tile(tn)
         fa, fb = capi.frames_from_robot(c, A), capi.frames_from_robot(c, B)
-        if tn:
-            os.environ["SEPB_K2T_TN"] = tn
-        try:
-            outs.append(capi.match_pairs(c, fa, fb, pairs, nndr=0.8))
-        finally:
-            os.environ.pop("SEPB_K2T_TN", None)
+        outs.append(capi.match_pairs(c, fa, fb, pairs, nndr=0.8))
         fa.close(); fb.close(); c.close()
     for other in outs[1:]:
         for k in ("knn_idx", "knn_dist", "n_matches", "n_unique_to"):

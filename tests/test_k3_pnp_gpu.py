@@ -152,3 +152,38 @@ def test_two_phase_launch_identical_in_the_second_call(ctx):
     assert int((one["status"] == 1).sum()) >= len(same) - 3
     for k in one:
         assert np.array_equal(one[k], two[k], equal_nan=True), k
+
+
+def test_async_reupload_waits_for_the_covariance_kernel(ctx):
+    """Double-buffer pattern of include/sepb200.h: an asynchronous re-upload of a store enqueued right after
+    sepb_verify_pairs_async must wait for EVERY kernel of that call that reads the store -- including pose_cov, which runs
+    after K3 -- so the results (covariance included) equal those of a blocking run on the original data."""
+    import torch
+    A, B = synth.make_robots(2, 40, n_feat=1000, dim=128, seed=1003)
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    same = [(a, b) for a in range(40) for b in range(40) if A.place[a] == B.place[b]]
+    pairs = np.array(same * 8, np.int32)
+    prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY)
+    want = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+    assert int((want["status"] == 1).sum()) >= len(same) - 2
+
+    def pinned(shape, dtype):
+        return torch.zeros(shape, dtype=getattr(torch, np.dtype(dtype).name)).pin_memory().numpy()
+
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    out = capi.verify_buffers(len(pairs), 1000, want_lists=True, alloc=pinned)
+    pairs_pin = pin(pairs)
+    junk = dict(desc=pin(np.zeros_like(A.desc)), kp2d=pin(np.full_like(A.kp2d, 7.0)), kp3d=pin(np.full_like(A.kp3d, np.nan)),
+                count=pin(A.count), octave=pin(A.octave))
+    for _ in range(3):
+        capi.verify_pairs(ctx, fa, fb, pairs_pin, prm, out=out, async_=True)
+        # overwrite BOTH stores behind the call, without waiting
+        fa.upload(0, junk["desc"], junk["kp2d"], junk["kp3d"], junk["count"], junk["octave"], async_=True)
+        fb.upload(0, junk["desc"], junk["kp2d"], junk["kp3d"], junk["count"], junk["octave"], async_=True)
+        ctx.sync()
+        fa.wait(); fb.wait()
+        for k in ("status", "n_matches", "n_inliers", "pose", "transform", "inlier_mask", "covariance"):
+            assert np.array_equal(out[k], want[k], equal_nan=True), k
+        fa.upload(0, A.desc, A.kp2d, A.kp3d, A.count, A.octave)
+        fb.upload(0, B.desc, B.kp2d, B.kp3d, B.count, B.octave)
+    fa.close(); fb.close()

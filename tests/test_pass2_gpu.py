@@ -129,15 +129,16 @@ def test_two_pass_driver(world):
             assert res["status"][p] != 1 and not res["transform"][p].any()
             assert np.array_equal(res["covariance"][p].reshape(6, 6), np.eye(6))      # no transform: identity stands
             continue
-        T1 = matching.transform_from_pnp(rv1, tv1, synth.R_LOCAL, np.zeros(3))
+        # the first call's pose agrees with cv2 to 1e-4 (checked in test_k3_pnp_gpu); the second call is seeded with the
+        # f32 transform the FIRST CALL ITSELF produced, so the oracle gets exactly that one: every pair must then agree
+        # exactly (no boundary flips from a last-bit difference between the two first-call transforms)
+        T1_cv = matching.transform_from_pnp(rv1, tv1, synth.R_LOCAL, np.zeros(3))
+        T1 = one["transform"][p]
+        assert np.abs(T1 - T1_cv).max() < 1e-4
         pr, rvg, tvg = oracle_pass2(w, o, l, T1)
         m = int(res["n_matches"][p])
         got = list(zip(res["match_from"][p, :m].tolist(), res["match_to"][p, :m].tolist()))
-        # the GPU's own first-pass transform may differ from the oracle's in the last f32 bit: the window
-        # membership of a keypoint can flip only on an exact boundary
-        assert len(set(got) ^ set(pr)) <= 2
-        if got != pr:
-            continue
+        assert got == pr, f"pair {p}: second-call correspondences differ ({len(got)} vs {len(pr)})"
         obj, img, _, _ = matching.pnp_correspondences(pr, w["A"].kp3d[o], w["B"].kp2d[l])
         ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, w["K"], rvg, tvg)
         assert (res["status"][p] == 1) == bool(ok and len(inl) >= 5)
@@ -152,4 +153,4 @@ def test_two_pass_driver(world):
             assert np.allclose(got_c, want, rtol=1e-4, atol=1e-12), (np.diag(got_c), np.diag(want))
             assert got_c[0, 0] != 1.0 and got_c[3, 3] != 1.0
         n2 += 1
-    assert n2 >= 8
+    assert n2 == int((one["status"] == 1).sum()) and n2 >= 8     # every pair whose first call succeeded was compared

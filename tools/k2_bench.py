@@ -25,6 +25,7 @@ L = capi.lib()
 stream = torch.cuda.ExternalStream(ctx.stream)
 which = sys.argv[3] if len(sys.argv) > 3 else "auto"
 ctx.set_match_kernel(which)
+ctx.set_match_tile(int(os.environ.get("SEPB_K2T_TN", "0")) % 256)   # tool-side switch -> SEPB_OPT_MATCH_TILE
 def run():
     rc = L.sepb_match_pairs_dev(ctx._h, fa._h, fb._h, C.c_void_p(pairs.data_ptr()), P, C.byref(prm), None, None,
                                 C.c_void_p(nm.data_ptr()), C.c_void_p(mf.data_ptr()), C.c_void_p(mt.data_ptr()),

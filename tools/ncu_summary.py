@@ -22,8 +22,10 @@ for h, u, v in zip(hdr, units, vals):
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
 h = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
-hdr, data = rows[h], [r for r in rows[h + 1:] if len(r) == len(rows[h])]
+hdr = rows[h]
 isrc, ins, isamp = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("# Samples")
+# multi-kernel reports repeat the header row per kernel: keep numeric rows only
+data = [r for r in rows[h + 1:] if len(r) == len(hdr) and r[ins].strip().isdigit() and r[isamp].strip().isdigit()]
 tot = sum(int(r[ins]) for r in data) or 1
 tots = sum(int(r[isamp]) for r in data) or 1
 c, cs = Counter(), Counter()
