@@ -58,9 +58,14 @@ SEPB_API int64_t sepb_ctx_launch_count(const sepb_ctx* ctx);
 #define SEPB_MATCH_AUTO (-1)
 #define SEPB_MATCH_POPC 0
 #define SEPB_MATCH_TENSOR 1
-/* batches of more than this many pairs run PnP-RANSAC as two launches (first 32 hypotheses of every pair, then the
- * rest longest-first; same results, shorter tail).  Default 4 x SM count; 0 forces it, INT_MAX disables it. */
-#define SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS 2
+/* how PnP-RANSAC is scheduled (identical results):
+ *   SEPB_PNP_SCHED_PERSISTENT  (default) one persistent CTA per SM; warps pop pairs from a device work list and, once it
+ *                              is empty, compute chunks of 32 hypotheses for the pairs still running (the chunks of a
+ *                              pair are independent; only the scan over their inlier counts is sequential)
+ *   SEPB_PNP_SCHED_PER_PAIR    one one-warp CTA per pair, every chunk by that warp (reference scheduling) */
+#define SEPB_OPT_PNP_SCHEDULER 2
+#define SEPB_PNP_SCHED_PERSISTENT 0
+#define SEPB_PNP_SCHED_PER_PAIR 1
 /* accumulator tile width of the tensor matcher: 0 (default) = 256 columns whenever the To frames fit its shared-memory
  * budget (up to ~1400 features), else 128; 128 forces the narrow geometry.  Identical results. */
 #define SEPB_OPT_MATCH_TILE 3

@@ -156,7 +156,7 @@ def _ptr(a):
 
 
 OPT_MATCH_KERNEL = 1
-OPT_PNP_TWO_PHASE_MIN_PAIRS = 2
+OPT_PNP_SCHEDULER = 2
 OPT_MATCH_TILE = 3
 
 
@@ -202,9 +202,10 @@ class Context:
         """Accumulator tile of the tensor matcher: 0 = widest that fits (256 columns up to ~1400 features), 128 = narrow."""
         self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_TILE, int(width)))
 
-    def set_pnp_two_phase_min_pairs(self, n: int):
-        """Batches above n pairs run K3 as two launches (chunk 0, then the rest longest-first); 0 forces it."""
-        self.check(lib().sepb_ctx_set_option(self._h, OPT_PNP_TWO_PHASE_MIN_PAIRS, int(n)))
+    def set_pnp_scheduler(self, which: str):
+        """'persistent' (default: persistent CTAs, device work list, idle warps compute chunks of running pairs) |
+        'per_pair' (one one-warp CTA per pair); identical results."""
+        self.check(lib().sepb_ctx_set_option(self._h, OPT_PNP_SCHEDULER, {"persistent": 0, "per_pair": 1}[which]))
 
     def close(self):
         if self._h:

@@ -74,9 +74,9 @@ int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value) {
     ctx->opt_match_kernel = value;
     return SEPB_OK;
   }
-  if (option == SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS) {
-    SEPB_REQUIRE(ctx, value >= 0, SEPB_E_INVALID);
-    ctx->opt_two_phase_min = value;
+  if (option == SEPB_OPT_PNP_SCHEDULER) {
+    SEPB_REQUIRE(ctx, value == SEPB_PNP_SCHED_PERSISTENT || value == SEPB_PNP_SCHED_PER_PAIR, SEPB_E_INVALID);
+    ctx->opt_pnp_sched = value;
     return SEPB_OK;
   }
   if (option == SEPB_OPT_MATCH_TILE) {
@@ -93,8 +93,8 @@ int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value) {
     *value = ctx->opt_match_kernel;
     return SEPB_OK;
   }
-  if (option == SEPB_OPT_PNP_TWO_PHASE_MIN_PAIRS) {
-    *value = ctx->opt_two_phase_min < 0 ? 4 * ctx->sm_count : ctx->opt_two_phase_min;
+  if (option == SEPB_OPT_PNP_SCHEDULER) {
+    *value = ctx->opt_pnp_sched;
     return SEPB_OK;
   }
   if (option == SEPB_OPT_MATCH_TILE) {

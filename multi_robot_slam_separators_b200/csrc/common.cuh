@@ -27,14 +27,14 @@ struct sepb_ctx {
   // cv::RNG(-1) minimal-sample index table [count][table_h][5] (K3)
   uint16_t* table = nullptr;
   int table_m = -1, table_h = 0;
-  // K3 launch order (pairs with the fewest correspondences = longest RANSAC runs first), grow-only
+  // K3 work queue (pair list, worker states, chunk slots of the helper protocol; pnp_ransac.cu), grow-only, in int32 units
   int32_t* k3_order = nullptr;
   size_t k3_order_cap = 0;
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
   size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_hamming_mma_smem_wide = 0, cfg_guess_smem = 0;
   int opt_match_kernel = SEPB_MATCH_AUTO;
   int opt_match_tile = 0;       // 0: widest K2T accumulator tile that fits, 128: force the narrow geometry
-  int opt_two_phase_min = -1;   // -1: 4 x sm_count
+  int opt_pnp_sched = SEPB_PNP_SCHED_PERSISTENT;
   int opt_nn_mode = -1;  // reserved
   bool cfg_pnp = false, cfg_exact = false, cfg_gemm = false;
 };

@@ -40,6 +40,17 @@
 #define K3_ACC(slot, v)
 #endif
 
+#ifndef SEPB_JACOBI_REGROWS
+// 1: the two rows of a Jacobi rotation stay in registers between the dot product and the rotation; 0 (developer A/B):
+// re-read from the scratch heap per element, each load ordered behind the previous element's stores
+#define SEPB_JACOBI_REGROWS 1
+#endif
+#ifndef SEPB_JACOBI_BRANCHFREE
+#define SEPB_JACOBI_BRANCHFREE 1   // 0 (developer A/B): the branches of the scalar code
+#endif
+#ifndef SEPB_JACOBI_COMPACT
+#define SEPB_JACOBI_COMPACT 1      // 12 x 12 Jacobi with per-lane pair sequences (jacobi12_compact); 0: the shared loop
+#endif
 #ifndef SEPB_JACOBI_ILP
 // 1: 12 x 12 sweep with two row-disjoint rotations in flight (jacobi12_sweeps_ilp).  Measured on B200 (tools/k3_ab.sh):
 // 10 % fewer cycles per warp but no shorter kernel (26.85 vs 26.57 ms verify), so the plain cyclic loop stays the default.
@@ -117,6 +128,44 @@ CVM_HD inline double cv_hypot(double a, double b) {
     return b * sqrt(1 + a * a);
   }
   return 0;
+}
+
+// rotation angle of JacobiSVDImpl_ for the row pair with squared norms a, b and dot product p:
+//   p *= 2; beta = a - b; gamma = hypot(p, beta);
+//   beta < 0:  delta = (gamma - beta) / 2; s = sqrt(delta / gamma); c = p / (gamma * s * 2)
+//   else:      c = sqrt((gamma + beta) / (gamma * 2));              s = p / (gamma * c * 2)
+// The SAME operations on the same operands, with the operands SELECTED instead of branched on (cv_hypot's two cases
+// and the sign of beta): the lanes of a warp each hold their own hypothesis, and a branch here makes the warp run the
+// divide / square-root chains of both sides one after the other.
+CVM_HD inline void jacobi_cs(double p, double a, double b, double& c, double& s) {
+#if SEPB_JACOBI_BRANCHFREE
+  p *= 2;
+  const double beta = a - b;
+  const double ha = fabs(p), hb = fabs(beta);
+  const bool agtb = ha > hb;
+  const double big = agtb ? ha : hb, small = agtb ? hb : ha;
+  const double q = small / big;
+  const double gq = big * sqrt(1 + q * q);
+  const double gamma = (agtb || hb > 0) ? gq : 0.0;
+  const bool neg = beta < 0;
+  const double num = neg ? (gamma - beta) * 0.5 : (gamma + beta);
+  const double den = neg ? gamma : gamma * 2;
+  const double r1 = sqrt(num / den);
+  const double r2 = p / (gamma * r1 * 2);
+  s = neg ? r1 : r2;
+  c = neg ? r2 : r1;
+#else
+  p *= 2;
+  const double beta = a - b, gamma = cv_hypot(p, beta);
+  if (beta < 0) {
+    const double delta = (gamma - beta) * 0.5;
+    s = sqrt(delta / gamma);
+    c = p / (gamma * s * 2);
+  } else {
+    c = sqrt((gamma + beta) / (gamma * 2));
+    s = p / (gamma * c * 2);
+  }
+#endif
 }
 
 // tail of JacobiSVDImpl_: singular values, descending sort, normalisation (random completion of zero rows)
@@ -223,26 +272,32 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd_fixed(Heap At, Heap W, Heap Vt) {
       for (int j = i + 1; j < n; ++j) {
         const Heap Ai = At.at(i * m), Aj = At.at(j * m);
         double a = W[i], p = 0, b = W[j];
+        // both rows stay in registers from the dot product to the rotation (the scratch accessors are ordered volatile
+        // accesses: re-reading them per element would serialise every load behind the previous element's stores)
+        double x[m], y[m];
         CVM_UNROLL
-        for (int k = 0; k < m; ++k) p += Ai[k] * Aj[k];
-        if (fabs(p) <= eps * sqrt(a * b)) continue;
-        p *= 2;
-        const double beta = a - b, gamma = cv_hypot(p, beta);
-        double c, s;
-        if (beta < 0) {
-          const double delta = (gamma - beta) * 0.5;
-          s = sqrt(delta / gamma);
-          c = p / (gamma * s * 2);
-        } else {
-          c = sqrt((gamma + beta) / (gamma * 2));
-          s = p / (gamma * c * 2);
+        for (int k = 0; k < m; ++k) {
+          x[k] = Ai[k];
+          y[k] = Aj[k];
         }
+        CVM_UNROLL
+        for (int k = 0; k < m; ++k) p += x[k] * y[k];
+#if !SEPB_JACOBI_REGROWS
+#define CVM_ROW_X(k) ((double)Ai[k])
+#define CVM_ROW_Y(k) ((double)Aj[k])
+#else
+#define CVM_ROW_X(k) x[k]
+#define CVM_ROW_Y(k) y[k]
+#endif
+        if (fabs(p) <= eps * sqrt(a * b)) continue;
+        double c, s;
+        jacobi_cs(p, a, b, c, s);
         a = b = 0;
         CVM_UNROLL
         for (int k = 0; k < m; ++k) {
-          const double x = Ai[k], y = Aj[k];
-          const double t0 = c * x + s * y;
-          const double t1 = -s * x + c * y;
+          const double xk = CVM_ROW_X(k), yk = CVM_ROW_Y(k);
+          const double t0 = c * xk + s * yk;
+          const double t1 = -s * xk + c * yk;
           Ai[k] = t0;
           Aj[k] = t1;
           a += t0 * t0;
@@ -253,11 +308,16 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd_fixed(Heap At, Heap W, Heap Vt) {
         changed = true;
         if (want_v) {
           const Heap Vi = Vt.at(i * n), Vj = Vt.at(j * n);
+          double vx[n], vy[n];
           CVM_UNROLL
           for (int k = 0; k < n; ++k) {
-            const double x = Vi[k], y = Vj[k];
-            Vi[k] = c * x + s * y;
-            Vj[k] = -s * x + c * y;
+            vx[k] = Vi[k];
+            vy[k] = Vj[k];
+          }
+          CVM_UNROLL
+          for (int k = 0; k < n; ++k) {
+            Vi[k] = c * vx[k] + s * vy[k];
+            Vj[k] = -s * vx[k] + c * vy[k];
           }
         }
       }
@@ -363,26 +423,30 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd_rt(Heap At, Heap W, Heap Vt, const in
       for (int j = i + 1; j < n; ++j) {
         const Heap Ai = At.at(i * m), Aj = At.at(j * m);
         double a = W[i], p = 0, b = W[j];
+        double x[m], y[m];   // rows kept in registers between the dot product and the rotation (see jacobi_svd_fixed)
         CVM_UNROLL
-        for (int k = 0; k < m; ++k) p += Ai[k] * Aj[k];
-        if (fabs(p) <= eps * sqrt(a * b)) continue;
-        p *= 2;
-        const double beta = a - b, gamma = cv_hypot(p, beta);
-        double c, s;
-        if (beta < 0) {
-          const double delta = (gamma - beta) * 0.5;
-          s = sqrt(delta / gamma);
-          c = p / (gamma * s * 2);
-        } else {
-          c = sqrt((gamma + beta) / (gamma * 2));
-          s = p / (gamma * c * 2);
+        for (int k = 0; k < m; ++k) {
+          x[k] = Ai[k];
+          y[k] = Aj[k];
         }
+        CVM_UNROLL
+        for (int k = 0; k < m; ++k) p += x[k] * y[k];
+#if !SEPB_JACOBI_REGROWS
+#define CVM_ROW_X(k) ((double)Ai[k])
+#define CVM_ROW_Y(k) ((double)Aj[k])
+#else
+#define CVM_ROW_X(k) x[k]
+#define CVM_ROW_Y(k) y[k]
+#endif
+        if (fabs(p) <= eps * sqrt(a * b)) continue;
+        double c, s;
+        jacobi_cs(p, a, b, c, s);
         a = b = 0;
         CVM_UNROLL
         for (int k = 0; k < m; ++k) {
-          const double x = Ai[k], y = Aj[k];
-          const double t0 = c * x + s * y;
-          const double t1 = -s * x + c * y;
+          const double xk = CVM_ROW_X(k), yk = CVM_ROW_Y(k);
+          const double t0 = c * xk + s * yk;
+          const double t1 = -s * xk + c * yk;
           Ai[k] = t0;
           Aj[k] = t1;
           a += t0 * t0;
@@ -394,9 +458,9 @@ CVM_HD CVM_NOINLINE inline void jacobi_svd_rt(Heap At, Heap W, Heap Vt, const in
         if (want_v) {
           const Heap Vi = Vt.at(i * n), Vj = Vt.at(j * n);
           for (int k = 0; k < n; ++k) {
-            const double x = Vi[k], y = Vj[k];
-            Vi[k] = c * x + s * y;
-            Vj[k] = -s * x + c * y;
+            const double vx = Vi[k], vy = Vj[k];
+            Vi[k] = c * vx + s * vy;
+            Vj[k] = -s * vx + c * vy;
           }
         }
       }
@@ -543,6 +607,97 @@ __device__ CVM_NOINLINE inline void jacobi12_sweeps_ilp(Heap At, Heap W) {
         }
     }
     if (!__any_sync(mask, changed)) break;
+  }
+  jacobi_finish<12, 12, false>(At, W, W);
+}
+#endif
+
+#if defined(__CUDA_ARCH__)
+// The 12 x 12 one-sided Jacobi of M^T M with every lane walking ITS OWN (i, j) sequence.  In the plain loop the 32
+// hypotheses of a warp share the loop counters, so a pair (i, j) costs the whole divide / square-root chain of a
+// rotation as soon as ONE lane has to rotate it -- from the third sweep on almost every pair, although each lane
+// rotates only a few of them.  Here a lane first runs ahead over the pairs it skips (dot product + convergence test
+// only), stops at the next pair it has to rotate, and the warp then executes one rotation for all lanes at once, each
+// on its own rows: the number of rotation chains a warp pays for drops from "pairs any lane rotates" to about
+// "pairs the busiest lane rotates".  Per lane the sequence of operations is exactly that of jacobi_svd_fixed
+// (same order of pairs, same sweeps, same arithmetic), so the results are bit-identical.
+__device__ CVM_NOINLINE inline void jacobi12_compact(Heap At, Heap W) {
+  constexpr int m = 12, n = 12, max_iter = 30;
+  constexpr uint32_t kEl = kHeapStride * 8, kRow = m * kEl;
+  const double eps = kDblEps * 10;
+  for (int r = 0; r < n; ++r) {
+    double sd = 0;
+    CVM_UNROLL
+    for (int k = 0; k < m; ++k) {
+      const double t = At[r * m + k];
+      sd += t * t;
+    }
+    W[r] = sd;
+  }
+  int i = 0, j = 1, iter = 0;
+  bool changed = false, done = false;
+#if defined(SEPB_K3_PROFILE)
+  if ((threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[6], 1ull);
+#endif
+  // next pair in the cyclic order; at the end of a sweep: stop if nothing rotated, else start the next one
+  auto advance = [&]() {
+    if (++j == n) {
+      ++i;
+      j = i + 1;
+      if (i == n - 1) {
+        if (!changed || ++iter == max_iter) done = true;
+#if defined(SEPB_K3_PROFILE)
+        else if ((threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[6], 1ull);
+#endif
+        changed = false;
+        i = 0;
+        j = 1;
+      }
+    }
+  };
+  for (;;) {
+    double x[m], y[m], a = 0, b = 0, p = 0;
+    uint32_t ai = 0, aj = 0;
+    bool need = false;
+    // run ahead over the pairs this lane does not rotate
+    while (!done) {
+      ai = At.a + (uint32_t)i * kRow;
+      aj = At.a + (uint32_t)j * kRow;
+      a = lds_f64(W.a + (uint32_t)i * kEl);
+      b = lds_f64(W.a + (uint32_t)j * kEl);
+      CVM_UNROLL
+      for (int k = 0; k < m; ++k) {
+        x[k] = lds_f64(ai + k * kEl);
+        y[k] = lds_f64(aj + k * kEl);
+      }
+      p = 0;
+      CVM_UNROLL
+      for (int k = 0; k < m; ++k) p += x[k] * y[k];
+      if (!(fabs(p) <= eps * sqrt(a * b))) {
+        need = true;
+        break;
+      }
+      advance();
+    }
+    if (!__any_sync(0xFFFFFFFFu, need)) break;   // every lane has converged (or hit max_iter)
+    if (need) {
+      double c, s;
+      jacobi_cs(p, a, b, c, s);
+      a = b = 0;
+      CVM_UNROLL
+      for (int k = 0; k < m; ++k) {
+        const double t0 = c * x[k] + s * y[k];
+        const double t1 = -s * x[k] + c * y[k];
+        sts_f64(ai + k * kEl, t0);
+        sts_f64(aj + k * kEl, t1);
+        a += t0 * t0;
+        b += t1 * t1;
+      }
+      sts_f64(W.a + (uint32_t)i * kEl, a);
+      sts_f64(W.a + (uint32_t)j * kEl, b);
+      changed = true;
+      advance();
+    }
   }
   jacobi_finish<12, 12, false>(At, W, W);
 }

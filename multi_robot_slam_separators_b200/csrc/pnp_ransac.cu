@@ -1,4 +1,4 @@
-// K3: batched PnP-RANSAC + ITERATIVE refit, one keyframe pair per CTA (one warp).
+// K3: batched PnP-RANSAC + ITERATIVE refit, one warp per keyframe pair at a time (persistent work-queue kernel).
 //
 // Replaces util3d::estimateMotion3DTo2D -> cv::solvePnPRansac (useExtrinsicGuess, 5-point EPnP
 // minimal sets, confidence 0.99) called at R/src/myRegistrationVis.cpp:1077-1090.
@@ -9,9 +9,11 @@
 // must be replayed serially, see cvmath.cuh, so a hypothesis cannot be split across lanes), then
 // SCORES them one after the other with all 32 lanes striding over the correspondences (warp per
 // hypothesis), applying OpenCV's `goodCount > max(best, 4)` rule and RANSACUpdateNumIters after each
-// one, which reproduces the sequential result exactly and keeps most of its early exit.
+// one, which reproduces the sequential result exactly and keeps most of its early exit.  For the same
+// reason whole chunks of a pair can be computed by other warps (see "K3 scheduling" below).
 // Compiled with -fmad=false (see build.py): no multiply-add contraction, like the cv2 build.
 #include <cstdlib>
+#include <algorithm>
 
 #include "common.cuh"
 
@@ -34,9 +36,9 @@ constexpr int kWarp = 32;
 constexpr int kSolveLanes = cvm::kHeapStride;   // hypotheses solved at once by a warp (one lane each)
 constexpr int kMaskWords = SEPB_MAX_FEATURES / 32;
 #ifndef SEPB_SCORE_ILP
-#define SEPB_SCORE_ILP 1   // measured: 1 -> 26.57 ms, 2 -> 26.98 ms, 4 -> 29.8 ms per verify of 50 k pairs (staged LDS are cheap)
+#define SEPB_SCORE_ILP 1
 #endif
-constexpr int kScoreIlp = SEPB_SCORE_ILP;                    // correspondences per lane scored together
+constexpr int kScoreIlp = SEPB_SCORE_ILP;   // correspondences per lane scored together (developer A/B)
 
 struct PnpKernelParams {
   cvm::Intrinsics K;
@@ -72,73 +74,6 @@ __global__ void sample_table_kernel(uint16_t* table, int max_count, int H) {
       idx[i] = v;
       row[h * 5 + i] = (uint16_t)v;
     }
-  }
-}
-
-// Two-phase launch of K3.  A pair's cost is its number of 32-hypothesis chunks (1..10 at 300 iterations), unknown
-// until RANSAC runs, and the hardware hands CTAs out in blockIdx order: in one launch a 7-chunk pair that happens to
-// start last keeps an SM busy for 5 ms after the rest has drained (measured: 16 ms against 11.6 ms of work).  So
-// phase 0 runs chunk 0 of every pair (uniform cost; pairs that are done after it finish there), saves
-// {niters, best count, best hypothesis, mask} of the others, and phase 1 resumes them in DESCENDING order of the
-// iteration bound left after chunk 0 (longest first).  Counting sort in one CTA; order inside a bin is arbitrary
-// because every pair writes only its own outputs.
-constexpr int kOrderThreads = 1024;
-constexpr int kStateInts = 4;   // per-pair state header: niters (0 = nothing left to do), best_good, best_h, hk
-__global__ void __launch_bounds__(kOrderThreads)
-pnp_order_kernel(const int32_t* __restrict__ state, int state_stride, int n_pairs, int32_t* __restrict__ order,
-                 const int32_t* __restrict__ n_matches, const int32_t* __restrict__ only_if_ok) {
-  __shared__ int hist[SEPB_MAX_FEATURES + 2];   // bin max(0, 4096 - niters); last bin = pairs with nothing left
-  __shared__ int warp_tot[32];
-  constexpr int kBins = SEPB_MAX_FEATURES + 2;
-  const int tid = threadIdx.x;
-  for (int i = tid; i < kBins; i += kOrderThreads) hist[i] = 0;
-  __syncthreads();
-  auto key_of = [&](int p) {
-    if (n_matches) {   // before phase 0: pairs that will run RANSAC first (so that they share CTAs), every pair listed
-      const bool run = n_matches[p] >= 5 && (!only_if_ok || only_if_ok[p] == 1);
-      return run ? 0 : kBins - 1;
-    }
-    const int it = state[(size_t)p * state_stride];
-    return it > 0 ? max(0, SEPB_MAX_FEATURES - it) : kBins - 1;
-  };
-  for (int p = tid; p < n_pairs; p += kOrderThreads) atomicAdd(&hist[key_of(p)], 1);
-  __syncthreads();
-  if (tid == 0) order[n_pairs] = n_matches ? n_pairs : n_pairs - hist[kBins - 1];   // pairs listed
-  // exclusive scan of the bins: each thread owns a contiguous run of bins
-  constexpr int kPer = (kBins + kOrderThreads - 1) / kOrderThreads;
-  int local[kPer], sum = 0;
-  for (int i = 0; i < kPer; ++i) {
-    const int b = tid * kPer + i;
-    local[i] = b < kBins ? hist[b] : 0;
-    sum += local[i];
-  }
-  int incl = sum;
-  for (int o = 1; o < 32; o <<= 1) {
-    const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-    if ((tid & 31) >= o) incl += v;
-  }
-  if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
-  __syncthreads();
-  if (tid < 32) {
-    int w = warp_tot[tid];
-    for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xFFFFFFFFu, w, o);
-      if (tid >= o) w += v;
-    }
-    warp_tot[tid] = w;
-  }
-  __syncthreads();
-  int base = incl - sum + ((tid >> 5) ? warp_tot[(tid >> 5) - 1] : 0);
-  __syncthreads();
-  for (int i = 0; i < kPer; ++i) {
-    const int b = tid * kPer + i;
-    if (b < kBins) hist[b] = base;
-    base += local[i];
-  }
-  __syncthreads();
-  for (int p = tid; p < n_pairs; p += kOrderThreads) {
-    const int k = key_of(p);
-    if (k != kBins - 1 || n_matches) order[atomicAdd(&hist[k], 1)] = p;
   }
 }
 
@@ -270,200 +205,365 @@ __device__ __forceinline__ void lm_step_warp(cvm::Heap h, const double* JtJ, con
   for (int i = 0; i < 6; ++i) param[i] = __shfl_sync(0xFFFFFFFFu, param[i], 0);
 }
 
-// One warp per keyframe pair.  WPC warps (pairs) share a CTA: the warps of a CTA start together and, as long as their
-// work is alike (phase 0: chunk 0 of every pair), run the same code at about the same time, which is what the
-// instruction caches want -- ncu shows the GPC-level cache at 40-50 % of its request rate for this 330 KB kernel.
-template <int WPC>
-__global__ void __launch_bounds__(kWarp * WPC, 5 / WPC)
-pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs,
-                  const int32_t* __restrict__ n_matches, const uint16_t* __restrict__ match_from,
-                  const uint16_t* __restrict__ match_to, const int32_t* __restrict__ n_unique_to,
-                  const uint16_t* __restrict__ table, const int32_t* __restrict__ custom_samples, int custom_h,
-                  const double* __restrict__ guess /*[P][6] or null*/, const int32_t* __restrict__ only_if_ok,
-                  PnpKernelParams prm,
-                  int32_t* __restrict__ status, int32_t* __restrict__ n_inliers, double* __restrict__ pose /*[P][6]*/,
-                  float* __restrict__ transform /*[P][12]*/, uint32_t* __restrict__ inlier_mask, int mask_words,
-                  int32_t* __restrict__ best_hyp, int32_t* __restrict__ iters_run, const int32_t* __restrict__ order,
-                  int phase /*-1: whole run, 0: chunk 0 (+ finish if done), 1: resume*/, int32_t* __restrict__ state,
-                  int state_stride) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  constexpr size_t kWarpBytes = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
-  uint8_t* wsm = smem_raw + (threadIdx.x >> 5) * kWarpBytes;   // this warp's heap + masks
-  double* heap_base = reinterpret_cast<double*>(wsm);
-  uint32_t* s_mask = reinterpret_cast<uint32_t*>(wsm + (size_t)cvm::kEpnpHeap * kSolveLanes * 8);  // 2 * kMaskWords
-  const int lane = threadIdx.x & 31;
-  const int slot = blockIdx.x * WPC + (threadIdx.x >> 5);
-  if (slot >= (order ? order[n_pairs] : n_pairs)) return;
-  const int pair = order ? order[slot] : slot;
-  int32_t* st = state ? state + (size_t)pair * state_stride : nullptr;
-  if (phase == 0 && lane == 0) st[0] = 0;   // nothing to resume unless the chunk loop says so
-  // second pass (estimate_transformation's call with guess = first result): pairs whose first pass failed keep it
-  if (only_if_ok && only_if_ok[pair] != 1) return;
-  const cvm::Heap heap{heap_base + lane};
-  int fi = pairs[2 * pair], ti = pairs[2 * pair + 1];
-  const bool valid_pair = fi >= 0 && fi < from.size && ti >= 0 && ti < to.size;
-  if (!valid_pair) fi = ti = 0;
-  const int M = valid_pair ? n_matches[pair] : 0;
-  const int nf = valid_pair ? from.count[fi] : 0;
-  const int nu = n_unique_to ? n_unique_to[pair] : M;
-  float* stage_buf = reinterpret_cast<float*>(wsm + kStageOffBytes);
-  Corr cr{from.kp3d + (size_t)fi * from.max_feat * 3, to.kp2d + (size_t)ti * to.max_feat * 2,
-          match_from + (size_t)pair * from.max_feat, match_to + (size_t)pair * from.max_feat,
-          M <= kStageCap ? stage_buf : nullptr};
+// ---- K3 scheduling ---------------------------------------------------------------------------------------------
+// A pair's cost is its number of 32-hypothesis chunks (1..10 at 300 iterations), unknown until RANSAC runs, and one
+// chunk is ~0.7 ms of serial f64 work for a warp: a pair that needs every chunk is a 7 ms dependency chain, longer than
+// the rest of the batch.  But hypothesis h is a pure function of (match count, h) and so is its inlier count, hence
+// the chunks of a pair can be computed by DIFFERENT warps at the same time and only the cheap scan over the counts
+// (OpenCV's `>` rule + RANSACUpdateNumIters, in hypothesis order) has to be sequential.
+//
+// pnp_persist_kernel: one CTA per SM, kPersistWarps warps, every warp a worker:
+//   * owner:  pops pairs from a list (pnp_prepare_kernel compacts the pairs that run RANSAC, the others get their null
+//             result there), runs the chunks of its pair one after the other -- solve 32 hypotheses (lane each), score
+//             them in order (warp each) with the live early exit -- then the refit;
+//   * helper: once the list is empty a worker looks for the owner with the most iterations left, claims that pair's
+//             next chunk (atomic counter per owner), solves + scores it and leaves {32 inlier counts, 32 poses} in the
+//             owner's slot array.  The owner claims chunks from the same counter; when it finds chunks taken by
+//             helpers it computes the one it got into a slot too, then consumes the slots in hypothesis order (the
+//             same scan), and re-scores only the winning hypothesis to get its mask.
+// A helper exists only after the list ran empty, so an owner being helped is on its last pair and its slots are
+// written at most once per launch.  Results are bit-identical to the one-warp-per-pair kernel (pnp_ransac_kernel).
+constexpr int kPersistWarps = 5;      // workers per SM (shared-memory bound: 44.5 KB heap each)
+constexpr int kMaxHelpChunks = 64;    // slots per worker; more chunks than that (iterations > 2048): no helping
+
+struct PnpArgs {
+  FramesView from, to;
+  const int32_t* pairs;
+  int n_pairs;
+  const int32_t* n_matches;
+  const uint16_t* match_from;
+  const uint16_t* match_to;
+  const int32_t* n_unique_to;
+  const uint16_t* table;
+  const int32_t* custom_samples;
+  int custom_h;
+  const double* guess;          // [P][6] or null
+  const int32_t* only_if_ok;    // second call of estimate_transformation: pairs whose first call failed keep its result
+  PnpKernelParams prm;
+  int32_t* status;
+  int32_t* n_inliers;
+  double* pose;                 // [P][6]
+  float* transform;             // [P][12]
+  uint32_t* inlier_mask;
+  int mask_words;
+  int32_t* best_hyp;
+  int32_t* iters_run;
+};
+
+struct PnpQueue {          // device memory, head (ctrl, wk, slot_ready) zeroed before every launch
+  int32_t* ctrl;           // [0] list cursor, [1] pairs listed, [2] pairs finished
+  int32_t* wk;             // [n_workers][4]: pair, next chunk to claim, published iteration bound, accepting help
+  int32_t* slot_ready;     // [n_workers][max_chunks]
+  int32_t* list;           // [n_pairs] pairs that run RANSAC
+  int32_t* slot_good;      // [n_workers][max_chunks][32] inlier counts
+  double* slot_rt;         // [n_workers][max_chunks][12][32] R (9) | t (3), hypothesis-minor
+  int n_workers, max_chunks;   // max_chunks == 0: helping disabled
+};
+
+__device__ __forceinline__ int ld_volatile(const int32_t* p) { return *reinterpret_cast<const volatile int32_t*>(p); }
+__device__ __forceinline__ void st_volatile(int32_t* p, int v) { *reinterpret_cast<volatile int32_t*>(p) = v; }
+// one lane reads, every lane gets the same value (control flow that depends on it stays warp-uniform)
+__device__ __forceinline__ int ld_volatile_warp(const int32_t* p) {
+  int v = 0;
+  if ((threadIdx.x & 31) == 0) v = ld_volatile(p);
+  return __shfl_sync(0xFFFFFFFFu, v, 0);
+}
+
+struct PairIn {
+  int pair, fi, ti, M, nf, nu;
+  bool valid;
+  Corr cr;
   double g[6];
+};
+
+__device__ __forceinline__ PairIn load_pair(const PnpArgs& a, int pair, float* stage_buf) {
+  PairIn in;
+  in.pair = pair;
+  in.fi = a.pairs[2 * pair];
+  in.ti = a.pairs[2 * pair + 1];
+  in.valid = in.fi >= 0 && in.fi < a.from.size && in.ti >= 0 && in.ti < a.to.size;
+  if (!in.valid) in.fi = in.ti = 0;
+  in.M = in.valid ? a.n_matches[pair] : 0;
+  in.nf = in.valid ? a.from.count[in.fi] : 0;
+  in.nu = a.n_unique_to ? a.n_unique_to[pair] : in.M;
+  in.cr = Corr{a.from.kp3d + (size_t)in.fi * a.from.max_feat * 3, a.to.kp2d + (size_t)in.ti * a.to.max_feat * 2,
+               a.match_from + (size_t)pair * a.from.max_feat, a.match_to + (size_t)pair * a.from.max_feat,
+               in.M <= kStageCap ? stage_buf : nullptr};
+#pragma unroll
   for (int i = 0; i < 3; ++i) {
-    g[i] = guess ? guess[6 * pair + i] : prm.rvec0[i];
-    g[3 + i] = guess ? guess[6 * pair + 3 + i] : prm.tvec0[i];
+    in.g[i] = a.guess ? a.guess[6 * pair + i] : a.prm.rvec0[i];
+    in.g[3 + i] = a.guess ? a.guess[6 * pair + 3 + i] : a.prm.tvec0[i];
   }
-  uint32_t* out_mask = inlier_mask ? inlier_mask + (size_t)pair * mask_words : nullptr;
-  if (out_mask && phase != 1)
-    for (int w = lane; w < mask_words; w += 32) out_mask[w] = 0;
+  return in;
+}
 
-  auto finish = [&](int st, int ninl, const double* p6, int bh, int it) {
-    if (lane == 0) {
-      status[pair] = st;
-      n_inliers[pair] = ninl;
-      if (best_hyp) best_hyp[pair] = bh;
-      if (iters_run) iters_run[pair] = it;
-      for (int i = 0; i < 6; ++i) pose[6 * pair + i] = p6[i];
-      float* T = transform + 12 * (size_t)pair;
-      if (st == 1) {
-        // T = (local * [R|t])^-1  (maps To-base coordinates into the From base frame)
-        double R[9], RP[9], tP[3];
-        cvm::rodrigues_vec_to_mat(p6, R, nullptr);
-        for (int i = 0; i < 3; ++i) {
-          for (int j = 0; j < 3; ++j)
-            RP[3 * i + j] = prm.local_R[3 * i] * R[j] + prm.local_R[3 * i + 1] * R[3 + j] + prm.local_R[3 * i + 2] * R[6 + j];
-          tP[i] = prm.local_R[3 * i] * p6[3] + prm.local_R[3 * i + 1] * p6[4] + prm.local_R[3 * i + 2] * p6[5] + prm.local_t[i];
-        }
-        for (int i = 0; i < 3; ++i) {
-          for (int j = 0; j < 3; ++j) T[4 * i + j] = (float)RP[3 * j + i];
-          T[4 * i + 3] = (float)(-(RP[i] * tP[0] + RP[3 + i] * tP[1] + RP[6 + i] * tP[2]));
-        }
-      } else {
-        for (int i = 0; i < 12; ++i) T[i] = 0.f;  // null transform (Transform::isNull())
-      }
+// myRegistrationVis.cpp:1069-1070 and estimateMotion3DTo2D: >= minInliers on every side (and a minimal set)
+__device__ __forceinline__ bool pair_runs(const PnpArgs& a, const PairIn& in) {
+  return !(in.M < a.prm.min_inliers || in.nf < a.prm.min_inliers || in.nu < a.prm.min_inliers || in.M < 5);
+}
+
+// result of one pair (one thread)
+__device__ __noinline__ void write_result(const PnpArgs& a, int pair, int st, int ninl, const double* p6, int bh, int it) {
+  a.status[pair] = st;
+  a.n_inliers[pair] = ninl;
+  if (a.best_hyp) a.best_hyp[pair] = bh;
+  if (a.iters_run) a.iters_run[pair] = it;
+  for (int i = 0; i < 6; ++i) a.pose[6 * pair + i] = p6[i];
+  float* T = a.transform + 12 * (size_t)pair;
+  if (st == 1) {
+    // T = (local * [R|t])^-1  (maps To-base coordinates into the From base frame)
+    const PnpKernelParams& prm = a.prm;
+    double R[9], RP[9], tP[3];
+    cvm::rodrigues_vec_to_mat(p6, R, nullptr);
+    for (int i = 0; i < 3; ++i) {
+      for (int j = 0; j < 3; ++j)
+        RP[3 * i + j] = prm.local_R[3 * i] * R[j] + prm.local_R[3 * i + 1] * R[3 + j] + prm.local_R[3 * i + 2] * R[6 + j];
+      tP[i] = prm.local_R[3 * i] * p6[3] + prm.local_R[3 * i + 1] * p6[4] + prm.local_R[3 * i + 2] * p6[5] + prm.local_t[i];
     }
-  };
+    for (int i = 0; i < 3; ++i) {
+      for (int j = 0; j < 3; ++j) T[4 * i + j] = (float)RP[3 * j + i];
+      T[4 * i + 3] = (float)(-(RP[i] * tP[0] + RP[3 + i] * tP[1] + RP[6 + i] * tP[2]));
+    }
+  } else {
+    for (int i = 0; i < 12; ++i) T[i] = 0.f;  // null transform (Transform::isNull())
+  }
+}
 
-  // myRegistrationVis.cpp:1069-1070 and estimateMotion3DTo2D: need >= minInliers on every side
-  if (M < prm.min_inliers || nf < prm.min_inliers || nu < prm.min_inliers || M < 5) {
-    finish(0, 0, g, -1, 0);
+// thread per pair: pairs that run RANSAC go to the work list, the others get their null result here
+__global__ void __launch_bounds__(256) pnp_prepare_kernel(PnpArgs a, PnpQueue q) {
+  const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= a.n_pairs) return;
+  // second call (estimate_transformation's call with guess = first result): pairs whose first call failed keep it
+  if (a.only_if_ok && a.only_if_ok[pair] != 1) return;
+  const PairIn in = load_pair(a, pair, nullptr);
+  if (pair_runs(a, in)) {
+    q.list[atomicAdd(&q.ctrl[1], 1)] = pair;
     return;
   }
+  if (a.inlier_mask)
+    for (int w = 0; w < a.mask_words; ++w) a.inlier_mask[(size_t)pair * a.mask_words + w] = 0;
+  write_result(a, pair, 0, 0, in.g, -1, 0);
+}
+
+struct WarpScratch {
+  double* heap_base;    // this warp's strided scratch heap
+  float* stage_buf;     // correspondence staging area inside it
+  uint32_t* s_mask;     // [2][kMaskWords] ping-pong inlier masks
+};
+
+// ---- solve: lane <-> hypothesis.  h_cap: hypotheses at or past it are never consumed (their lanes redo h_cap - 1)
+__device__ __forceinline__ void solve_chunk(const PnpArgs& a, const PairIn& in, const WarpScratch& ws, int chunk0, int h_cap,
+                                            double* Rh, double* th) {
+  const int lane = threadIdx.x & 31;
+  const cvm::Heap heap{ws.heap_base + lane};
+  int h = chunk0 + lane;
+  if (h >= h_cap) h = h_cap - 1;
+  float o[15], im[10];
+  for (int i = 0; i < 5; ++i) {
+    const int s = a.custom_samples ? a.custom_samples[((size_t)in.pair * a.custom_h + h) * 5 + i]
+                                   : a.table[((size_t)in.M * a.prm.table_h + h) * 5 + i];
+    in.cr.load(min(max(s, 0), in.M - 1), o + 3 * i, im + 2 * i);
+  }
+  __syncwarp();   // every lane has read its samples from the staging area before a solve overwrites it
+  double R0[9], rv[3];
+  K3_T0(t_e);
+  cvm::epnp5(heap, o, im, a.prm.K, R0, th);
+  K3_ACC(0, t_e);
+  K3_T0(t_r);
+  cvm::rodrigues_mat_to_vec(heap, R0, rv);   // runKernel hands the model on as rvec
+  cvm::rodrigues_vec_to_mat(rv, Rh, nullptr);  // projectPoints turns it back into a matrix
+  K3_ACC(1, t_r);
+  __syncwarp();
+  in.cr.stage(ws.stage_buf, in.M);   // the solve overwrote the staging area
+}
+
+// ---- score: warp <-> hypothesis.  Inlier mask of pose (R, t) into cand[], returns the count (PnPRansacCallback::computeError)
+__device__ __forceinline__ int score_one(const PnpArgs& a, const PairIn& in, const double* R, const double* t, uint32_t* cand) {
+  const int lane = threadIdx.x & 31;
+  int good = 0;
+  // kScoreIlp independent correspondences per lane in flight: the projection is a dependent f64 chain with a divide
+  for (int base = 0; base < in.M; base += 32 * kScoreIlp) {
+    bool inl[kScoreIlp];
+#pragma unroll
+    for (int u = 0; u < kScoreIlp; ++u) {
+      const int m = base + 32 * u + lane;
+      float o3[3], i2[2];
+      in.cr.load(min(m, in.M - 1), o3, i2);
+      inl[u] = (cvm::reproj_err_f32(R, t, a.prm.K, o3, i2) <= a.prm.thr2) && m < in.M;
+    }
+#pragma unroll
+    for (int u = 0; u < kScoreIlp; ++u) {
+      const uint32_t b = __ballot_sync(0xFFFFFFFFu, inl[u]);
+      if (base + 32 * u < in.M) {
+        if (lane == 0) cand[(base >> 5) + u] = b;
+        good += __popc(b);
+      }
+    }
+  }
+  return good;
+}
+
+// a whole chunk for somebody else's scan: solve, score every hypothesis, leave counts and poses in the owner's slot
+__device__ __noinline__ void chunk_to_slot(const PnpArgs& a, const PnpQueue& q, const PairIn& in, const WarpScratch& ws,
+                                           int owner, int cc, uint32_t* cand) {
+  const int lane = threadIdx.x & 31;
+  double Rh[9], th[3];
+  solve_chunk(a, in, ws, cc * kSolveLanes, a.prm.iterations, Rh, th);
+  K3_T0(t_s);
+  int mygood = 0;
+  for (int k = 0; k < kSolveLanes; ++k) {
+    // the owner's published bound never undercuts its live iteration count: what lies past it is never consumed
+    if (cc * kSolveLanes + k >= ld_volatile_warp(q.wk + 4 * owner + 2)) break;
+    double R[9], t[3];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = __shfl_sync(0xFFFFFFFFu, Rh[i], k);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) t[i] = __shfl_sync(0xFFFFFFFFu, th[i], k);
+    const int good = score_one(a, in, R, t, cand);
+    if (lane == k) mygood = good;
+  }
+  K3_ACC(2, t_s);
+#ifdef SEPB_K3_PROFILE
+  if (lane == 0) atomicAdd(&g_k3_prof[4], 1ull);
+#endif
+  const size_t slot = (size_t)owner * q.max_chunks + cc;
+  q.slot_good[slot * 32 + lane] = mygood;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) q.slot_rt[(slot * 12 + i) * 32 + lane] = Rh[i];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) q.slot_rt[(slot * 12 + 9 + i) * 32 + lane] = th[i];
+  __threadfence();
+  __syncwarp();
+  if (lane == 0) st_volatile(q.slot_ready + slot, 1);
+}
+
+// One keyframe pair, one warp.  worker >= 0: persistent kernel (chunks are claimed from the owner's counter and may
+// arrive from helpers); worker < 0: the warp runs every chunk itself.
+__device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, int worker, int pair, const WarpScratch& ws) {
+  const PnpKernelParams& prm = a.prm;
+  const int lane = threadIdx.x & 31;
+  const cvm::Heap heap{ws.heap_base + lane};
+  uint32_t* s_mask = ws.s_mask;
+  const PairIn in = load_pair(a, pair, ws.stage_buf);
+  const int M = in.M;
+  const Corr& cr = in.cr;
+  uint32_t* out_mask = a.inlier_mask ? a.inlier_mask + (size_t)pair * a.mask_words : nullptr;
+  if (out_mask)
+    for (int w = lane; w < a.mask_words; w += 32) out_mask[w] = 0;
 
   if (M == 5) {  // count == modelPoints: one EPnP over all five, no refit, all inliers
     float o[15], im[10];
     for (int i = 0; i < 5; ++i) cr.load_global(i, o + 3 * i, im + 2 * i);
     double R[9], p6[6] = {0, 0, 0, 0, 0, 0};
-    if (lane < kSolveLanes) {   // only these lanes own a slice of the scratch heap; lane 0 reports
-      cvm::epnp5(heap, o, im, prm.K, R, p6 + 3);
-      cvm::rodrigues_mat_to_vec(heap, R, p6);
+    cvm::epnp5(heap, o, im, prm.K, R, p6 + 3);
+    cvm::rodrigues_mat_to_vec(heap, R, p6);
+    if (lane == 0) {
+      if (out_mask) out_mask[0] = 0x1Fu;
+      write_result(a, pair, 5 >= prm.min_inliers ? 1 : 3, 5, p6, 0, 1);
     }
-    if (out_mask && lane == 0) out_mask[0] = 0x1Fu;
-    finish(5 >= prm.min_inliers ? 1 : 3, 5, p6, 0, 1);
     return;
   }
 
   int niters = prm.iterations > 1 ? prm.iterations : 1;
-  int best_good = 0, best_h = -1, cur = 0, hk = 0, chunk0 = 0;
-  if (phase == 1) {   // resume after chunk 0
-    niters = st[0];
-    best_good = st[1];
-    best_h = st[2];
-    hk = st[3];
-    chunk0 = kSolveLanes;
-    for (int w = lane; w < (M + 31) / 32; w += 32) s_mask[w] = (uint32_t)st[kStateInts + w];
+  int best_good = 0, best_h = -1, cur = 0, hk = 0;
+  bool best_in_smem = true;    // the mask of the best hypothesis is in s_mask[cur] (else: re-score it from its slot)
+  const bool queued = worker >= 0 && q.max_chunks > 0;
+  int32_t* wk = queued ? q.wk + 4 * worker : nullptr;
+  if (queued) {
+    if (lane == 0) {
+      st_volatile(wk + 0, pair);
+      st_volatile(wk + 1, 0);
+      st_volatile(wk + 2, niters);
+      __threadfence();
+      st_volatile(wk + 3, 1);
+    }
     __syncwarp();
   }
-  cr.stage(stage_buf, M);
-  for (int chunk = chunk0; chunk < niters; chunk += kSolveLanes) {
-    // ---- solve: lane <-> hypothesis (the first kSolveLanes lanes; more resident warps hide the f64 latency
-    //      better than wider warps, and shorter chunks waste fewer hypotheses past the adaptive stop)
-    int h = chunk + lane;
-    if (h >= niters) h = niters - 1;
-    double Rh[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, th[3] = {0, 0, 0};
-    if (lane < kSolveLanes) {
-      float o[15], im[10];
-      for (int i = 0; i < 5; ++i) {
-        const int s = custom_samples ? custom_samples[((size_t)pair * custom_h + h) * 5 + i]
-                                     : table[((size_t)M * prm.table_h + h) * 5 + i];
-        cr.load(min(max(s, 0), M - 1), o + 3 * i, im + 2 * i);
-      }
-      __syncwarp();   // every lane has read its samples from the staging area before a solve overwrites it
-      double R0[9], rv[3];
-      K3_T0(t_e);
-      cvm::epnp5(heap, o, im, prm.K, R0, th);
-      K3_ACC(0, t_e);
-      K3_T0(t_r);
-      cvm::rodrigues_mat_to_vec(heap, R0, rv);   // runKernel hands the model on as rvec
-      cvm::rodrigues_vec_to_mat(rv, Rh, nullptr);  // projectPoints turns it back into a matrix
-      K3_ACC(1, t_r);
+  cr.stage(ws.stage_buf, M);
+  int c_next = 0;   // chunks below it have been consumed
+  while (c_next * kSolveLanes < niters) {
+    int my = c_next;
+    if (queued) {
+      if (lane == 0) my = atomicAdd(wk + 1, 1);
+      my = __shfl_sync(0xFFFFFFFFu, my, 0);
     }
-    __syncwarp();
-    cr.stage(stage_buf, M);   // the solve overwrote the staging area
-    K3_T0(t_s);
-    // ---- score: warp <-> hypothesis, in RANSAC order
-    for (int k = 0; k < kSolveLanes; ++k) {
-      hk = chunk + k;
-      if (hk >= niters) break;
-      double R[9], t[3];
+    if (my == c_next) {
+      // ---- nobody is helping: solve, then score in RANSAC order with the live early exit
+      const int chunk = my * kSolveLanes;
+      double Rh[9], th[3];
+      solve_chunk(a, in, ws, chunk, niters, Rh, th);
+      K3_T0(t_s);
+      for (int k = 0; k < kSolveLanes; ++k) {
+        hk = chunk + k;
+        if (hk >= niters) break;
+        double R[9], t[3];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) R[i] = __shfl_sync(0xFFFFFFFFu, Rh[i], k);
+        for (int i = 0; i < 9; ++i) R[i] = __shfl_sync(0xFFFFFFFFu, Rh[i], k);
 #pragma unroll
-      for (int i = 0; i < 3; ++i) t[i] = __shfl_sync(0xFFFFFFFFu, th[i], k);
-      uint32_t* cand = s_mask + (cur ^ 1) * kMaskWords;
-      int good = 0;
-      // kScoreIlp independent correspondences per lane in flight: the projection is a long dependent f64 chain
-      // behind two dependent loads, and a warp has only itself to hide that latency
-      for (int base = 0; base < M; base += 32 * kScoreIlp) {
-        bool inl[kScoreIlp];
-#pragma unroll
-        for (int u = 0; u < kScoreIlp; ++u) {
-          const int m = base + 32 * u + lane;
-          float o3[3], i2[2];
-          cr.load(min(m, M - 1), o3, i2);
-          inl[u] = (cvm::reproj_err_f32(R, t, prm.K, o3, i2) <= prm.thr2) && m < M;
+        for (int i = 0; i < 3; ++i) t[i] = __shfl_sync(0xFFFFFFFFu, th[i], k);
+        const int good = score_one(a, in, R, t, s_mask + (cur ^ 1) * kMaskWords);
+        if (good > max(best_good, 4)) {
+          cur ^= 1;
+          best_good = good;
+          best_h = hk;
+          best_in_smem = true;
+          niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, 5, niters);
         }
-#pragma unroll
-        for (int u = 0; u < kScoreIlp; ++u) {
-          const uint32_t b = __ballot_sync(0xFFFFFFFFu, inl[u]);
-          if (base + 32 * u < M) {
-            if (lane == 0) cand[(base >> 5) + u] = b;
-            good += __popc(b);
-          }
-        }
+        hk = hk + 1;
       }
-      if (good > max(best_good, 4)) {
-        cur ^= 1;
-        best_good = good;
-        best_h = hk;
-        niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, 5, niters);
-      }
-      hk = hk + 1;
-    }
-    K3_ACC(2, t_s);
+      K3_ACC(2, t_s);
 #ifdef SEPB_K3_PROFILE
-    if (lane == 0) atomicAdd(&g_k3_prof[4], 1ull);
+      if (lane == 0) atomicAdd(&g_k3_prof[4], 1ull);
 #endif
-    if (phase == 0 && chunk + kSolveLanes < niters) {   // more chunks to run: hand the pair over to phase 1
-      __syncwarp();
-      if (lane == 0) {
-        st[0] = niters;
-        st[1] = best_good;
-        st[2] = best_h;
-        st[3] = hk;
+      c_next = my + 1;
+    } else {
+      // ---- helpers hold chunks c_next .. my-1: do chunk `my` the way they do, then scan everything in order
+      if (my * kSolveLanes < niters) chunk_to_slot(a, q, in, ws, worker, my, s_mask + (cur ^ 1) * kMaskWords);
+      for (int cc = c_next; cc <= my && cc * kSolveLanes < niters; ++cc) {
+        const size_t slot = (size_t)worker * q.max_chunks + cc;
+        while (ld_volatile_warp(q.slot_ready + slot) == 0) __nanosleep(200);
+        __threadfence();
+        const int gk = *reinterpret_cast<const volatile int32_t*>(q.slot_good + slot * 32 + lane);
+        for (int k = 0; k < kSolveLanes; ++k) {
+          hk = cc * kSolveLanes + k;
+          if (hk >= niters) break;
+          const int good = __shfl_sync(0xFFFFFFFFu, gk, k);
+          if (good > max(best_good, 4)) {
+            best_good = good;
+            best_h = hk;
+            best_in_smem = false;
+            niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, 5, niters);
+          }
+          hk = hk + 1;
+        }
       }
-      const uint32_t* bm = s_mask + cur * kMaskWords;
-      for (int w = lane; w < (M + 31) / 32; w += 32) st[kStateInts + w] = (int32_t)bm[w];
-      return;
+      c_next = my + 1;
+    }
+    if (queued && lane == 0) st_volatile(wk + 2, niters);
+  }
+  if (queued) {
+    __syncwarp();
+    if (lane == 0) {
+      st_volatile(wk + 3, 0);   // no more chunks wanted
+      __threadfence();          // ... and nobody may see this pair's flag once the list cursor has moved on
     }
   }
   __syncwarp();
   K3_T0(t_lm);
   if (best_h < 0) {
-    finish(2, 0, g, -1, hk);
+    if (lane == 0) write_result(a, pair, 2, 0, in.g, -1, hk);
     return;
+  }
+  if (!best_in_smem) {   // the winner came out of a slot: its mask is one more scoring pass
+    const size_t slot = (size_t)worker * q.max_chunks + best_h / kSolveLanes;
+    const int k = best_h % kSolveLanes;
+    double R[9], t[3];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = *reinterpret_cast<const volatile double*>(q.slot_rt + (slot * 12 + i) * 32 + k);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) t[i] = *reinterpret_cast<const volatile double*>(q.slot_rt + (slot * 12 + 9 + i) * 32 + k);
+    score_one(a, in, R, t, s_mask + cur * kMaskWords);
+    __syncwarp();
   }
   const uint32_t* best = s_mask + cur * kMaskWords;
   if (out_mask)
@@ -471,7 +571,7 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
 
   // ---- refit: solvePnP(inliers, ITERATIVE, useExtrinsicGuess) == CvLevMarq from the caller's guess
   double param[6], prev[6], JtJ[21], JtE[6];
-  for (int i = 0; i < 6; ++i) param[i] = prev[i] = g[i];
+  for (int i = 0; i < 6; ++i) param[i] = prev[i] = in.g[i];
   int lambda_lg10 = -3, iters = 0;
   double err2 = 0, prev_err_norm = 0;
   const int max_iter = 20;
@@ -502,7 +602,85 @@ pnp_ransac_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pa
     lm_accumulate(cr, best, M, prm.K, param, true, JtJ, JtE, err2);
   }
   K3_ACC(3, t_lm);
-  finish(best_good >= prm.min_inliers ? 1 : 3, best_good, param, best_h, hk);
+  if (lane == 0) write_result(a, pair, best_good >= prm.min_inliers ? 1 : 3, best_good, param, best_h, hk);
+}
+
+constexpr size_t kWarpBytes = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
+
+__device__ __forceinline__ WarpScratch warp_scratch(uint8_t* smem_raw) {
+  uint8_t* wsm = smem_raw + (threadIdx.x >> 5) * kWarpBytes;   // this warp's heap + masks
+  return WarpScratch{reinterpret_cast<double*>(wsm), reinterpret_cast<float*>(wsm + kStageOffBytes),
+                     reinterpret_cast<uint32_t*>(wsm + (size_t)cvm::kEpnpHeap * kSolveLanes * 8)};
+}
+
+// reference scheduling (SEPB_PNP_SCHED_PER_PAIR): one one-warp CTA per listed pair, every chunk by that warp
+__global__ void __launch_bounds__(kWarp, 5) pnp_ransac_kernel(PnpArgs a, PnpQueue q) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  if ((int)blockIdx.x >= q.ctrl[1]) return;
+  run_pair(a, q, -1, q.list[blockIdx.x], warp_scratch(smem_raw));
+}
+
+__global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(PnpArgs a, PnpQueue q) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const WarpScratch ws = warp_scratch(smem_raw);
+  const int lane = threadIdx.x & 31;
+  const int worker = blockIdx.x * kPersistWarps + (threadIdx.x >> 5);
+  const int n_listed = q.ctrl[1];
+  // ---- owner: pairs off the list until it is empty
+  for (;;) {
+    int slot = 0;
+    if (lane == 0) slot = atomicAdd(&q.ctrl[0], 1);
+    slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
+    if (slot >= n_listed) break;
+    run_pair(a, q, worker, q.list[slot], ws);
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence();
+      atomicAdd(&q.ctrl[2], 1);
+    }
+  }
+  if (q.max_chunks == 0) return;
+  // ---- helper: chunks of the owners still running, most iterations left first.  The list is empty for good, so every
+  //      owner seen from here on is on its last pair (its worker state is never reset again).
+  __threadfence();
+  for (;;) {
+    int best_rem = 0, best_w = -1;
+    for (int i = lane; i < q.n_workers; i += 32) {
+      if (ld_volatile(q.wk + 4 * i + 3)) {
+        __threadfence();
+        const int rem = ld_volatile(q.wk + 4 * i + 2) - ld_volatile(q.wk + 4 * i + 1) * kSolveLanes;
+        if (rem > best_rem) {
+          best_rem = rem;
+          best_w = i;
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const int r2 = __shfl_xor_sync(0xFFFFFFFFu, best_rem, o), w2 = __shfl_xor_sync(0xFFFFFFFFu, best_w, o);
+      if (r2 > best_rem || (r2 == best_rem && w2 > best_w)) {
+        best_rem = r2;
+        best_w = w2;
+      }
+    }
+    if (best_w < 0) {
+      if (ld_volatile_warp(q.ctrl + 2) >= n_listed) break;   // every pair has its result
+      __nanosleep(1000);
+      continue;
+    }
+    int cc = 0;
+    if (lane == 0) cc = atomicAdd(q.wk + 4 * best_w + 1, 1);
+    cc = __shfl_sync(0xFFFFFFFFu, cc, 0);
+    // the owner only waits for chunks below its live iteration count (<= the bound read here) while it accepts help
+    if (cc >= q.max_chunks || cc * kSolveLanes >= ld_volatile_warp(q.wk + 4 * best_w + 2) ||
+        !ld_volatile_warp(q.wk + 4 * best_w + 3))
+      continue;
+    __threadfence();
+    const int pair = ld_volatile_warp(q.wk + 4 * best_w);
+    const PairIn in = load_pair(a, pair, ws.stage_buf);
+    in.cr.stage(ws.stage_buf, in.M);
+    chunk_to_slot(a, q, in, ws, best_w, cc, ws.s_mask);
+  }
 }
 
 }  // namespace
@@ -541,7 +719,21 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
                            float* d_transform, uint32_t* d_inlier_mask, int mask_words, int32_t* d_best_hyp,
                            int32_t* d_iters_run) {
   if (n_pairs == 0) return SEPB_OK;
-  PnpKernelParams k;
+  PnpArgs a;
+  a.from = from;
+  a.to = to;
+  a.pairs = d_pairs;
+  a.n_pairs = n_pairs;
+  a.n_matches = d_n_matches;
+  a.match_from = d_match_from;
+  a.match_to = d_match_to;
+  a.n_unique_to = d_n_unique_to;
+  a.table = d_table;
+  a.custom_samples = d_custom_samples;
+  a.custom_h = custom_h;
+  a.guess = d_guess;
+  a.only_if_ok = d_only_if_ok;
+  PnpKernelParams& k = a.prm;
   k.K = cvm::Intrinsics{p->fx, p->fy, p->cx, p->cy};
   k.iterations = p->iterations;
   k.thr2 = (float)(p->reproj_error * p->reproj_error);
@@ -554,42 +746,33 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   }
   for (int i = 0; i < 9; ++i) k.local_R[i] = p->local_R[i];
   k.table_h = table_h;
-  size_t smem = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
+  a.status = d_status;
+  a.n_inliers = d_n_inliers;
+  a.pose = d_pose;
+  a.transform = d_transform;
+  a.inlier_mask = d_inlier_mask;
+  a.mask_words = mask_words;
+  a.best_hyp = d_best_hyp;
+  a.iters_run = d_iters_run;
+
+  size_t smem = kWarpBytes;
   if (const char* e = sepb_dev_env("SEPB_K3_PAD_SMEM")) smem += (size_t)atoi(e);   // developer switch: fewer resident CTAs per SM
-  bool& configured = ctx->cfg_pnp;
-  if (!configured) {
-    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem + 200000 > 232448 ? 232448 : smem + 200000)));
-    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(5 * smem)));
-    configured = true;
+  if (!ctx->cfg_pnp) {
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem + 200000 > 232448 ? 232448 : smem + 200000)));
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kPersistWarps * kWarpBytes)));
+    ctx->cfg_pnp = true;
   }
-  int wpc0 = 5;   // warps (pairs) per CTA in phase 0; the other launches use one-warp CTAs (variable work per pair)
-  if (const char* e = sepb_dev_env("SEPB_K3_WPC")) wpc0 = atoi(e);
-  int wpc1 = 1;
-  if (const char* e = sepb_dev_env("SEPB_K3_WPC1")) wpc1 = atoi(e);
-  auto launch = [&](int phase, const int32_t* d_order, int32_t* d_state, int stride) {
-#define SEPB_K3_LAUNCH(W)                                                                                              \
-  pnp_ransac_kernel<W><<<(n_pairs + W - 1) / W, kWarp * W, smem * W, ctx->stream>>>(                                   \
-      from, to, d_pairs, n_pairs, d_n_matches, d_match_from, d_match_to, d_n_unique_to, d_table, d_custom_samples,     \
-      custom_h, d_guess, d_only_if_ok, k, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words,      \
-      d_best_hyp, d_iters_run, d_order, phase, d_state, stride)
-    const int w = phase == 0 ? wpc0 : phase == 1 ? wpc1 : 1;
-    if (w == 5) {
-      SEPB_K3_LAUNCH(5);
-    } else {
-      SEPB_K3_LAUNCH(1);
-    }
-#undef SEPB_K3_LAUNCH
-    ctx->launches++;
-  };
-  // below a few waves of CTAs there is no tail to trim: one launch.  Otherwise chunk 0, sort, resume (pnp_order_kernel)
-  const int two_phase_min = ctx->opt_two_phase_min < 0 ? 4 * ctx->sm_count : ctx->opt_two_phase_min;
-  if (n_pairs <= two_phase_min || p->iterations <= kSolveLanes) {
-    launch(-1, nullptr, nullptr, 0);
-    SEPB_CUDA(ctx, cudaGetLastError());
-    return SEPB_OK;
-  }
-  const int stride = kStateInts + (from.max_feat + 31) / 32;
-  const size_t want = (size_t)n_pairs * (stride + 1) + 1;   // state + order + resume count
+  // queue memory (grow-only): zeroed head {ctrl, wk, slot_ready} | list | slot_good | slot_rt
+  const bool persistent = ctx->opt_pnp_sched == SEPB_PNP_SCHED_PERSISTENT;
+  const int n_workers = persistent ? ctx->sm_count * kPersistWarps : 0;
+  const int chunks = (p->iterations + kSolveLanes - 1) / kSolveLanes;
+  int max_chunks = persistent && chunks > 1 && chunks <= kMaxHelpChunks ? chunks : 0;
+  if (const char* e = sepb_dev_env("SEPB_K3_NO_HELP")) max_chunks = atoi(e) ? 0 : max_chunks;   // developer A/B
+  const size_t n_head = 4 + (size_t)4 * n_workers + (size_t)n_workers * max_chunks;
+  const size_t n_good = (size_t)n_workers * max_chunks * 32;
+  size_t n_ints = n_head + (size_t)n_pairs + n_good;
+  n_ints = (n_ints + 3) & ~(size_t)3;
+  const size_t want = n_ints + (size_t)n_workers * max_chunks * 12 * 32 * 2;   // doubles counted as two ints
   if (want > ctx->k3_order_cap) {
     if (ctx->k3_order) {
       cudaStreamSynchronize(ctx->stream);
@@ -597,22 +780,32 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
       ctx->k3_order = nullptr;
       ctx->k3_order_cap = 0;
     }
-    const size_t cap = want + want / 2;
+    const size_t cap = want + want / 4;
     SEPB_CUDA(ctx, cudaMalloc(&ctx->k3_order, cap * sizeof(int32_t)));
     ctx->k3_order_cap = cap;
   }
-  int32_t* d_state = ctx->k3_order;
-  int32_t* d_order = ctx->k3_order + (size_t)n_pairs * stride;
-  if (wpc0 > 1) {   // group the pairs that will run RANSAC into the same CTAs
-    pnp_order_kernel<<<1, kOrderThreads, 0, ctx->stream>>>(nullptr, 0, n_pairs, d_order, d_n_matches, d_only_if_ok);
-    ctx->launches++;
-    launch(0, d_order, d_state, stride);
-  } else {
-    launch(0, nullptr, d_state, stride);
-  }
-  pnp_order_kernel<<<1, kOrderThreads, 0, ctx->stream>>>(d_state, stride, n_pairs, d_order, nullptr, nullptr);
+  PnpQueue q;
+  q.ctrl = ctx->k3_order;
+  q.wk = q.ctrl + 4;
+  q.slot_ready = q.wk + (size_t)4 * n_workers;
+  q.list = q.ctrl + n_head;
+  q.slot_good = q.list + n_pairs;
+  q.slot_rt = reinterpret_cast<double*>(ctx->k3_order + n_ints);
+  q.n_workers = n_workers;
+  q.max_chunks = max_chunks;
+  SEPB_CUDA(ctx, cudaMemsetAsync(q.ctrl, 0, n_head * sizeof(int32_t), ctx->stream));
+  pnp_prepare_kernel<<<(n_pairs + 255) / 256, 256, 0, ctx->stream>>>(a, q);
   ctx->launches++;
-  launch(1, d_order, d_state, stride);
+  if (persistent) {
+    // fewer CTAs than SMs when the batch cannot feed them all even with every chunk of every pair in flight
+    const long long units = (long long)n_pairs * (max_chunks > 0 ? max_chunks : 1);
+    const int ctas = (int)std::min<long long>(ctx->sm_count, (units + kPersistWarps - 1) / kPersistWarps);
+    q.n_workers = ctas * kPersistWarps;
+    pnp_persist_kernel<<<ctas, kWarp * kPersistWarps, kPersistWarps * kWarpBytes, ctx->stream>>>(a, q);
+  } else {
+    pnp_ransac_kernel<<<n_pairs, kWarp, smem, ctx->stream>>>(a, q);
+  }
+  ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());
   return SEPB_OK;
 }

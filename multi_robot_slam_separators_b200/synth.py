@@ -88,8 +88,15 @@ def make_netvlad(place_ids, dim, seed, noise=0.25, full_dim=4096, chunk=2048):
 
 
 def make_frames(place_ids, robot, seed, n_feat=1000, dim=128, n_landmarks=700, flip_p=0.06,
-                pix_sigma=0.5, disp_sigma=0.3, nan_frac=0.05, true_frac=0.55, gross_frac=0.35, chunk=256):
-    """Generate one robot's keyframes for the given place ids."""
+                pix_sigma=0.5, disp_sigma=0.3, nan_frac=0.05, true_frac=0.55, gross_frac=0.35, chunk=256,
+                hard_negatives=0.0, vocabulary=2000):
+    """Generate one robot's keyframes for the given place ids.
+
+    hard_negatives > 0: that fraction of the clutter features takes its descriptor from a vocabulary of `vocabulary`
+    words shared by every place and robot (with the same bit-flip noise as landmarks), like repetitive structure seen by
+    a real ORB front-end: frames of DIFFERENT places then share a few dozen words, pass the ratio test on them and send
+    all-outlier correspondence sets into RANSAC, which burns every iteration (the K3-bound regime).  0 = every clutter
+    descriptor is uniform random, so unrelated frames produce ~no matches (the configs[1] mix of round 1)."""
     n = len(place_ids)
     F = n_feat
     desc = np.empty((n, F, 32), dtype=np.uint8)
@@ -145,6 +152,13 @@ def make_frames(place_ids, robot, seed, n_feat=1000, dim=128, n_landmarks=700, f
         uc = r.uniform(0, WIDTH, (B, F))
         vc = r.uniform(0, HEIGHT, (B, F))
         dsc = r.integers(0, 256, (B, F, 32), dtype=np.uint8)
+        if hard_negatives > 0:     # own random stream: the default data does not change
+            r2 = np.random.default_rng([seed, 17, robot, s])
+            vocab = np.random.default_rng([seed, 13]).integers(0, 256, (vocabulary, 32), dtype=np.uint8)
+            hn = r2.random((B, F)) < hard_negatives
+            word = r2.integers(0, vocabulary, (B, F))
+            wflip = np.packbits(r2.random((B, F, 256)) < flip_p, axis=2, bitorder="little")
+            dsc = np.where(hn[..., None], vocab[word] ^ wflip, dsc)
         lid = np.full((B, F), -1, dtype=np.int32)
         bi = np.arange(B)[:, None]
         zt = np.take_along_axis(z, order, axis=1)

@@ -63,8 +63,8 @@ def test_config4_kitti_sized_frames(mode, match_kernel):
 
 def test_config5_sweep_batch_is_order_independent():
     """configs[4]: one large batch of candidate pairs drawn from a resident frame store.  Size-independent property:
-    every pair's result depends on the pair alone -- a 20 000-pair batch (two-phase K3 launch, multi-wave K2) gives,
-    pair for pair, what the same pairs give in small single-launch batches, and duplicates agree."""
+    every pair's result depends on the pair alone -- a 20 000-pair batch (persistent K3 work queue, multi-wave K2) gives,
+    pair for pair, what the same pairs give in small one-warp-per-pair batches, and duplicates agree."""
     n, F = 64, 1000
     A, B = synth.make_robots(2, n, n_feat=F, dim=8, seed=5000)
     ctx = capi.Context(0)
@@ -81,7 +81,7 @@ def test_config5_sweep_batch_is_order_independent():
         big = capi.verify_pairs(ctx, fa, fb, pairs, prm, want_lists=False)
         assert int((big["status"] == 1).sum()) > 1000
         uniq, first = np.unique(pairs, axis=0, return_index=True)
-        ctx.set_pnp_two_phase_min_pairs(1 << 30)
+        ctx.set_pnp_scheduler("per_pair")      # reference scheduling: one warp runs every chunk of its pair
         small = capi.verify_pairs(ctx, fa, fb, uniq[:500], prm, want_lists=False)
         key = {tuple(p): i for i, p in enumerate(uniq[:500])}
         rows = np.array([key.get(tuple(p), -1) for p in pairs])

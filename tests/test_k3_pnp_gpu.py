@@ -105,9 +105,10 @@ def test_synthetic_pairs_vs_cv2(ctx):
     assert n_ok >= len(same) - 2
 
 
-def test_two_phase_launch_identical(ctx, golden):
-    """Large batches run K3 as chunk 0 + longest-first resume (pnp_order_kernel): every output must equal the
-    single-launch run, including pairs that finish in chunk 0, degenerate pairs and injected sample indices."""
+def test_persistent_scheduler_identical(ctx, golden):
+    """The persistent work-queue kernel (idle warps compute chunks of other warps' pairs; the owner scans their inlier
+    counts in hypothesis order) must equal the one-warp-per-pair kernel on every output, including pairs that finish in
+    chunk 0 and degenerate pairs.  Few pairs against 740 workers: almost every chunk here comes from a helper."""
     A, B = synth.make_robots(2, 40, n_feat=1000, dim=128, seed=1003)
     A.count[3] = 700
     B.count[5] = 300
@@ -118,13 +119,12 @@ def test_two_phase_launch_identical(ctx, golden):
     pairs = same + [(int(rng.integers(40)), int(rng.integers(40))) for _ in range(30)] + [(7, 1), (3, 5)]
     for iters in (300, 40, 1000):
         prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY, iterations=iters)
-        ctx.set_pnp_two_phase_min_pairs(1 << 30)
-        one = capi.verify_pairs(ctx, fa, fb, pairs, prm)
-        ctx.set_pnp_two_phase_min_pairs(0)
+        ctx.set_pnp_scheduler("per_pair")
         try:
-            two = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+            one = capi.verify_pairs(ctx, fa, fb, pairs, prm)
         finally:
-            ctx.set_pnp_two_phase_min_pairs(4 * 148)
+            ctx.set_pnp_scheduler("persistent")
+        two = capi.verify_pairs(ctx, fa, fb, pairs, prm)
         assert int((one["status"] == 1).sum()) >= len(same) - 2
         assert int((one["iters_run"] > 32).sum()) > 0 or iters <= 32
         for k in ("status", "n_matches", "n_inliers", "inlier_mask", "pose", "transform", "best_hyp", "iters_run", "covariance"):
@@ -132,9 +132,9 @@ def test_two_phase_launch_identical(ctx, golden):
                 assert np.array_equal(one[k], two[k], equal_nan=True), (iters, k)
 
 
-def test_two_phase_launch_identical_in_the_second_call(ctx):
+def test_persistent_scheduler_identical_in_the_second_call(ctx):
     """The second call of estimate_transformation (guess = first result, only pairs whose first call succeeded) through
-    the two-phase launch: every output equals the single-launch run."""
+    the persistent kernel: every output equals the one-warp-per-pair run."""
     A, B = synth.make_robots(2, 40, n_feat=1000, dim=128, seed=1003)
     fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
     rng = np.random.default_rng(8)
@@ -142,13 +142,12 @@ def test_two_phase_launch_identical_in_the_second_call(ctx):
     pairs = same + [(int(rng.integers(40)), int(rng.integers(40))) for _ in range(30)]
     prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY)
     gprm = capi.guess_params(1241, 376, 20.0)
-    ctx.set_pnp_two_phase_min_pairs(1 << 30)
-    one = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gprm)
-    ctx.set_pnp_two_phase_min_pairs(0)
+    ctx.set_pnp_scheduler("per_pair")
     try:
-        two = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gprm)
+        one = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gprm)
     finally:
-        ctx.set_pnp_two_phase_min_pairs(4 * 148)
+        ctx.set_pnp_scheduler("persistent")
+    two = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gprm)
     assert int((one["status"] == 1).sum()) >= len(same) - 3
     for k in one:
         assert np.array_equal(one[k], two[k], equal_nan=True), k
