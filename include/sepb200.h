@@ -32,7 +32,8 @@ extern "C" {
 #define SEPB_OK 0
 #define SEPB_E_INVALID (-1)   /* null pointer / negative size */
 #define SEPB_E_SHAPE (-2)     /* inconsistent shapes or capacity exceeded */
-#define SEPB_E_STATE (-3)     /* handle used before it was filled */
+#define SEPB_E_STATE (-3)     /* handle used before it was filled / NCCL not available for a multi-device group */
+#define SEPB_E_NCCL (-4)      /* an NCCL call failed; text via sepb_group_last_error() */
 
 #define SEPB_DESC_BYTES 32    /* 256-bit binary descriptors (ORB / BRIEF-32), R/msg/Descriptors.msg */
 #define SEPB_MAX_FEATURES 4096
@@ -40,6 +41,7 @@ extern "C" {
 typedef struct sepb_ctx sepb_ctx;        /* one device + one stream + scratch */
 typedef struct sepb_frames sepb_frames;  /* device-resident keyframe feature store of one robot */
 typedef struct sepb_db sepb_db;          /* device-resident NetVLAD descriptor database */
+typedef struct sepb_group sepb_group;    /* the devices of one box + their NCCL communicator */
 
 /* ---- context -------------------------------------------------------------------------- */
 SEPB_API int sepb_ctx_create(int device, sepb_ctx** out);
@@ -275,6 +277,41 @@ SEPB_API int sepb_estimate_transformations_dev(sepb_ctx* ctx, const sepb_frames*
                                                const int32_t* d_pairs, int n_pairs, const sepb_match_params* mprm,
                                                const sepb_pnp_params* pprm, const sepb_guess_params* gprm,
                                                const sepb_verify_out* d_out, int32_t* d_status_pass1);
+
+/* ---- multi-GPU: row-sharded NetVLAD database over NVLink / NVSwitch ---------------------------------
+ * SURVEY.md 8e / BASELINE.json configs[2]: the peer database (received_descriptors, R/scripts/data_handler.py:300-301,
+ * searched whole on every call, :168-170) is partitioned by rows over the GPUs of one box; queries are replicated,
+ * every device searches its shard (sepb_db_set_base gives the shard's rows their GLOBAL indices), the per-shard
+ * [nq][k] lists travel with ONE all-gather (ncclAllGather: 12 bytes per candidate and shard) and are merged on every
+ * device in the (distance, index) order of the single-device search -- results identical to one database.
+ * Verification pairs need no collective: they are independent units (sepb_verify_pairs on each device's share).
+ *
+ *   sepb_group_create(ndev, devices)         one process drives ndev devices: a context per device and ncclCommInitAll
+ *                                            (devices == NULL: 0 .. ndev-1).  ndev == 1 needs no NCCL.
+ *   sepb_group_unique_id + _create_rank      one process per device (e.g. under torchrun): rank 0 makes the id
+ *                                            (ncclGetUniqueId), the launcher hands it to every rank, each wraps ITS
+ *                                            context (ncclCommInitRank); the context stays owned by the caller.
+ * NCCL is loaded at run time (libnccl.so.2); without it multi-device groups fail with SEPB_E_STATE. */
+SEPB_API int sepb_group_create(int ndev, const int* devices, sepb_group** out);
+SEPB_API int sepb_group_unique_id(uint8_t* id128);
+SEPB_API int sepb_group_create_rank(sepb_ctx* ctx, const uint8_t* id128, int rank, int nranks, sepb_group** out);
+SEPB_API void sepb_group_destroy(sepb_group* g);
+SEPB_API int sepb_group_local_size(const sepb_group* g);   /* devices driven by this process */
+SEPB_API int sepb_group_nranks(const sepb_group* g);       /* devices in the communicator = shards */
+SEPB_API sepb_ctx* sepb_group_ctx(sepb_group* g, int i);   /* context of local device i (create databases / stores on it) */
+SEPB_API const char* sepb_group_last_error(const sepb_group* g);
+SEPB_API int sepb_group_nccl_version(void);                /* e.g. 22809; 0 = NCCL not available */
+SEPB_API int64_t sepb_group_last_gather_bytes(const sepb_group* g);   /* bytes received by this process in the last all-gather */
+/* sharded search, device form: dbs[i] = the shard on local device i (created on sepb_group_ctx(g, i));
+ * d_queries[i] [nq][dim] f64, d_out_idx[i] [nq][k] i32, d_out_dist[i] [nq][k] f64 on that device.  Asynchronous: shard
+ * search, all-gather and merge are enqueued on each context's stream.  Every process of the communicator must call it
+ * with the same nq / k.  mode as sepb_netvlad_topk. */
+SEPB_API int sepb_group_netvlad_topk_dev(sepb_group* g, sepb_db* const* dbs, const double* const* d_queries, int nq, int k,
+                                         int mode, int32_t* const* d_out_idx, double* const* d_out_dist);
+/* host form: queries [nq][dim] f64 are copied to local device 0 and broadcast over NVLink to the other local devices;
+ * out_idx / out_dist receive the merged lists (identical on every device); returns when they are in place. */
+SEPB_API int sepb_group_netvlad_topk(sepb_group* g, sepb_db* const* dbs, const double* queries, int nq, int k, int mode,
+                                     int32_t* out_idx, double* out_dist);
 
 /* ---- measurement support (roofline denominators not in MEASURED_PEAKS.json) ----------------
  * Microbenchmarks, best of `reps`.  kind 0: POPC instructions/s (K2's bounding pipe); 1: FP64 FMA/s (K3's);

@@ -144,6 +144,30 @@ def _declare(L):
         f = getattr(L, name)
         f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), vp, vp, vp, vp, vp, vp]
         f.restype = i32
+    L.sepb_group_create.argtypes = [i32, vp, C.POINTER(vp)]
+    L.sepb_group_create.restype = i32
+    L.sepb_group_unique_id.argtypes = [vp]
+    L.sepb_group_unique_id.restype = i32
+    L.sepb_group_create_rank.argtypes = [vp, vp, i32, i32, C.POINTER(vp)]
+    L.sepb_group_create_rank.restype = i32
+    L.sepb_group_destroy.argtypes = [vp]
+    L.sepb_group_destroy.restype = None
+    L.sepb_group_local_size.argtypes = [vp]
+    L.sepb_group_local_size.restype = i32
+    L.sepb_group_nranks.argtypes = [vp]
+    L.sepb_group_nranks.restype = i32
+    L.sepb_group_ctx.argtypes = [vp, i32]
+    L.sepb_group_ctx.restype = vp
+    L.sepb_group_last_error.argtypes = [vp]
+    L.sepb_group_last_error.restype = C.c_char_p
+    L.sepb_group_nccl_version.argtypes = []
+    L.sepb_group_nccl_version.restype = i32
+    L.sepb_group_last_gather_bytes.argtypes = [vp]
+    L.sepb_group_last_gather_bytes.restype = i64
+    L.sepb_group_netvlad_topk_dev.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+    L.sepb_group_netvlad_topk_dev.restype = i32
+    L.sepb_group_netvlad_topk.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+    L.sepb_group_netvlad_topk.restype = i32
 
 
 def _ptr(a):
@@ -161,11 +185,16 @@ OPT_MATCH_TILE = 3
 
 
 class Context:
-    def __init__(self, device: int = 0):
-        self._h = C.c_void_p()
-        rc = lib().sepb_ctx_create(device, C.byref(self._h))
-        if rc != 0:
-            raise SepbError(f"sepb_ctx_create(device={device}) failed with code {rc} (CUDA device required)")
+    def __init__(self, device: int = 0, _borrowed=None):
+        """_borrowed: handle of a context owned by a sepb_group (close() then only closes the children)."""
+        self._owned = _borrowed is None
+        if _borrowed is not None:
+            self._h = C.c_void_p(_borrowed)
+        else:
+            self._h = C.c_void_p()
+            rc = lib().sepb_ctx_create(device, C.byref(self._h))
+            if rc != 0:
+                raise SepbError(f"sepb_ctx_create(device={device}) failed with code {rc} (CUDA device required)")
         # stores / databases created on this context: they hold a raw pointer to it, so close() destroys them first
         self._children = weakref.WeakSet()
 
@@ -211,7 +240,8 @@ class Context:
         if self._h:
             for child in list(getattr(self, "_children", ())):
                 child.close()
-            lib().sepb_ctx_destroy(self._h)
+            if getattr(self, "_owned", True):
+                lib().sepb_ctx_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
@@ -453,3 +483,87 @@ def select_matches(row_min_idx, row_min_dist, netvlad_distance=0.13, max_matches
     if n < 0:
         raise SepbError(f"sepb_select_matches failed: {n}")
     return [(int(a), int(b)) for a, b in out[:n]]
+
+
+class Group:
+    """sepb_group: the devices of one box and their NCCL communicator (include/sepb200.h, multi-GPU section).
+
+    Group(ndev=N)                       one process drives N devices (ncclCommInitAll);
+    Group(ctx=c, rank=r, nranks=N, unique_id=b)   one process per device (ncclCommInitRank); `unique_id` = 128 bytes made
+                                        by Group.unique_id() on rank 0 and handed to every rank by the launcher."""
+
+    def __init__(self, ndev: int | None = None, devices=None, ctx: Context | None = None, rank: int = 0, nranks: int = 1,
+                 unique_id: bytes | None = None):
+        self._h = C.c_void_p()
+        if ctx is None:
+            ndev = len(devices) if devices is not None else int(ndev or 1)
+            dv = np.ascontiguousarray(devices, dtype=np.int32) if devices is not None else None
+            rc = lib().sepb_group_create(ndev, _ptr(dv), C.byref(self._h))
+            if rc != 0:
+                raise SepbError(f"sepb_group_create({ndev}) failed with code {rc} (-3: NCCL not available, -4: NCCL error)")
+            self.ctxs = [Context(_borrowed=lib().sepb_group_ctx(self._h, i)) for i in range(ndev)]
+        else:
+            uid = np.frombuffer(unique_id if unique_id is not None else bytes(128), dtype=np.uint8).copy()
+            assert uid.size == 128
+            rc = lib().sepb_group_create_rank(ctx._h, _ptr(uid), int(rank), int(nranks), C.byref(self._h))
+            if rc != 0:
+                raise SepbError(f"sepb_group_create_rank(rank={rank}, nranks={nranks}) failed with code {rc}")
+            self.ctxs = [ctx]
+        self.nranks = lib().sepb_group_nranks(self._h)
+
+    @staticmethod
+    def unique_id() -> bytes:
+        uid = np.zeros(128, np.uint8)
+        rc = lib().sepb_group_unique_id(_ptr(uid))
+        if rc != 0:
+            raise SepbError(f"sepb_group_unique_id failed with code {rc} (NCCL not available?)")
+        return uid.tobytes()
+
+    @staticmethod
+    def nccl_version() -> int:
+        return int(lib().sepb_group_nccl_version())
+
+    def check(self, rc: int):
+        if rc != 0:
+            raise SepbError(f"sepb group error {rc}: {lib().sepb_group_last_error(self._h).decode()}")
+
+    @property
+    def last_gather_bytes(self) -> int:
+        return int(lib().sepb_group_last_gather_bytes(self._h))
+
+    def _handles(self, dbs):
+        assert len(dbs) == len(self.ctxs)
+        return (C.c_void_p * len(dbs))(*[d._h for d in dbs])
+
+    def netvlad_topk(self, dbs, queries, k=5, mode=1):
+        """Host form: merged (idx [nq,k] i32 GLOBAL row ids, dist [nq,k] f64) over all shards."""
+        q = np.ascontiguousarray(queries, dtype=np.float64).reshape(-1, dbs[0].dim)
+        nq = q.shape[0]
+        idx = np.full((nq, k), -1, np.int32)
+        dist = np.full((nq, k), np.inf, np.float64)
+        self.check(lib().sepb_group_netvlad_topk(self._h, self._handles(dbs), _ptr(q), nq, k, mode, _ptr(idx), _ptr(dist)))
+        return idx, dist
+
+    def netvlad_topk_dev(self, dbs, d_queries, nq, k, mode, d_out_idx, d_out_dist):
+        """Device form: lists of device pointers (ints), one per local device; asynchronous on each context's stream."""
+        n = len(self.ctxs)
+        arr = lambda ps: (C.c_void_p * n)(*[C.c_void_p(int(p)) for p in ps])
+        self.check(lib().sepb_group_netvlad_topk_dev(self._h, self._handles(dbs), arr(d_queries), nq, k, mode,
+                                                     arr(d_out_idx), arr(d_out_dist)))
+
+    def close(self):
+        if self._h:
+            for c in self.ctxs:
+                for child in list(c._children):
+                    child.close()
+            lib().sepb_group_destroy(self._h)
+            self._h = C.c_void_p()
+            for c in self.ctxs:
+                if not c._owned:
+                    c._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -48,9 +48,6 @@
 #ifndef SEPB_JACOBI_BRANCHFREE
 #define SEPB_JACOBI_BRANCHFREE 1   // 0 (developer A/B): the branches of the scalar code
 #endif
-#ifndef SEPB_JACOBI_COMPACT
-#define SEPB_JACOBI_COMPACT 1      // 12 x 12 Jacobi with per-lane pair sequences (jacobi12_compact); 0: the shared loop
-#endif
 #ifndef SEPB_JACOBI_ILP
 // 1: 12 x 12 sweep with two row-disjoint rotations in flight (jacobi12_sweeps_ilp).  Measured on B200 (tools/k3_ab.sh):
 // 10 % fewer cycles per warp but no shorter kernel (26.85 vs 26.57 ms verify), so the plain cyclic loop stays the default.
@@ -487,7 +484,8 @@ CVM_HD inline void jacobi_svd(Heap At, Heap W, Heap Vt) {
 // The sweep loop is warp-uniform: a lane that has converged only sees skipped rotations (no stores) in extra sweeps.
 constexpr int kJacobiIlp = 2;
 constexpr int kJacobiRounds = 35;
-static __device__ const unsigned char kJacobi12Sched[kJacobiRounds][kJacobiIlp][2] = {
+static __constant__ unsigned char kJacobi12Sched[kJacobiRounds][kJacobiIlp][2] = {   // warp-uniform reads: constant cache
+
     {{0, 1}, {0, 0}}, {{0, 2}, {0, 0}}, {{0, 3}, {1, 2}}, {{0, 4}, {1, 3}}, {{0, 5}, {1, 4}},
     {{2, 3}, {0, 6}}, {{1, 5}, {2, 4}}, {{0, 7}, {1, 6}}, {{2, 5}, {3, 4}}, {{0, 8}, {1, 7}},
     {{2, 6}, {3, 5}}, {{0, 9}, {1, 8}}, {{2, 7}, {3, 6}}, {{4, 5}, {0, 10}}, {{1, 9}, {2, 8}},
@@ -612,94 +610,90 @@ __device__ CVM_NOINLINE inline void jacobi12_sweeps_ilp(Heap At, Heap W) {
 }
 #endif
 
-#if defined(__CUDA_ARCH__)
-// The 12 x 12 one-sided Jacobi of M^T M with every lane walking ITS OWN (i, j) sequence.  In the plain loop the 32
-// hypotheses of a warp share the loop counters, so a pair (i, j) costs the whole divide / square-root chain of a
-// rotation as soon as ONE lane has to rotate it -- from the third sweep on almost every pair, although each lane
-// rotates only a few of them.  Here a lane first runs ahead over the pairs it skips (dot product + convergence test
-// only), stops at the next pair it has to rotate, and the warp then executes one rotation for all lanes at once, each
-// on its own rows: the number of rotation chains a warp pays for drops from "pairs any lane rotates" to about
-// "pairs the busiest lane rotates".  Per lane the sequence of operations is exactly that of jacobi_svd_fixed
-// (same order of pairs, same sweeps, same arithmetic), so the results are bit-identical.
-__device__ CVM_NOINLINE inline void jacobi12_compact(Heap At, Heap W) {
-  constexpr int m = 12, n = 12, max_iter = 30;
-  constexpr uint32_t kEl = kHeapStride * 8, kRow = m * kEl;
+#if defined(__CUDACC__)
+// wavefront schedule of the 15 cyclic pairs of a 6 x 6 sweep: pair (i, j) runs in round i + j; the pairs of a round are
+// row-disjoint and every row still meets its rotations in cyclic order, so the result is bit-identical to the serial loop
+constexpr int kJacobi6Rounds = 9;
+static __constant__ unsigned char kJacobi6Sched[kJacobi6Rounds][3][2] = {
+    {{0, 1}, {0, 0}, {0, 0}}, {{0, 2}, {0, 0}, {0, 0}}, {{0, 3}, {1, 2}, {0, 0}}, {{0, 4}, {1, 3}, {0, 0}},
+    {{0, 5}, {1, 4}, {2, 3}}, {{1, 5}, {2, 4}, {0, 0}}, {{2, 5}, {3, 4}, {0, 0}}, {{3, 5}, {0, 0}, {0, 0}},
+    {{4, 5}, {0, 0}, {0, 0}}};
+// JacobiSVDImpl_ for ONE 6 x 6 problem (the normal equations of the refit) with the whole warp on it: lanes 0..2 each
+// rotate one pair of the round.  Rotations on disjoint rows commute exactly, every rotation is the serial code's, so
+// At / W / Vt end up bit-identical to jacobi_svd_rt<6, true>(.., 6) -- in 9 dependent rotation chains per sweep
+// instead of 15.  All lanes pass the SAME scratch (one lane's slice); the whole warp must call it.
+__device__ CVM_NOINLINE inline void jacobi_svd6_warp(Heap At, Heap W, Heap Vt) {
+  constexpr int m = 6, n = 6;
   const double eps = kDblEps * 10;
-  for (int r = 0; r < n; ++r) {
-    double sd = 0;
-    CVM_UNROLL
-    for (int k = 0; k < m; ++k) {
-      const double t = At[r * m + k];
-      sd += t * t;
-    }
-    W[r] = sd;
-  }
-  int i = 0, j = 1, iter = 0;
-  bool changed = false, done = false;
-#if defined(SEPB_K3_PROFILE)
-  if ((threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[6], 1ull);
-#endif
-  // next pair in the cyclic order; at the end of a sweep: stop if nothing rotated, else start the next one
-  auto advance = [&]() {
-    if (++j == n) {
-      ++i;
-      j = i + 1;
-      if (i == n - 1) {
-        if (!changed || ++iter == max_iter) done = true;
-#if defined(SEPB_K3_PROFILE)
-        else if ((threadIdx.x & 31) == 0) atomicAdd(&g_k3_prof[6], 1ull);
-#endif
-        changed = false;
-        i = 0;
-        j = 1;
-      }
-    }
-  };
-  for (;;) {
-    double x[m], y[m], a = 0, b = 0, p = 0;
-    uint32_t ai = 0, aj = 0;
-    bool need = false;
-    // run ahead over the pairs this lane does not rotate
-    while (!done) {
-      ai = At.a + (uint32_t)i * kRow;
-      aj = At.a + (uint32_t)j * kRow;
-      a = lds_f64(W.a + (uint32_t)i * kEl);
-      b = lds_f64(W.a + (uint32_t)j * kEl);
+  const int lane = threadIdx.x & 31;
+  if (lane == 0) {
+    for (int i = 0; i < n; ++i) {
+      double sd = 0;
       CVM_UNROLL
       for (int k = 0; k < m; ++k) {
-        x[k] = lds_f64(ai + k * kEl);
-        y[k] = lds_f64(aj + k * kEl);
+        const double t = At[i * m + k];
+        sd += t * t;
       }
-      p = 0;
-      CVM_UNROLL
-      for (int k = 0; k < m; ++k) p += x[k] * y[k];
-      if (!(fabs(p) <= eps * sqrt(a * b))) {
-        need = true;
-        break;
-      }
-      advance();
-    }
-    if (!__any_sync(0xFFFFFFFFu, need)) break;   // every lane has converged (or hit max_iter)
-    if (need) {
-      double c, s;
-      jacobi_cs(p, a, b, c, s);
-      a = b = 0;
-      CVM_UNROLL
-      for (int k = 0; k < m; ++k) {
-        const double t0 = c * x[k] + s * y[k];
-        const double t1 = -s * x[k] + c * y[k];
-        sts_f64(ai + k * kEl, t0);
-        sts_f64(aj + k * kEl, t1);
-        a += t0 * t0;
-        b += t1 * t1;
-      }
-      sts_f64(W.a + (uint32_t)i * kEl, a);
-      sts_f64(W.a + (uint32_t)j * kEl, b);
-      changed = true;
-      advance();
+      W[i] = sd;
+      for (int k = 0; k < n; ++k) Vt[i * n + k] = 0;
+      Vt[i * n + i] = 1;
     }
   }
-  jacobi_finish<12, 12, false>(At, W, W);
+  __syncwarp();
+  CVM_NOUNROLL
+  for (int iter = 0; iter < 30; ++iter) {
+    bool changed = false;
+    CVM_NOUNROLL
+    for (int r = 0; r < kJacobi6Rounds; ++r) {
+      const int g = lane < 3 ? lane : 0;
+      const int i = kJacobi6Sched[r][g][0], j = kJacobi6Sched[r][g][1];
+      if (lane < 3 && i != j) {
+        const Heap Ai = At.at(i * m), Aj = At.at(j * m);
+        double a = W[i], p = 0, b = W[j];
+        double x[m], y[m];
+        CVM_UNROLL
+        for (int k = 0; k < m; ++k) {
+          x[k] = Ai[k];
+          y[k] = Aj[k];
+        }
+        CVM_UNROLL
+        for (int k = 0; k < m; ++k) p += x[k] * y[k];
+        if (!(fabs(p) <= eps * sqrt(a * b))) {
+          double c, s;
+          jacobi_cs(p, a, b, c, s);
+          a = b = 0;
+          CVM_UNROLL
+          for (int k = 0; k < m; ++k) {
+            const double t0 = c * x[k] + s * y[k];
+            const double t1 = -s * x[k] + c * y[k];
+            Ai[k] = t0;
+            Aj[k] = t1;
+            a += t0 * t0;
+            b += t1 * t1;
+          }
+          W[i] = a;
+          W[j] = b;
+          changed = true;
+          const Heap Vi = Vt.at(i * n), Vj = Vt.at(j * n);
+          double vx[n], vy[n];
+          CVM_UNROLL
+          for (int k = 0; k < n; ++k) {
+            vx[k] = Vi[k];
+            vy[k] = Vj[k];
+          }
+          CVM_UNROLL
+          for (int k = 0; k < n; ++k) {
+            Vi[k] = c * vx[k] + s * vy[k];
+            Vj[k] = -s * vx[k] + c * vy[k];
+          }
+        }
+      }
+      __syncwarp();
+    }
+    if (!__any_sync(0xFFFFFFFFu, changed)) break;
+  }
+  if (lane == 0) jacobi_finish_rt<6, true>(At, W, Vt, 6);
+  __syncwarp();
 }
 #endif
 

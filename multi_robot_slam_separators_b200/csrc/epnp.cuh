@@ -311,9 +311,7 @@ CVM_HD CVM_NOINLINE inline void epnp5(Heap h, const float* o, const float* im, c
     for (int a = 0; a < 12; ++a)
       for (int b = a + 1; b < 12; ++b) At[b * 12 + a] = At[a * 12 + b];  // symmetric: row a of MtM^T == row a of MtM
     K3_T0(t_j);
-#if defined(__CUDA_ARCH__) && SEPB_JACOBI_COMPACT
-    jacobi12_compact(At, h.at(H_W));      // same arithmetic per lane, lanes no longer share the pair counters (cvmath.cuh)
-#elif defined(__CUDA_ARCH__) && SEPB_JACOBI_ILP
+#if defined(__CUDA_ARCH__) && SEPB_JACOBI_ILP
     jacobi12_sweeps_ilp(At, h.at(H_W));   // same arithmetic, three row-disjoint rotations in flight (cvmath.cuh)
 #else
     jacobi_svd<12, 12, false>(At, h.at(H_W), h.at(H_W));

@@ -196,11 +196,40 @@ __device__ __noinline__ void lm_step(cvm::Heap h, const double* JtJ, const doubl
   for (int i = 0; i < 6; ++i) param[i] = prev[i] - x[i];
 }
 
-// every lane needs the new parameters, but only the first kSolveLanes lanes own scratch: lane 0's result is broadcast
-__device__ __forceinline__ void lm_step_warp(cvm::Heap h, const double* JtJ, const double* JtE, int lambda_lg10,
+#ifndef SEPB_LM_WARP_SVD
+#define SEPB_LM_WARP_SVD 1   // 0 (developer A/B): every lane runs the serial 6 x 6 SVD on its own copy
+#endif
+// CvLevMarq::step() for the whole warp: every lane holds the same normal equations and needs the new parameters.
+// h0 = lane 0's scratch slice: ONE copy of the 6 x 6 problem, its Jacobi sweeps spread over lanes (jacobi_svd6_warp).
+__device__ __forceinline__ void lm_step_warp(cvm::Heap h, cvm::Heap h0, const double* JtJ, const double* JtE, int lambda_lg10,
                                              const double* prev, double* param) {
-  if ((threadIdx.x & 31) < kSolveLanes) lm_step(h, JtJ, JtE, lambda_lg10, prev, param);
+#if SEPB_LM_WARP_SVD
+  (void)h;
+  const double lambda = exp(lambda_lg10 * log(10.));
+  cvm::Heap At = h0.at(0), W = h0.at(36), Vt = h0.at(42);
+  if ((threadIdx.x & 31) == 0) {
+    int k = 0;
+    for (int a = 0; a < 6; ++a)
+      for (int b = a; b < 6; ++b) {
+        const double v = JtJ[k++];
+        At[a * 6 + b] = v;
+        At[b * 6 + a] = v;
+      }
+    for (int a = 0; a < 6; ++a) At[a * 6 + a] = At[a * 6 + a] * (1. + lambda);
+  }
   __syncwarp();
+  cvm::jacobi_svd6_warp(At, W, Vt);
+  if ((threadIdx.x & 31) == 0) {
+    double x[6];
+    cvm::svd_backsubst<6, 6>(At, W, Vt, JtE, x);
+    for (int i = 0; i < 6; ++i) param[i] = prev[i] - x[i];
+  }
+  __syncwarp();
+#else
+  (void)h0;
+  lm_step(h, JtJ, JtE, lambda_lg10, prev, param);
+  __syncwarp();
+#endif
 #pragma unroll
   for (int i = 0; i < 6; ++i) param[i] = __shfl_sync(0xFFFFFFFFu, param[i], 0);
 }
@@ -580,14 +609,14 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
   for (;;) {
     // CALC_J
     for (int i = 0; i < 6; ++i) prev[i] = param[i];
-    lm_step_warp(heap, JtJ, JtE, lambda_lg10, prev, param);
+    lm_step_warp(heap, cvm::Heap{ws.heap_base}, JtJ, JtE, lambda_lg10, prev, param);
     if (iters == 0) prev_err_norm = sqrt(err2);
     double dJ[21], dE[6];
     lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
     // CHECK_ERR
     double err_norm = sqrt(err2);
     while (err_norm > prev_err_norm && ++lambda_lg10 <= 16) {
-      lm_step_warp(heap, JtJ, JtE, lambda_lg10, prev, param);
+      lm_step_warp(heap, cvm::Heap{ws.heap_base}, JtJ, JtE, lambda_lg10, prev, param);
       lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
       err_norm = sqrt(err2);
     }
@@ -643,16 +672,24 @@ __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(P
   // ---- helper: chunks of the owners still running, most iterations left first.  The list is empty for good, so every
   //      owner seen from here on is on its last pair (its worker state is never reset again).
   __threadfence();
+  // Claimable work only shrinks once the list is empty (bounds fall, claim counters rise); the one exception is an
+  // owner that popped the last pairs a moment ago and has not published yet (a few microseconds).  So a helper that
+  // finds nothing looks again after 1, 2, 4, 8 us and then leaves: an idle warp must not take issue slots from the
+  // owners on its SM.
+  unsigned backoff = 1000;
   for (;;) {
     int best_rem = 0, best_w = -1;
+    // a racy look at every worker's state (one 16-byte load each); whatever is picked is re-checked after the claim
+#pragma unroll 1
     for (int i = lane; i < q.n_workers; i += 32) {
-      if (ld_volatile(q.wk + 4 * i + 3)) {
-        __threadfence();
-        const int rem = ld_volatile(q.wk + 4 * i + 2) - ld_volatile(q.wk + 4 * i + 1) * kSolveLanes;
-        if (rem > best_rem) {
-          best_rem = rem;
-          best_w = i;
-        }
+      int4 w4;   // pair, next chunk, bound, accepting help
+      asm volatile("ld.volatile.global.v4.s32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(w4.x), "=r"(w4.y), "=r"(w4.z), "=r"(w4.w)
+                   : "l"(q.wk + 4 * i));
+      const int rem = w4.w ? w4.z - w4.y * kSolveLanes : 0;
+      if (rem > best_rem) {
+        best_rem = rem;
+        best_w = i;
       }
     }
 #pragma unroll
@@ -665,9 +702,12 @@ __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(P
     }
     if (best_w < 0) {
       if (ld_volatile_warp(q.ctrl + 2) >= n_listed) break;   // every pair has its result
-      __nanosleep(1000);
+      if (backoff > 8000u) break;
+      __nanosleep(backoff);
+      backoff *= 2;
       continue;
     }
+    backoff = 1000;
     int cc = 0;
     if (lane == 0) cc = atomicAdd(q.wk + 4 * best_w + 1, 1);
     cc = __shfl_sync(0xFFFFFFFFu, cc, 0);

@@ -72,9 +72,9 @@ def merge_on_device(ctx) -> Callable[[torch.Tensor, torch.Tensor], Tuple[torch.T
         _order(lib_stream, cur)
         ctx.check(capi.lib().sepb_topk_merge_dev(ctx._h, C.c_void_p(all_idx.data_ptr()), C.c_void_p(all_dist.data_ptr()),
                                                  lists, Q, k, C.c_void_p(out_i.data_ptr()), C.c_void_p(out_d.data_ptr())))
+        # torch's stream now waits for the merge: the caching allocator may reuse these buffers on it safely (no
+        # record_stream on the library's stream -- it can be destroyed before the tensors are)
         _order(cur, lib_stream)
-        for t in (all_idx, all_dist, out_i, out_d):
-            t.record_stream(lib_stream)
         return out_i, out_d
 
     return merge
