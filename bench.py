@@ -361,6 +361,16 @@ def run_ours(args):
     value = world * P * args.steps / (ms_total_max * 1e-3)
     e2e_value = world * P * e2e_steps / (ms_e2e_max * 1e-3)
 
+    # ---- N > 1: the one path with a data-path collective (configs[2] shape: the peer database row-sharded over the
+    # ranks, ncclAllGather of the top-k lists + merge inside its timed region), measured in the same job so that the
+    # scaling record of the driver holds it; it runs after the headline's timed regions, on its own context
+    sharded_line = None
+    if world > 1 and not args.no_sharded_leg:
+        import copy
+        a2 = copy.copy(args)
+        a2.steps, a2.warmup = max(3, min(args.steps, 10)), 3
+        sharded_line = run_config2(a2, embed=True)
+
     if rank == 0:
         peaks = {}
         try:
@@ -459,6 +469,12 @@ def run_ours(args):
                                     "sample": "%d query rows NN (scipy cdist vs %d rows) + their top-%d = %d pairs through "
                                               "cv2.BFMatcher(k=2)+NNDR+uniqueness and cv2.solvePnPRansac, single thread"
                                               % (args.cpu_queries, args.frames, args.topk, n)}
+        if sharded_line is not None:
+            keep = ("metric", "value", "unit", "ms_per_step", "steps", "scaling", "e2e", "collective", "roofline",
+                    "identical_to_single_database", "checked_queries", "gpu_launches")
+            line["sharded_nn"] = dict({k: sharded_line[k] for k in keep if k in sharded_line},
+                                      workload=sharded_line["config"]["workload"],
+                                      db_rows_per_gpu=sharded_line["config"]["db_rows_per_gpu"])
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -509,7 +525,9 @@ def sharded_nn_setup(rows, queries, dim, seed, rank, world):
     return lo, hi, db, q
 
 
-def run_config2(args):
+def run_config2(args, embed=False):
+    """embed=True: called from the configs[1] run at N > 1 (the driver's scaling run) so that its line carries the sharded
+    search with the NCCL all-gather measured on the same box; returns the line instead of printing it."""
     import ctypes as C
     import torch
     import torch.distributed as dist
@@ -653,7 +671,7 @@ def run_config2(args):
                              "peak_source": ("MEASURED_PEAKS.json" if peaks else "fallback") + " (bf16 burst); algorithmic 2*Q*N_shard*D, "
                                             "the 3-term split costs 3x that on the pipe"},
                 "identical_to_single_database": ok, "checked_queries": int(min(args.check_queries, Q)), "synth_seconds": t_gen}
-        if not args.no_cpu_baseline and world == 1:
+        if not args.no_cpu_baseline and world == 1 and not embed:
             from oracle import find_matches as fm
             n = min(args.cpu_queries, Q)
             t0 = time.perf_counter()
@@ -661,11 +679,17 @@ def run_config2(args):
             sec = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": n / sec, "unit": "queries/s", "cores": 1, "kind": "port",
                                     "sample": "%d queries x %d rows: scipy cdist (f64) + stable argsort top-%d, single thread" % (n, R, k)}
-        print(json.dumps(line), flush=True)
+        if not embed:
+            print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
     grp.close()
     ctx.close()
+    if embed:
+        if rank == 0:
+            line["identical_to_single_database"] = ok
+            return line
+        return None
     if world > 1:
         dist.destroy_process_group()
     if not ok:
@@ -797,8 +821,16 @@ def main():
     ap.add_argument("--db-rows", type=int, default=350000, help="configs[2]: rows of the sharded database (7 peers x 50k)")
     ap.add_argument("--queries", type=int, default=50000, help="configs[2]: query descriptors per step")
     ap.add_argument("--check-queries", type=int, default=4096, help="configs[2]: queries compared with the unsharded search")
+    ap.add_argument("--no-sharded-leg", action="store_true",
+                    help="configs[1] at N > 1: skip the sharded-database leg (NCCL all-gather) appended to the line")
     ap.add_argument("--sizes", default="1000,10000,100000,1000000", help="configs[4]: batch sizes")
     args = ap.parse_args()
+    # stdout carries the JSON line(s) only: libraries that write to fd 1 (NCCL's version banner under NCCL_DEBUG) go to
+    # stderr from here on
+    sys.stdout.flush()
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(out_fd, "w", buffering=1)
     defaults = {1: (10000, 1000, 128, 300), 2: (10000, 1000, 128, 300), 3: (4000, 2000, 4096, 1000), 4: (10000, 1000, 128, 300)}[args.config]
     for name, v in zip(("frames", "feat", "dim", "iterations"), defaults):
         if getattr(args, name) is None:

@@ -54,7 +54,7 @@ void transformToPoseMsg(const float* T, bool is_null, msgs::Pose& msg) {
 GeometricTools::GeometricTools(Device& dev, const CameraModel& cam, int min_inliers, int max_features)
     : dev_(dev), max_feat_(max_features) {
   sepb_pnp_params_init(&pnp_, cam.fx, cam.fy, cam.cx, cam.cy);
-  pnp_.min_inliers = std::max(min_inliers, 5);
+  pnp_.min_inliers = std::max(min_inliers, 4);   // util3d::solvePnPRansac: max(minInliers, 4); four points take the P3P solve
   sepb_guess_params_init(&guess_, cam.width, cam.height);
   match_.nndr = 0.8f;
   match_.nndr_strict = 0;

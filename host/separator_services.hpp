@@ -21,7 +21,6 @@
 
 namespace sepb_host {
 
-namespace msgs = multi_robot_separators;
 
 struct CameraModel {                  // cam_.left(): rectified intrinsics + image size (stereoCamGeometricTools.cpp:56-77)
   double fx = 0, fy = 0, cx = 0, cy = 0;
@@ -53,6 +52,17 @@ class GeometricTools {
   void setGuessWinSize(float px) { guess_.win_size = px; }   // Vis/CorGuessWinSize
   void setIterations(int n) { pnp_.iterations = n; }         // Vis/Iterations
   void setReprojError(double px) { pnp_.reproj_error = px; } // Vis/PnPReprojError
+  // cam_.localTransform(): pose of the (left, optical) camera in the robot base frame -- tf frame_id <- camera frame
+  // (stereoCamGeometricTools.cpp:42-60).  Row-major 3x3 rotation and translation; also re-derives the identity guess.
+  void setLocalTransform(const double* R9, const double* t3) {
+    for (int i = 0; i < 9; ++i) pnp_.local_R[i] = R9[i];
+    for (int i = 0; i < 3; ++i) pnp_.local_t[i] = t3[i];
+    const double I[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    sepb_pnp_set_guess(&pnp_, I);
+  }
+  void setPnPFlags(int flags) { pnp_.flags = flags; }        // Vis/PnPFlags: 0 ITERATIVE, 2 P3P, 5 AP3P (myRegistrationVis.cpp:103)
+  void setPnPRefineIterations(int n) { pnp_.refine_iterations = n; }   // Vis/PnPRefineIterations (:104)
+  void setOpenCV32Semantics(bool on) { pnp_.minimal_model = on ? 1 : 0; }   // return the minimal-set model (OpenCV 3.2)
 
   // Always returns true (the ROS convention: the response is valid); failure of the computation is in-band:
   // res.success = false with a zero pose (MsgConversion.cpp:77-80).  Never throws, never aborts: malformed

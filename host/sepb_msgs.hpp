@@ -9,7 +9,9 @@
 #include <cstdint>
 #include <vector>
 
-namespace multi_robot_separators {
+// (their own namespace: a ROS build also sees the generated multi_robot_separators:: types, ros_node.cpp copies between the two)
+namespace sepb_host {
+namespace msgs {
 
 struct Descriptors {             // msg/Descriptors.msg
   uint16_t rows = 0;
@@ -84,4 +86,5 @@ struct ReceiveSeparators {       // srv/ReceiveSeparators.srv
   };
 };
 
-}  // namespace multi_robot_separators
+}  // namespace msgs
+}  // namespace sepb_host

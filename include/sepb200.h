@@ -176,14 +176,29 @@ SEPB_API int sepb_select_matches(const int32_t* row_min_idx, const double* row_m
 typedef struct sepb_pnp_params {
   double fx, fy, cx, cy;  /* intrinsics of the To camera, cam_.left() (stereoCamGeometricTools.cpp:142-143) */
   int32_t iterations;     /* Vis/Iterations, RTAB-Map default 300 */
-  int32_t min_inliers;    /* Vis/MinInliers = separators_min_inliers (launch default 5); must be >= 5 */
+  int32_t min_inliers;    /* Vis/MinInliers = separators_min_inliers (launch default 5); must be >= 4 */
   double reproj_error;    /* Vis/PnPReprojError, default 2.0 px */
   double confidence;      /* 0.99, hard-coded in util3d::solvePnPRansac */
   double guess_rvec[3];   /* (guess * localTransform)^-1 as Rodrigues vector ... */
   double guess_tvec[3];   /* ... and translation; sepb_pnp_params_init sets the identity guess of pass 1 */
   double local_R[9];      /* camera localTransform rotation (optical -> base), row-major */
   double local_t[3];
+  int32_t flags;          /* Vis/PnPFlags (R/src/myRegistrationVis.cpp:103,1084): SEPB_PNP_ITERATIVE (0, default) = 5-point
+                           * EPnP minimal sets + ITERATIVE refit from the guess; SEPB_PNP_P3P (2) / SEPB_PNP_AP3P (5) =
+                           * 4-point P3P minimal sets + EPnP refit over the consensus set (what cv::solvePnPRansac does
+                           * for these flags).  Exactly four correspondences always take the single P3P solve. */
+  int32_t refine_iterations; /* Vis/PnPRefineIterations (:104,1085; 0 in the pinned RTAB-Map, 1 in older ones): rounds of
+                           * RTAB-Map's refineModel loop after RANSAC -- refit on the inliers, re-select the inliers of ALL
+                           * points with threshold min(reproj_error, refine_sigma * std of the errors) -- until the set stops
+                           * changing.  SEPB_PNP_ITERATIVE only. */
+  double refine_sigma;    /* 3.0, hard-coded in util3d::solvePnPRansac */
+  int32_t minimal_model;  /* 0 (default): OpenCV >= 3.3 semantics, the refit over the inliers is returned; 1: OpenCV 3.2
+                           * semantics (the reference image's version), the winning minimal-set model is returned */
+  int32_t reserved_;
 } sepb_pnp_params;
+#define SEPB_PNP_ITERATIVE 0
+#define SEPB_PNP_P3P 2
+#define SEPB_PNP_AP3P 5
 
 /* defaults above + optical->base localTransform + identity guess (stereoCamGeometricTools.cpp:126) */
 SEPB_API void sepb_pnp_params_init(sepb_pnp_params* p, double fx, double fy, double cx, double cy);
@@ -192,9 +207,9 @@ SEPB_API void sepb_pnp_params_init(sepb_pnp_params* p, double fx, double fy, dou
 SEPB_API void sepb_pnp_set_guess(sepb_pnp_params* p, const double* guess3x4);
 
 /* status per pair */
-#define SEPB_PNP_TOO_FEW 0     /* fewer than min_inliers correspondences: null transform, no RANSAC */
+#define SEPB_PNP_TOO_FEW 0     /* fewer than min_inliers (or than a minimal set of) correspondences: null transform, no RANSAC */
 #define SEPB_PNP_OK 1          /* transform valid (success=true in EstTransform.srv) */
-#define SEPB_PNP_NO_MODEL 2    /* RANSAC found no hypothesis with > 4 inliers */
+#define SEPB_PNP_NO_MODEL 2    /* RANSAC found no hypothesis with more inliers than a minimal set has points */
 #define SEPB_PNP_FEW_INLIERS 3 /* inliers < min_inliers */
 
 /* Outputs (device or host according to the entry point):
@@ -202,8 +217,8 @@ SEPB_API void sepb_pnp_set_guess(sepb_pnp_params* p, const double* guess3x4);
  *   transform[P][12] f32 (3x4 row-major T, From-base <- To-base; zeros when not SEPB_PNP_OK, like
  *   MsgConversion.cpp:77-80), inlier_mask[P][mask_words] u32 over match-list positions (optional),
  *   best_hyp[P], iters_run[P] i32 (optional; index of the winning hypothesis, iterations executed).
- * custom_samples: optional i32 [P][custom_h][5] minimal-sample indices (into the match list)
- *   replacing the built-in replay of cv::RNG(-1) -- "feed the reference's own indices". */
+ * custom_samples: optional i32 [P][custom_h][mp] minimal-sample indices (into the match list; mp = 5, or 4 with the
+ *   P3P flags) replacing the built-in replay of cv::RNG(-1) -- "feed the reference's own indices". */
 SEPB_API int sepb_pnp_ransac_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
                                  int n_pairs, const int32_t* d_n_matches, const uint16_t* d_match_from,
                                  const uint16_t* d_match_to, const int32_t* d_n_unique_to, const sepb_pnp_params* prm,

@@ -40,7 +40,9 @@ class PnpParams(C.Structure):
     _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double),
                 ("iterations", C.c_int32), ("min_inliers", C.c_int32), ("reproj_error", C.c_double),
                 ("confidence", C.c_double), ("guess_rvec", C.c_double * 3), ("guess_tvec", C.c_double * 3),
-                ("local_R", C.c_double * 9), ("local_t", C.c_double * 3)]
+                ("local_R", C.c_double * 9), ("local_t", C.c_double * 3),
+                ("flags", C.c_int32), ("refine_iterations", C.c_int32), ("refine_sigma", C.c_double),
+                ("minimal_model", C.c_int32), ("reserved_", C.c_int32)]
 
 
 class GuessParams(C.Structure):
@@ -52,10 +54,15 @@ class VerifyOut(C.Structure):
                                           "match_to", "inlier_mask", "best_hyp", "iters_run", "covariance")]
 
 
-def pnp_params(fx, fy, cx, cy, iterations=300, min_inliers=5, reproj_error=2.0, confidence=0.99, guess=None):
+PNP_ITERATIVE, PNP_P3P, PNP_AP3P = 0, 2, 5      # sepb_pnp_params.flags (cv::SolvePnPMethod values, Vis/PnPFlags)
+
+
+def pnp_params(fx, fy, cx, cy, iterations=300, min_inliers=5, reproj_error=2.0, confidence=0.99, guess=None,
+               flags=PNP_ITERATIVE, refine_iterations=0, refine_sigma=3.0, minimal_model=False):
     p = PnpParams()
     lib().sepb_pnp_params_init(C.byref(p), fx, fy, cx, cy)
     p.iterations, p.min_inliers, p.reproj_error, p.confidence = iterations, min_inliers, reproj_error, confidence
+    p.flags, p.refine_iterations, p.refine_sigma, p.minimal_model = flags, refine_iterations, refine_sigma, int(minimal_model)
     if guess is not None:
         g = np.ascontiguousarray(np.asarray(guess, dtype=np.float64)[:3, :4])
         lib().sepb_pnp_set_guess(C.byref(p), _ptr(g))
@@ -347,7 +354,7 @@ def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pn
     cs, ch = None, 0
     if custom_samples is not None:
         cs = np.ascontiguousarray(custom_samples, dtype=np.int32)
-        assert cs.ndim == 3 and cs.shape[0] == P and cs.shape[2] == 5
+        assert cs.ndim == 3 and cs.shape[0] == P and cs.shape[2] == (5 if pnp.flags == PNP_ITERATIVE else 4)
         ch = cs.shape[1]
     mp = MatchParams(nndr, 1 if strict else 0)
     fn = lib().sepb_verify_pairs_async if async_ else lib().sepb_verify_pairs

@@ -52,6 +52,7 @@ void sepb_ctx_destroy(sepb_ctx* ctx) {
   if (ctx->scratch) cudaFree(ctx->scratch);
   if (ctx->io) cudaFree(ctx->io);
   if (ctx->table) cudaFree(ctx->table);
+  if (ctx->table4) cudaFree(ctx->table4);
   if (ctx->k3_order) cudaFree(ctx->k3_order);
   cudaStreamDestroy(ctx->stream);
   delete ctx;

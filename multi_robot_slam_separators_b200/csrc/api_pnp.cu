@@ -8,26 +8,36 @@
 
 namespace {
 
-int ensure_table(sepb_ctx* ctx, int max_count, int H) {
-  if (ctx->table && ctx->table_m >= max_count && ctx->table_h >= H) return SEPB_OK;
-  const int m = max_count > ctx->table_m ? max_count : ctx->table_m;
-  const int h = H > ctx->table_h ? H : ctx->table_h;
-  if (ctx->table) {
+int ensure_table(sepb_ctx* ctx, int max_count, int H, int mp) {
+  uint16_t*& tab = mp == 4 ? ctx->table4 : ctx->table;
+  int& tm = mp == 4 ? ctx->table4_m : ctx->table_m;
+  int& th = mp == 4 ? ctx->table4_h : ctx->table_h;
+  if (tab && tm >= max_count && th >= H) return SEPB_OK;
+  const int m = max_count > tm ? max_count : tm;
+  const int h = H > th ? H : th;
+  if (tab) {
     SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(ctx->table);
-    ctx->table = nullptr;
+    cudaFree(tab);
+    tab = nullptr;
   }
-  SEPB_CUDA(ctx, cudaMalloc(&ctx->table, (size_t)(m + 1) * h * 5 * sizeof(uint16_t)));
-  ctx->table_m = m;
-  ctx->table_h = h;
-  return sepb_launch_sample_table(ctx, ctx->table, m, h);
+  SEPB_CUDA(ctx, cudaMalloc(&tab, (size_t)(m + 1) * h * mp * sizeof(uint16_t)));
+  tm = m;
+  th = h;
+  return sepb_launch_sample_table(ctx, tab, m, h, mp);
 }
 
+inline int model_points_of(const sepb_pnp_params* p) { return p->flags == SEPB_PNP_ITERATIVE ? 5 : 4; }
+
 int check_pnp_params(sepb_ctx* ctx, const sepb_pnp_params* p) {
-  SEPB_REQUIRE(ctx, p->min_inliers >= 5, SEPB_E_INVALID);  // 4-point P3P path is not implemented
+  SEPB_REQUIRE(ctx, p->min_inliers >= 4, SEPB_E_INVALID);  // util3d::solvePnPRansac: max(minInliers, 4)
   SEPB_REQUIRE(ctx, p->iterations >= 1 && p->iterations <= 65536, SEPB_E_INVALID);
   SEPB_REQUIRE(ctx, p->confidence > 0 && p->confidence < 1 && p->reproj_error > 0, SEPB_E_INVALID);
   SEPB_REQUIRE(ctx, p->fx > 0 && p->fy > 0, SEPB_E_INVALID);
+  SEPB_REQUIRE(ctx, p->flags == SEPB_PNP_ITERATIVE || p->flags == SEPB_PNP_P3P || p->flags == SEPB_PNP_AP3P, SEPB_E_INVALID);
+  SEPB_REQUIRE(ctx, p->refine_iterations >= 0 && p->refine_iterations <= 64, SEPB_E_INVALID);
+  // RTAB-Map's refine loop calls solvePnP(inliers, flags): P3P / AP3P cannot take more than four points there
+  SEPB_REQUIRE(ctx, p->refine_iterations == 0 || (p->flags == SEPB_PNP_ITERATIVE && p->refine_sigma > 0), SEPB_E_INVALID);
+  SEPB_REQUIRE(ctx, p->minimal_model == 0 || p->minimal_model == 1, SEPB_E_INVALID);
   return SEPB_OK;
 }
 
@@ -42,6 +52,11 @@ void sepb_pnp_params_init(sepb_pnp_params* p, double fx, double fy, double cx, d
   p->min_inliers = 5;
   p->reproj_error = 2.0;
   p->confidence = 0.99;
+  p->flags = SEPB_PNP_ITERATIVE;
+  p->refine_iterations = 0;
+  p->refine_sigma = 3.0;
+  p->minimal_model = 0;
+  p->reserved_ = 0;
   // optical (x right, y down, z forward) -> base (x forward, y left, z up)
   const double L[9] = {0, 0, 1, -1, 0, 0, 0, -1, 0};
   for (int i = 0; i < 9; ++i) p->local_R[i] = L[i];
@@ -86,12 +101,14 @@ static int pnp_ransac_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   if (rc) return rc;
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
   if (!d_custom_samples) {
-    rc = ensure_table(ctx, from->max_feat, prm->iterations);
+    rc = ensure_table(ctx, from->max_feat, prm->iterations, model_points_of(prm));
     if (rc) return rc;
   }
+  const bool four = model_points_of(prm) == 4;
   FramesUse use(ctx, from, to);
   return sepb_launch_pnp_ransac(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from,
-                                d_match_to, d_n_unique_to, ctx->table, ctx->table_h, d_custom_samples, custom_h, d_guess,
+                                d_match_to, d_n_unique_to, four ? ctx->table4 : ctx->table, four ? ctx->table4_h : ctx->table_h,
+                                d_custom_samples, custom_h, d_guess,
                                 d_only_if_ok, prm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask, mask_words,
                                 d_best_hyp, d_iters_run);
 }
@@ -190,7 +207,7 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   const size_t b_nu = align_up(P * 4, 256) + (gprm ? align_up(P * 48, 256) : 0);
   const size_t b_pairs = align_up(P * 8, 256), b_i = align_up(P * 4, 256), b_pose = align_up(P * 48, 256),
                b_T = align_up(P * 48, 256), b_m = align_up(P * F * 2, 256), b_mask = align_up(P * MW * 4, 256),
-               b_cs = custom_samples ? align_up(P * custom_h * 5 * 4, 256) : 0;
+               b_cs = custom_samples ? align_up(P * custom_h * model_points_of(pprm) * 4, 256) : 0;
   const size_t b_cov = out->covariance ? align_up(P * 288, 256) : 0;
   const size_t total = b_nu + b_pairs + 6 * b_i + b_pose + b_T + 2 * b_m + b_mask + b_cs + b_cov;
   uint8_t* s = (uint8_t*)sepb_scratch(ctx, total);
@@ -213,7 +230,7 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   int32_t* d_cs = nullptr;
   if (custom_samples) {
     d_cs = (int32_t*)s;
-    SEPB_CUDA(ctx, cudaMemcpyAsync(d_cs, custom_samples, P * custom_h * 5 * 4, cudaMemcpyHostToDevice, ctx->stream));
+    SEPB_CUDA(ctx, cudaMemcpyAsync(d_cs, custom_samples, P * custom_h * model_points_of(pprm) * 4, cudaMemcpyHostToDevice, ctx->stream));
   }
   SEPB_CUDA(ctx, cudaMemcpyAsync(d_pairs, pairs, P * 8, cudaMemcpyHostToDevice, ctx->stream));
   rc = verify_dev_impl(ctx, from, to, d_pairs, n_pairs, mprm, pprm, gprm, d_cs, custom_h, &d, gprm ? d_st1 : nullptr);

@@ -24,9 +24,11 @@ struct sepb_ctx {
   void* io = nullptr;
   size_t io_bytes = 0;
   int sm_count = 148;
-  // cv::RNG(-1) minimal-sample index table [count][table_h][5] (K3)
+  // cv::RNG(-1) minimal-sample index tables [count][table_h][mp] (K3): [0] 5-point sets, [1] 4-point sets (P3P flags)
   uint16_t* table = nullptr;
   int table_m = -1, table_h = 0;
+  uint16_t* table4 = nullptr;
+  int table4_m = -1, table4_h = 0;
   // K3 work queue (pair list, worker states, chunk slots of the helper protocol; pnp_ransac.cu), grow-only, in int32 units
   int32_t* k3_order = nullptr;
   size_t k3_order_cap = 0;
@@ -205,7 +207,7 @@ int sepb_launch_pose_cov(sepb_ctx* ctx, FramesView from, FramesView to, const in
                          const int32_t* d_status, const int32_t* d_n_matches, const uint16_t* d_match_from,
                          const uint16_t* d_match_to, const uint32_t* d_inlier_mask, int mask_words,
                          const float* d_transform, double* d_cov);
-int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H);
+int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H, int model_points);
 int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                            const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,
                            const int32_t* d_n_unique_to, const uint16_t* d_table, int table_h,

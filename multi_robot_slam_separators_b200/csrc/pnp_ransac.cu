@@ -29,6 +29,7 @@ __device__ unsigned long long g_k3_prof[8];
 
 #include "epnp.cuh"
 #include "pnp_geom.cuh"
+#include "p3p.cuh"
 
 namespace {
 
@@ -49,21 +50,24 @@ struct PnpKernelParams {
   double rvec0[3], tvec0[3];   // guess, camera frame (== (guess * local)^-1)
   double local_R[9], local_t[3];
   int table_h;                 // hypotheses per row of the sample table
+  int minimal_model;           // OpenCV 3.2 semantics: return the winning minimal-set model instead of the refit
+  int refine_iterations;       // RTAB-Map refineModel rounds after the refit (ITERATIVE only)
+  float refine_sigma, reproj_error;
 };
 
-// getSubset index stream: table[count][h][5]; thread per count value
-__global__ void sample_table_kernel(uint16_t* table, int max_count, int H) {
+// getSubset index stream: table[count][h][mp] (mp = model points: 5, or 4 with the P3P flags); thread per count value
+__global__ void sample_table_kernel(uint16_t* table, int max_count, int H, int mp) {
   const int count = blockIdx.x * blockDim.x + threadIdx.x;
   if (count > max_count) return;
-  uint16_t* row = table + (size_t)count * H * 5;
-  if (count < 5) {
-    for (int i = 0; i < H * 5; ++i) row[i] = 0;
+  uint16_t* row = table + (size_t)count * H * mp;
+  if (count < mp) {
+    for (int i = 0; i < H * mp; ++i) row[i] = 0;
     return;
   }
   cvm::Rng rng(0xFFFFFFFFFFFFFFFFULL);
   for (int h = 0; h < H; ++h) {
     int idx[5];
-    for (int i = 0; i < 5; ++i) {
+    for (int i = 0; i < mp; ++i) {
       int v;
       bool dup;
       do {
@@ -72,7 +76,7 @@ __global__ void sample_table_kernel(uint16_t* table, int max_count, int H) {
         for (int j = 0; j < i; ++j) dup |= idx[j] == v;
       } while (dup);
       idx[i] = v;
-      row[h * 5 + i] = (uint16_t)v;
+      row[h * mp + i] = (uint16_t)v;
     }
   }
 }
@@ -234,6 +238,115 @@ __device__ __forceinline__ void lm_step_warp(cvm::Heap h, cvm::Heap h0, const do
   for (int i = 0; i < 6; ++i) param[i] = __shfl_sync(0xFFFFFFFFu, param[i], 0);
 }
 
+// solvePnP(points under `mask`, SOLVEPNP_ITERATIVE, useExtrinsicGuess) == CvLevMarq started at `param`; whole warp,
+// every lane ends with the same refined [rvec | tvec] in `param`
+__device__ __noinline__ void lm_refit(const Corr& cr, const uint32_t* mask, int M, const cvm::Intrinsics& K, cvm::Heap heap,
+                                      cvm::Heap h0, double* param) {
+  double prev[6], JtJ[21], JtE[6];
+  for (int i = 0; i < 6; ++i) prev[i] = param[i];
+  int lambda_lg10 = -3, iters = 0;
+  double err2 = 0, prev_err_norm = 0;
+  const int max_iter = 20;
+  const double eps = 1.1920928955078125e-07;  // FLT_EPSILON
+  lm_accumulate(cr, mask, M, K, param, true, JtJ, JtE, err2);  // STARTED -> CALC_J
+  for (;;) {
+    // CALC_J
+    for (int i = 0; i < 6; ++i) prev[i] = param[i];
+    lm_step_warp(heap, h0, JtJ, JtE, lambda_lg10, prev, param);
+    if (iters == 0) prev_err_norm = sqrt(err2);
+    double dJ[21], dE[6];
+    lm_accumulate(cr, mask, M, K, param, false, dJ, dE, err2);
+    // CHECK_ERR
+    double err_norm = sqrt(err2);
+    while (err_norm > prev_err_norm && ++lambda_lg10 <= 16) {
+      lm_step_warp(heap, h0, JtJ, JtE, lambda_lg10, prev, param);
+      lm_accumulate(cr, mask, M, K, param, false, dJ, dE, err2);
+      err_norm = sqrt(err2);
+    }
+    lambda_lg10 = max(lambda_lg10 - 1, -16);
+    double dn = 0, pn = 0;
+    for (int i = 0; i < 6; ++i) {
+      dn += (param[i] - prev[i]) * (param[i] - prev[i]);
+      pn += prev[i] * prev[i];
+    }
+    if (++iters >= max_iter || sqrt(dn) / (sqrt(pn) + cvm::kDblEps) < eps) break;
+    prev_err_norm = err_norm;
+    lm_accumulate(cr, mask, M, K, param, true, JtJ, JtE, err2);
+  }
+}
+
+// RTAB-Map util3d::solvePnPRansac, `refineIterations > 0` (a clone of PCL's SampleConsensus::refineModel; SURVEY.md A.3
+// step 3, reached from R/src/myRegistrationVis.cpp:1085): refit on the current inliers from the current pose, re-select
+// the inliers of ALL points with the current threshold (strict <, on the f32 pixel distance), shrink the threshold to
+// min(reprojError, sigma * std of all errors), until the set stops changing, oscillates, or the round limit is hit.
+// prev / other: the two mask buffers (prev holds the RANSAC consensus set on entry).  On return *final points at the
+// buffer that refineModel leaves in `inliers` (the set the last fit ran on) and the pose is in `param`.
+__device__ __noinline__ int refine_model(const Corr& cr, int M, const PnpKernelParams& prm, cvm::Heap heap, cvm::Heap h0,
+                                         uint32_t* prev, uint32_t* other, int prev_count, double* param,
+                                         const uint32_t** final_mask) {
+  const int lane = threadIdx.x & 31;
+  float thr = prm.reproj_error;
+  int it = 0, n_sizes = 0, sizes[4] = {0, 0, 0, 0};
+  bool changed = false;
+  uint32_t* cur_new = other;
+  int new_count = 0;
+  for (;;) {
+    lm_refit(cr, prev, M, prm.K, heap, h0, param);
+    sizes[0] = sizes[1]; sizes[1] = sizes[2]; sizes[2] = sizes[3]; sizes[3] = prev_count;
+    ++n_sizes;
+    double R[9];
+    cvm::rodrigues_vec_to_mat(param, R, nullptr);
+    // errors of all points: new inlier set, and their sum in index order (uMean is a sequential f32 sum)
+    float sum = 0.f;
+    new_count = 0;
+    for (int base = 0; base < M; base += 32) {
+      const int m = base + lane;
+      float o3[3], i2[2];
+      cr.load(min(m, M - 1), o3, i2);
+      const float e = sqrtf(cvm::reproj_err_f32(R, param + 3, prm.K, o3, i2));
+      const uint32_t b = __ballot_sync(0xFFFFFFFFu, e < thr && m < M);
+      if (lane == 0) cur_new[base >> 5] = b;
+      new_count += __popc(b);
+      for (int k = 0; k < 32 && base + k < M; ++k) sum += __shfl_sync(0xFFFFFFFFu, e, k);
+    }
+    __syncwarp();
+    bool to_cond = false;
+    if (new_count < prm.min_inliers) {
+      ++it;
+      if (it >= prm.refine_iterations) break;
+      to_cond = true;
+    }
+    if (!to_cond) {
+      const float mean = sum / (float)(unsigned)M;
+      float sum2 = 0.f;
+      for (int base = 0; base < M; base += 32) {
+        const int m = base + lane;
+        float o3[3], i2[2];
+        cr.load(min(m, M - 1), o3, i2);
+        const float e = sqrtf(cvm::reproj_err_f32(R, param + 3, prm.K, o3, i2));
+        const float d2 = (e - mean) * (e - mean);
+        for (int k = 0; k < 32 && base + k < M; ++k) sum2 += __shfl_sync(0xFFFFFFFFu, d2, k);
+      }
+      const float variance = M > 1 ? sum2 / (float)(unsigned)(M - 1) : 0.f;
+      thr = fminf(prm.reproj_error, prm.refine_sigma * sqrtf(variance));
+      changed = false;
+      {   // std::swap(prev_inliers, new_inliers)
+        uint32_t* t = prev; prev = cur_new; cur_new = t;
+        const int c = prev_count; prev_count = new_count; new_count = c;
+      }
+      if (new_count != prev_count) {
+        if (n_sizes >= 4 && sizes[3] == sizes[1] && sizes[2] == sizes[0]) break;   // oscillating between two sizes
+        changed = true;
+      } else {
+        for (int w = 0; w < (M + 31) / 32; ++w) changed = changed || prev[w] != cur_new[w];
+      }
+    }
+    if (!(changed && ++it < prm.refine_iterations)) break;
+  }
+  *final_mask = cur_new;
+  return new_count;
+}
+
 // ---- K3 scheduling ---------------------------------------------------------------------------------------------
 // A pair's cost is its number of 32-hypothesis chunks (1..10 at 300 iterations), unknown until RANSAC runs, and one
 // chunk is ~0.7 ms of serial f64 work for a warp: a pair that needs every chunk is a 7 ms dependency chain, longer than
@@ -328,7 +441,7 @@ __device__ __forceinline__ PairIn load_pair(const PnpArgs& a, int pair, float* s
 
 // myRegistrationVis.cpp:1069-1070 and estimateMotion3DTo2D: >= minInliers on every side (and a minimal set)
 __device__ __forceinline__ bool pair_runs(const PnpArgs& a, const PairIn& in) {
-  return !(in.M < a.prm.min_inliers || in.nf < a.prm.min_inliers || in.nu < a.prm.min_inliers || in.M < 5);
+  return !(in.M < a.prm.min_inliers || in.nf < a.prm.min_inliers || in.nu < a.prm.min_inliers || in.M < 4);
 }
 
 // result of one pair (one thread)
@@ -380,28 +493,42 @@ struct WarpScratch {
   uint32_t* s_mask;     // [2][kMaskWords] ping-pong inlier masks
 };
 
-// ---- solve: lane <-> hypothesis.  h_cap: hypotheses at or past it are never consumed (their lanes redo h_cap - 1)
+// ---- solve: lane <-> hypothesis.  h_cap: hypotheses at or past it are never consumed (their lanes redo h_cap - 1).
+// MP = model points: 5 -> EPnP, 4 -> P3P (a set without a solution gets a NaN translation: it scores no inlier, which
+// is what the skipped iteration of RANSACPointSetRegistrator::run amounts to).  rv_out (optional): the model as rvec.
+template <int MP>
 __device__ __forceinline__ void solve_chunk(const PnpArgs& a, const PairIn& in, const WarpScratch& ws, int chunk0, int h_cap,
-                                            double* Rh, double* th) {
+                                            double* Rh, double* th, double* rv_out = nullptr) {
   const int lane = threadIdx.x & 31;
   const cvm::Heap heap{ws.heap_base + lane};
   int h = chunk0 + lane;
   if (h >= h_cap) h = h_cap - 1;
-  float o[15], im[10];
-  for (int i = 0; i < 5; ++i) {
-    const int s = a.custom_samples ? a.custom_samples[((size_t)in.pair * a.custom_h + h) * 5 + i]
-                                   : a.table[((size_t)in.M * a.prm.table_h + h) * 5 + i];
+  float o[3 * MP], im[2 * MP];
+  for (int i = 0; i < MP; ++i) {
+    const int s = a.custom_samples ? a.custom_samples[((size_t)in.pair * a.custom_h + h) * MP + i]
+                                   : a.table[((size_t)in.M * a.prm.table_h + h) * MP + i];
     in.cr.load(min(max(s, 0), in.M - 1), o + 3 * i, im + 2 * i);
   }
   __syncwarp();   // every lane has read its samples from the staging area before a solve overwrites it
   double R0[9], rv[3];
   K3_T0(t_e);
-  cvm::epnp5(heap, o, im, a.prm.K, R0, th);
+  bool solved = true;
+  if (MP == 5) {
+    cvm::epnp5(heap, o, im, a.prm.K, R0, th);
+  } else {
+    solved = cvm::p3p4(o, im, a.prm.K, R0, th);
+    if (!solved) {
+      for (int i = 0; i < 9; ++i) R0[i] = (i % 4 == 0) ? 1.0 : 0.0;
+    }
+  }
   K3_ACC(0, t_e);
   K3_T0(t_r);
   cvm::rodrigues_mat_to_vec(heap, R0, rv);   // runKernel hands the model on as rvec
   cvm::rodrigues_vec_to_mat(rv, Rh, nullptr);  // projectPoints turns it back into a matrix
   K3_ACC(1, t_r);
+  if (!solved) th[0] = th[1] = th[2] = __longlong_as_double(0x7FF8000000000000LL);
+  if (rv_out)
+    for (int i = 0; i < 3; ++i) rv_out[i] = rv[i];
   __syncwarp();
   in.cr.stage(ws.stage_buf, in.M);   // the solve overwrote the staging area
 }
@@ -433,11 +560,12 @@ __device__ __forceinline__ int score_one(const PnpArgs& a, const PairIn& in, con
 }
 
 // a whole chunk for somebody else's scan: solve, score every hypothesis, leave counts and poses in the owner's slot
+template <int MP>
 __device__ __noinline__ void chunk_to_slot(const PnpArgs& a, const PnpQueue& q, const PairIn& in, const WarpScratch& ws,
                                            int owner, int cc, uint32_t* cand) {
   const int lane = threadIdx.x & 31;
   double Rh[9], th[3];
-  solve_chunk(a, in, ws, cc * kSolveLanes, a.prm.iterations, Rh, th);
+  solve_chunk<MP>(a, in, ws, cc * kSolveLanes, a.prm.iterations, Rh, th);
   K3_T0(t_s);
   int mygood = 0;
   for (int k = 0; k < kSolveLanes; ++k) {
@@ -468,6 +596,7 @@ __device__ __noinline__ void chunk_to_slot(const PnpArgs& a, const PnpQueue& q, 
 
 // One keyframe pair, one warp.  worker >= 0: persistent kernel (chunks are claimed from the owner's counter and may
 // arrive from helpers); worker < 0: the warp runs every chunk itself.
+template <int MP>
 __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, int worker, int pair, const WarpScratch& ws) {
   const PnpKernelParams& prm = a.prm;
   const int lane = threadIdx.x & 31;
@@ -480,7 +609,25 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
   if (out_mask)
     for (int w = lane; w < a.mask_words; w += 32) out_mask[w] = 0;
 
-  if (M == 5) {  // count == modelPoints: one EPnP over all five, no refit, all inliers
+  if (M == 4) {  // count == 4: cv::solvePnPRansac turns to ONE P3P solve over the four, whatever the flags; all inliers
+    float o[12], im[8];
+    for (int i = 0; i < 4; ++i) cr.load_global(i, o + 3 * i, im + 2 * i);
+    double R[9], p6[6];
+    for (int i = 0; i < 6; ++i) p6[i] = in.g[i];
+    const bool ok = cvm::p3p4(o, im, prm.K, R, p6 + 3);
+    if (ok) cvm::rodrigues_mat_to_vec(heap, R, p6);
+    if (lane == 0) {
+      if (!ok) {
+        for (int i = 0; i < 3; ++i) p6[3 + i] = in.g[3 + i];
+        write_result(a, pair, 2, 0, p6, -1, 1);
+      } else {
+        if (out_mask) out_mask[0] = 0xFu;
+        write_result(a, pair, 4 >= prm.min_inliers ? 1 : 3, 4, p6, 0, 1);
+      }
+    }
+    return;
+  }
+  if (MP == 5 && M == 5) {  // count == modelPoints: one EPnP over all five, no refit, all inliers
     float o[15], im[10];
     for (int i = 0; i < 5; ++i) cr.load_global(i, o + 3 * i, im + 2 * i);
     double R[9], p6[6] = {0, 0, 0, 0, 0, 0};
@@ -520,7 +667,7 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
       // ---- nobody is helping: solve, then score in RANSAC order with the live early exit
       const int chunk = my * kSolveLanes;
       double Rh[9], th[3];
-      solve_chunk(a, in, ws, chunk, niters, Rh, th);
+      solve_chunk<MP>(a, in, ws, chunk, niters, Rh, th);
       K3_T0(t_s);
       for (int k = 0; k < kSolveLanes; ++k) {
         hk = chunk + k;
@@ -531,12 +678,12 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
 #pragma unroll
         for (int i = 0; i < 3; ++i) t[i] = __shfl_sync(0xFFFFFFFFu, th[i], k);
         const int good = score_one(a, in, R, t, s_mask + (cur ^ 1) * kMaskWords);
-        if (good > max(best_good, 4)) {
+        if (good > max(best_good, MP - 1)) {
           cur ^= 1;
           best_good = good;
           best_h = hk;
           best_in_smem = true;
-          niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, 5, niters);
+          niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, MP, niters);
         }
         hk = hk + 1;
       }
@@ -547,7 +694,7 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
       c_next = my + 1;
     } else {
       // ---- helpers hold chunks c_next .. my-1: do chunk `my` the way they do, then scan everything in order
-      if (my * kSolveLanes < niters) chunk_to_slot(a, q, in, ws, worker, my, s_mask + (cur ^ 1) * kMaskWords);
+      if (my * kSolveLanes < niters) chunk_to_slot<MP>(a, q, in, ws, worker, my, s_mask + (cur ^ 1) * kMaskWords);
       for (int cc = c_next; cc <= my && cc * kSolveLanes < niters; ++cc) {
         const size_t slot = (size_t)worker * q.max_chunks + cc;
         while (ld_volatile_warp(q.slot_ready + slot) == 0) __nanosleep(200);
@@ -557,11 +704,11 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
           hk = cc * kSolveLanes + k;
           if (hk >= niters) break;
           const int good = __shfl_sync(0xFFFFFFFFu, gk, k);
-          if (good > max(best_good, 4)) {
+          if (good > max(best_good, MP - 1)) {
             best_good = good;
             best_h = hk;
             best_in_smem = false;
-            niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, 5, niters);
+            niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, MP, niters);
           }
           hk = hk + 1;
         }
@@ -598,40 +745,51 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
   if (out_mask)
     for (int w = lane; w < (M + 31) / 32; w += 32) out_mask[w] = best[w];
 
-  // ---- refit: solvePnP(inliers, ITERATIVE, useExtrinsicGuess) == CvLevMarq from the caller's guess
-  double param[6], prev[6], JtJ[21], JtE[6];
-  for (int i = 0; i < 6; ++i) param[i] = prev[i] = in.g[i];
-  int lambda_lg10 = -3, iters = 0;
-  double err2 = 0, prev_err_norm = 0;
-  const int max_iter = 20;
-  const double eps = 1.1920928955078125e-07;  // FLT_EPSILON
-  lm_accumulate(cr, best, M, prm.K, param, true, JtJ, JtE, err2);  // STARTED -> CALC_J
-  for (;;) {
-    // CALC_J
-    for (int i = 0; i < 6; ++i) prev[i] = param[i];
-    lm_step_warp(heap, cvm::Heap{ws.heap_base}, JtJ, JtE, lambda_lg10, prev, param);
-    if (iters == 0) prev_err_norm = sqrt(err2);
-    double dJ[21], dE[6];
-    lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
-    // CHECK_ERR
-    double err_norm = sqrt(err2);
-    while (err_norm > prev_err_norm && ++lambda_lg10 <= 16) {
-      lm_step_warp(heap, cvm::Heap{ws.heap_base}, JtJ, JtE, lambda_lg10, prev, param);
-      lm_accumulate(cr, best, M, prm.K, param, false, dJ, dE, err2);
-      err_norm = sqrt(err2);
+  double param[6];
+  int final_good = best_good;
+  if (prm.minimal_model) {
+    // OpenCV 3.2 (the reference image's version): solvePnPRansac hands back the winning minimal-set model itself
+    double Rh[9], th[3], rv[3];
+    solve_chunk<MP>(a, in, ws, best_h, best_h + 1, Rh, th, rv);   // every lane redoes hypothesis best_h
+    for (int i = 0; i < 3; ++i) {
+      param[i] = rv[i];
+      param[3 + i] = th[i];
     }
-    lambda_lg10 = max(lambda_lg10 - 1, -16);
-    double dn = 0, pn = 0;
-    for (int i = 0; i < 6; ++i) {
-      dn += (param[i] - prev[i]) * (param[i] - prev[i]);
-      pn += prev[i] * prev[i];
+  } else if (MP == 4) {
+    // ---- refit, P3P / AP3P flags: solvePnP(inliers as f64, SOLVEPNP_EPNP) -- EPnP over the whole consensus set (the
+    // guess is not used).  Every lane runs the same serial solve on its own scratch; points come through the mask.
+    int w = 0;
+    uint32_t bits = 0;
+    double R[9];
+    cvm::epnp_n(heap, best_good, [&](int i, double* o3, double* px) {
+      if (i == 0) {
+        w = 0;
+        bits = best[0];
+      }
+      while (!bits) bits = best[++w];
+      const int m = w * 32 + __ffs(bits) - 1;
+      bits &= bits - 1;
+      float of[3], i2[2];
+      cr.load_global(m, of, i2);
+      o3[0] = of[0]; o3[1] = of[1]; o3[2] = of[2];
+      px[0] = i2[0]; px[1] = i2[1];
+    }, prm.K, R, param + 3);
+    cvm::rodrigues_mat_to_vec(heap, R, param);
+  } else {
+    // ---- refit: solvePnP(inliers, ITERATIVE, useExtrinsicGuess) == CvLevMarq from the caller's guess
+    for (int i = 0; i < 6; ++i) param[i] = in.g[i];
+    lm_refit(cr, best, M, prm.K, heap, cvm::Heap{ws.heap_base}, param);
+    if (prm.refine_iterations > 0 && best_good >= prm.min_inliers) {
+      const uint32_t* fin = best;
+      final_good = refine_model(cr, M, prm, heap, cvm::Heap{ws.heap_base}, s_mask + cur * kMaskWords,
+                                s_mask + (cur ^ 1) * kMaskWords, best_good, param, &fin);
+      __syncwarp();
+      if (out_mask)
+        for (int w = lane; w < (M + 31) / 32; w += 32) out_mask[w] = fin[w];
     }
-    if (++iters >= max_iter || sqrt(dn) / (sqrt(pn) + cvm::kDblEps) < eps) break;
-    prev_err_norm = err_norm;
-    lm_accumulate(cr, best, M, prm.K, param, true, JtJ, JtE, err2);
   }
   K3_ACC(3, t_lm);
-  if (lane == 0) write_result(a, pair, best_good >= prm.min_inliers ? 1 : 3, best_good, param, best_h, hk);
+  if (lane == 0) write_result(a, pair, final_good >= prm.min_inliers ? 1 : 3, final_good, param, best_h, hk);
 }
 
 constexpr size_t kWarpBytes = (size_t)cvm::kEpnpHeap * kSolveLanes * 8 + 2 * kMaskWords * 4;
@@ -643,12 +801,14 @@ __device__ __forceinline__ WarpScratch warp_scratch(uint8_t* smem_raw) {
 }
 
 // reference scheduling (SEPB_PNP_SCHED_PER_PAIR): one one-warp CTA per listed pair, every chunk by that warp
+template <int MP>
 __global__ void __launch_bounds__(kWarp, 5) pnp_ransac_kernel(PnpArgs a, PnpQueue q) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   if ((int)blockIdx.x >= q.ctrl[1]) return;
-  run_pair(a, q, -1, q.list[blockIdx.x], warp_scratch(smem_raw));
+  run_pair<MP>(a, q, -1, q.list[blockIdx.x], warp_scratch(smem_raw));
 }
 
+template <int MP>
 __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(PnpArgs a, PnpQueue q) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const WarpScratch ws = warp_scratch(smem_raw);
@@ -661,7 +821,7 @@ __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(P
     if (lane == 0) slot = atomicAdd(&q.ctrl[0], 1);
     slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
     if (slot >= n_listed) break;
-    run_pair(a, q, worker, q.list[slot], ws);
+    run_pair<MP>(a, q, worker, q.list[slot], ws);
     __syncwarp();
     if (lane == 0) {
       __threadfence();
@@ -719,7 +879,7 @@ __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(P
     const int pair = ld_volatile_warp(q.wk + 4 * best_w);
     const PairIn in = load_pair(a, pair, ws.stage_buf);
     in.cr.stage(ws.stage_buf, in.M);
-    chunk_to_slot(a, q, in, ws, best_w, cc, ws.s_mask);
+    chunk_to_slot<MP>(a, q, in, ws, best_w, cc, ws.s_mask);
   }
 }
 
@@ -743,9 +903,9 @@ extern "C" SEPB_API int sepb_debug_k3_prof(unsigned long long* out8, int reset) 
 #endif
 }
 
-int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H) {
+int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H, int model_points) {
   const int threads = 128;
-  sample_table_kernel<<<(max_count + 1 + threads - 1) / threads, threads, 0, ctx->stream>>>(d_table, max_count, H);
+  sample_table_kernel<<<(max_count + 1 + threads - 1) / threads, threads, 0, ctx->stream>>>(d_table, max_count, H, model_points);
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());
   return SEPB_OK;
@@ -786,6 +946,11 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   }
   for (int i = 0; i < 9; ++i) k.local_R[i] = p->local_R[i];
   k.table_h = table_h;
+  k.minimal_model = p->minimal_model;
+  k.refine_iterations = p->refine_iterations;
+  k.refine_sigma = (float)p->refine_sigma;
+  k.reproj_error = (float)p->reproj_error;
+  const bool four = p->flags != SEPB_PNP_ITERATIVE;
   a.status = d_status;
   a.n_inliers = d_n_inliers;
   a.pose = d_pose;
@@ -798,8 +963,11 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   size_t smem = kWarpBytes;
   if (const char* e = sepb_dev_env("SEPB_K3_PAD_SMEM")) smem += (size_t)atoi(e);   // developer switch: fewer resident CTAs per SM
   if (!ctx->cfg_pnp) {
-    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem + 200000 > 232448 ? 232448 : smem + 200000)));
-    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kPersistWarps * kWarpBytes)));
+    const int big = (int)(smem + 200000 > 232448 ? 232448 : smem + 200000);
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_ransac_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_persist_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kPersistWarps * kWarpBytes)));
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(pnp_persist_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kPersistWarps * kWarpBytes)));
     ctx->cfg_pnp = true;
   }
   // queue memory (grow-only): zeroed head {ctrl, wk, slot_ready} | list | slot_good | slot_rt
@@ -841,9 +1009,11 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
     const long long units = (long long)n_pairs * (max_chunks > 0 ? max_chunks : 1);
     const int ctas = (int)std::min<long long>(ctx->sm_count, (units + kPersistWarps - 1) / kPersistWarps);
     q.n_workers = ctas * kPersistWarps;
-    pnp_persist_kernel<<<ctas, kWarp * kPersistWarps, kPersistWarps * kWarpBytes, ctx->stream>>>(a, q);
+    if (four) pnp_persist_kernel<4><<<ctas, kWarp * kPersistWarps, kPersistWarps * kWarpBytes, ctx->stream>>>(a, q);
+    else pnp_persist_kernel<5><<<ctas, kWarp * kPersistWarps, kPersistWarps * kWarpBytes, ctx->stream>>>(a, q);
   } else {
-    pnp_ransac_kernel<<<n_pairs, kWarp, smem, ctx->stream>>>(a, q);
+    if (four) pnp_ransac_kernel<4><<<n_pairs, kWarp, smem, ctx->stream>>>(a, q);
+    else pnp_ransac_kernel<5><<<n_pairs, kWarp, smem, ctx->stream>>>(a, q);
   }
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());

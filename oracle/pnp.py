@@ -89,16 +89,19 @@ def cv_solve_pnp_ransac(obj, img, K, rvec0, tvec0, iterations=300, reproj_error=
 
 
 def restated_solve_pnp_ransac(obj, img, K, rvec0, tvec0, iterations=300, reproj_error=2.0,
-                              confidence=0.99, sample_indices=None, hyp_solver="cv2", refit="cv2"):
-    """Explicit-loop restatement (flags=ITERATIVE => 5-point EPnP minimal sets).
+                              confidence=0.99, sample_indices=None, hyp_solver="cv2", refit="cv2", flags=0):
+    """Explicit-loop restatement.  flags=ITERATIVE (0) => 5-point EPnP minimal sets + ITERATIVE refit from the guess;
+    flags=SOLVEPNP_P3P (2) / AP3P (5) => 4-point P3P minimal sets (a set without a solution is a skipped iteration)
+    + EPNP refit over the inliers.
 
-    Returns dict(ok, rvec, tvec, inliers, best_h, n_iters_run, samples)."""
+    Returns dict(ok, rvec, tvec, inliers, best_h, n_iters_run, samples, model)."""
     obj = np.ascontiguousarray(obj, dtype=np.float32).reshape(-1, 3)
     img = np.ascontiguousarray(img, dtype=np.float32).reshape(-1, 2)
     n = obj.shape[0]
-    mp = 5
+    p3p = flags in (2, 5)
+    mp = 4 if p3p else 5
     fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
-    assert n > mp, "n == model_points is the single-solve path; n < 5 never reaches here"
+    assert n > mp, "n == model_points is the single-solve path; n < model_points never reaches here"
     niters = max(int(iterations), 1)
     if sample_indices is None:
         sample_indices = sample_index_stream(n, mp, niters)
@@ -107,14 +110,23 @@ def restated_solve_pnp_ransac(obj, img, K, rvec0, tvec0, iterations=300, reproj_
     it = 0
     while it < niters:
         s = sample_indices[it]
-        if hyp_solver == "cv2":
+        if p3p:
+            ok, rv, tv = cv2.solvePnP(obj[s], img[s], K, None, flags=cv2.SOLVEPNP_P3P)
+            if not ok:
+                it += 1
+                continue
+            rv, tv = rv.ravel(), tv.ravel()
+        elif hyp_solver == "cv2":
             ok, rv, tv = cv2.solvePnP(obj[s], img[s], K, None, flags=cv2.SOLVEPNP_EPNP)
             rv, tv = rv.ravel(), tv.ravel()
         else:
             rv, tv, _ = cv_epnp.solve_epnp(obj[s], img[s], fx, fy, cx, cy)
             rv, tv = np.array(rv), np.array(tv)
-        err = reproj_err_f32(obj, img, rv, tv, K)
-        mask = err <= thr
+        if np.all(np.isfinite(rv)) and np.all(np.isfinite(tv)):
+            err = reproj_err_f32(obj, img, rv, tv, K)
+            mask = err <= thr
+        else:
+            mask = np.zeros(n, bool)          # cv2's P3P hands back a NaN model on a few degenerate sets: no inlier
         good = int(mask.sum())
         if good > max(best_good, mp - 1):
             best_mask, best_good, best_h, best_model = mask, good, it, (rv, tv)
@@ -126,7 +138,10 @@ def restated_solve_pnp_ransac(obj, img, K, rvec0, tvec0, iterations=300, reproj_
     inl = np.nonzero(best_mask)[0].astype(np.int32)
     o64 = obj[inl].astype(np.float64)
     i64 = img[inl].astype(np.float64)
-    if refit == "cv2":
+    if p3p:
+        ok, rvec, tvec = cv2.solvePnP(o64, i64, K, None, flags=cv2.SOLVEPNP_EPNP)
+        rvec, tvec = rvec.ravel(), tvec.ravel()
+    elif refit == "cv2":
         rvec = np.array(rvec0, dtype=np.float64).reshape(3, 1).copy()
         tvec = np.array(tvec0, dtype=np.float64).reshape(3, 1).copy()
         ok, rvec, tvec = cv2.solvePnP(o64, i64, K, None, rvec, tvec, True, cv2.SOLVEPNP_ITERATIVE)
@@ -135,6 +150,64 @@ def restated_solve_pnp_ransac(obj, img, K, rvec0, tvec0, iterations=300, reproj_
         rvec, tvec, _ = lm_refine(o64, i64, K, rvec0, tvec0)
     return dict(ok=True, rvec=rvec, tvec=tvec, inliers=inl, best_h=best_h, n_iters_run=it,
                 samples=sample_indices, model=best_model)
+
+
+def refine_model(obj, img, K, rvec, tvec, inliers, min_inliers, refine_iterations, reproj_error=2.0, refine_sigma=3.0):
+    """RTAB-Map util3d::solvePnPRansac with refineIterations > 0 -- its clone of PCL's SampleConsensus::refineModel
+    (unvendored; restated from the published source; reached from
+    R/src/myRegistrationVis.cpp:1085 with _PnPRefineIterations parsed at :104).  All error arithmetic in f32 like the
+    C++ (std::vector<float> err, uNorm, uMean, uVariance).  Returns (rvec, tvec, inliers)."""
+    f32 = np.float32
+    obj = np.ascontiguousarray(obj, dtype=np.float32).reshape(-1, 3)
+    img = np.ascontiguousarray(img, dtype=np.float32).reshape(-1, 2)
+    n = obj.shape[0]
+    error_threshold = f32(reproj_error)
+    it = 0
+    inlier_changed = False
+    prev_inliers = [int(i) for i in inliers]
+    new_inliers = []
+    inliers_sizes = []
+    rv = np.array(rvec, np.float64).reshape(3, 1).copy()
+    tv = np.array(tvec, np.float64).reshape(3, 1).copy()
+    while True:
+        cont = False
+        _, rv, tv = cv2.solvePnP(obj[prev_inliers], img[prev_inliers], K, None, rv, tv, True, cv2.SOLVEPNP_ITERATIVE)
+        inliers_sizes.append(len(prev_inliers))
+        proj, _ = cv2.projectPoints(obj, rv, tv, K, None)
+        proj = proj.reshape(-1, 2).astype(np.float32)
+        dx, dy = img[:, 0] - proj[:, 0], img[:, 1] - proj[:, 1]
+        err = np.sqrt(dx * dx + dy * dy, dtype=np.float32)                 # uNorm, f32
+        new_inliers = [i for i in range(n) if err[i] < error_threshold]
+        if len(new_inliers) < min_inliers:
+            it += 1
+            if it >= refine_iterations:
+                break
+            cont = True
+        if not cont:
+            s = f32(0)
+            for e in err:
+                s = f32(s + e)
+            mean = f32(s / f32(n))
+            s2 = f32(0)
+            for e in err:
+                d = f32(e - mean)
+                s2 = f32(s2 + f32(d * d))
+            variance = f32(s2 / f32(n - 1)) if n > 1 else f32(0)
+            error_threshold = min(f32(reproj_error), f32(f32(refine_sigma) * np.sqrt(variance, dtype=np.float32)))
+            inlier_changed = False
+            prev_inliers, new_inliers = new_inliers, prev_inliers
+            if len(new_inliers) != len(prev_inliers):
+                if len(inliers_sizes) >= 4 and inliers_sizes[-1] == inliers_sizes[-3] and inliers_sizes[-2] == inliers_sizes[-4]:
+                    break
+                inlier_changed = True
+            else:
+                inlier_changed = any(a != b for a, b in zip(prev_inliers, new_inliers))
+        if inlier_changed:
+            it += 1
+            if it < refine_iterations:
+                continue
+        break
+    return rv.ravel(), tv.ravel(), np.array(new_inliers, np.int32)
 
 
 # ---------------------------------------------------------------------------------------

@@ -3,6 +3,7 @@
 // machine without a GPU.  Never linked into libsepb200.so; the product path is the CUDA kernel.
 #include "../../multi_robot_slam_separators_b200/csrc/epnp.cuh"
 #include "../../multi_robot_slam_separators_b200/csrc/pnp_geom.cuh"
+#include "../../multi_robot_slam_separators_b200/csrc/p3p.cuh"
 
 extern "C" {
 
@@ -36,6 +37,27 @@ void hh_reproj_err(const double* rvec, const double* t, const double* K4, const 
 }
 
 void hh_rodrigues_jac(const double* rvec, double* R, double* J) { cvm::rodrigues_vec_to_mat(rvec, R, J); }
+
+// cv::solvePnP(SOLVEPNP_P3P) on four correspondences; returns 0 when there is no solution
+int hh_p3p4(const float* obj, const float* img, const double* K4, double* R, double* t, double* rvec) {
+  double heap[cvm::kEpnpHeap];
+  cvm::Intrinsics K{K4[0], K4[1], K4[2], K4[3]};
+  if (!cvm::p3p4(obj, img, K, R, t)) return 0;
+  cvm::rodrigues_mat_to_vec(cvm::Heap{heap}, R, rvec);
+  return 1;
+}
+
+// cv::solvePnP(SOLVEPNP_EPNP) on n f64 correspondences (the refit of the P3P-flag path)
+void hh_epnp_n(const double* obj, const double* img, int n, const double* K4, double* R, double* t, double* rvec) {
+  double heap[cvm::kEpnpHeap];
+  cvm::Intrinsics K{K4[0], K4[1], K4[2], K4[3]};
+  cvm::epnp_n(cvm::Heap{heap}, n, [&](int i, double* o3, double* px) {
+    for (int k = 0; k < 3; ++k) o3[k] = obj[3 * i + k];
+    px[0] = img[2 * i];
+    px[1] = img[2 * i + 1];
+  }, K, R, t);
+  cvm::rodrigues_mat_to_vec(cvm::Heap{heap}, R, rvec);
+}
 
 int hh_update_iters(double p, double ep, int mp, int mx) { return cvm::ransac_update_num_iters(p, ep, mp, mx); }
 }

@@ -70,6 +70,22 @@ def test_builds_and_fails_in_band_without_device():
     L.sh_pr_destroy(pr); L.sh_geo_destroy(geo); L.sh_device_destroy(dev)
 
 
+def test_ros_node_compiles():
+    """host/ros_node.cpp needs roscpp + tf + the generated message headers, none of which this image has: it is compiled
+    (parsed and type-checked, -fsyntax-only) against the stand-in declarations of tests/host_harness/ros_stub, whose
+    message structs mirror R/msg/*.msg and R/srv/*.srv field for field.  Catches what an #ifdef'ed-out file hides:
+    a name clash with the generated multi_robot_separators:: types, calls of handlers that do not exist."""
+    import subprocess
+    stub = os.path.join(ROOT, "tests", "host_harness", "ros_stub")
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-DSEPB_WITH_ROS", "-I", stub, "-I", os.path.join(ROOT, "host"),
+                        "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "host", "ros_node.cpp")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    src = open(os.path.join(ROOT, "host", "ros_node.cpp")).read()
+    for needle in ("place.addKeyframe(", "add_separators_pose_graph", "lookupTransform(", "geo.setLocalTransform("):
+        assert needle in src
+
+
 @pytest.mark.gpu
 def test_estimate_transformation_matches_batch_path():
     from multi_robot_slam_separators_b200 import capi
