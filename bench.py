@@ -322,9 +322,12 @@ def run_ours(args):
         e.reset()
         e.receive_descriptors(nvA)
 
-    def keyframes(e):                  # 1.13 GB on the copy stream, returns at once
-        e.add_peer_keyframes(hostA["desc"], hostA["kp2d"], hostA["kp3d"], hostA["count"], hostA["octave"], async_=True)
-        e.add_local_keyframes(hostB["desc"], hostB["kp2d"], hostB["kp3d"], hostB["count"], hostB["octave"], async_=True)
+    lazy = args.e2e_upload == "lazy"
+
+    def keyframes(e):                  # copy stream, returns at once.  full: 1.13 GB (52 B per feature); lazy: descriptors +
+        # counts only (32 B per feature, 0.64 GB), the device pulls key points of the frames whose pairs reach PnP
+        e.add_peer_keyframes(hostA["desc"], hostA["kp2d"], hostA["kp3d"], hostA["count"], hostA["octave"], async_=True, lazy=lazy)
+        e.add_local_keyframes(hostB["desc"], hostB["kp2d"], hostB["kp3d"], hostB["count"], hostB["octave"], async_=True, lazy=lazy)
 
     def start(e, slot):                # search (blocking, small copies) + verification enqueued, results D2H to pinned
         i5, d5 = e.db.topk(nvB, args.topk, mode)
@@ -351,6 +354,10 @@ def run_ours(args):
     torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
     d2h_bytes = P * (4 + 4 + 4 + 48 + 48) + P * 12
+    if lazy:   # what really crossed the bus in the last step: descriptors + counts + search inputs + the pulled key points
+        pulled = slots[c].peer.fetched_bytes + slots[c].local.fetched_bytes
+        h2d_bytes = hostA["desc"].nbytes + hostB["desc"].nbytes + hostA["count"].nbytes + hostB["count"].nbytes + \
+            nvA.nbytes + nvB.nbytes + P * 8 + pulled
     assert int((r_e2e["status"] == 1).sum()) == n_ok, "e2e and resident paths disagree"
 
     # ---- aggregate over ranks -----------------------------------------------------------------
@@ -447,7 +454,10 @@ def run_ours(args):
                 "dtype": "s8/s32 (Hamming GEMM) + f64 (PnP, NetVLAD)" if match_kernel == "tensor" else "u32+f64",
                 "data": "synthetic", "config": workload_config(args), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
-                        "steps": e2e_steps, "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified"},
+                        "steps": e2e_steps, "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified",
+                        "upload": ("lazy key points: descriptors + counts of every frame are copied, kp2d / kp3d rows are pulled by the "
+                                   "device from pinned host memory for the frames whose pairs reach PnP (sepb_frames_bind_host_async)")
+                        if lazy else "full keyframes (52 B per feature)"},
                 "gpu_launches": int(launches),
                 "roofline": dict(rooflines[dominant], dominant=dominant, dominant_rule="largest share of the step; "
                                  "every kernel of the step is in `rooflines`"),
@@ -815,6 +825,8 @@ def main():
                     help="NetVLAD search: tcgen05 split-bf16 filter + exact f64 re-rank (tensor) or full f64 scan (exact); identical results")
     ap.add_argument("--match", default="auto", choices=["auto", "popc", "tensor"],
                     help="Hamming matcher kernel: tcgen05 int8 GEMM (tensor), POPC pipe (popc); identical results")
+    ap.add_argument("--e2e-upload", default="lazy", choices=["lazy", "full"],
+                    help="end-to-end leg: how keyframes reach the device (identical results)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (0 = --steps)")
     ap.add_argument("--cpu-queries", type=int, default=200)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -94,6 +94,17 @@ SEPB_API int sepb_frames_upload(sepb_ctx* ctx, sepb_frames* f, int first, int n,
 SEPB_API int sepb_frames_upload_async(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc,
                                       const float* kp2d, const float* kp3d, const int32_t* octave, const int32_t* count);
 SEPB_API int sepb_frames_wait(sepb_ctx* ctx, sepb_frames* f);
+/* Host-resident keyframes with lazy key points.  Like sepb_frames_upload_async, but only descriptors and counts are
+ * copied: kp2d / kp3d / octave (which MUST be pinned host memory -- cudaHostAlloc or cudaHostRegister -- covering
+ * [n][max_feat][..]) stay where they are and the device pulls, inside the verification calls, just the rows of the
+ * frames whose pairs reach PnP (>= min_inliers matches; myRegistrationVis.cpp:1069-1070) -- 32 instead of 52 bytes per
+ * feature cross the bus for every frame, the remaining 20 only for the few percent that need them.  The arrays must
+ * stay valid and unchanged until the next bind / upload of these slots.  Results are identical to a full upload.
+ * One binding per store at a time (a later bind replaces it).  EstTransform.srv:1-6 is the payload this trims. */
+SEPB_API int sepb_frames_bind_host_async(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc,
+                                         const float* kp2d, const float* kp3d, const int32_t* octave, const int32_t* count);
+/* bytes the device has pulled from the bound host arrays since the last bind (synchronises the context stream) */
+SEPB_API int64_t sepb_frames_fetched_bytes(sepb_ctx* ctx, const sepb_frames* f);
 
 /* ---- K2: brute-force Hamming 2-NN + NNDR + one-to-one filter ----------------------------
  * Replaces the global matching block R/src/myRegistrationVis.cpp:839-894 in brute-force mode
@@ -333,7 +344,7 @@ SEPB_API int sepb_group_netvlad_topk(sepb_group* g, sepb_db* const* dbs, const d
  * 2 / 3: TMEM bytes/s read by tcgen05.ld (plain / .pack::16b); 4 / 5: int8 op/s of a bare tcgen05.mma kind::i8 issue
  * loop, M128 x N128 / N256 x K32, both operands in shared memory (what K2T's instruction shape sustains per GPU);
  * 6: bf16 FLOP/s of the same loop with kind::f16 M128 x N256 x K16; 7: kind 4 with producer-like shared-memory
- * stores running beside it. */
+ * stores running beside it; 8 / 9: the loop issued by CTA pairs (cta_group::2, M256 x N256), int8 K32 / bf16 K16. */
 SEPB_API int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s);
 /* developer hook (K3): cycle counters {EPnP solve, Rodrigues, scoring, refit, chunk-solves, 12x12 Jacobi, Jacobi
  * sweeps, 0} summed over warps; all zero and return 0 unless the library was built with SEPB_K3_PROFILE=1. */

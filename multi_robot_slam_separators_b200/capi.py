@@ -93,7 +93,9 @@ def _declare(L):
     L.sepb_frames_destroy.restype = None
     L.sepb_frames_size.argtypes = [vp]
     L.sepb_frames_size.restype = i32
-    for name in ("sepb_frames_upload", "sepb_frames_upload_async"):
+    L.sepb_frames_fetched_bytes.argtypes = [vp, vp]
+    L.sepb_frames_fetched_bytes.restype = C.c_int64
+    for name in ("sepb_frames_upload", "sepb_frames_upload_async", "sepb_frames_bind_host_async"):
         f = getattr(L, name)
         f.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp]
         f.restype = i32
@@ -224,10 +226,12 @@ class Context:
         """'popc' -> POPC/s, 'dfma' -> FP64 FMA/s, 'tmem' / 'tmem_pack16' -> TMEM bytes/s read by tcgen05.ld
         (measured microbenchmarks); 'mma_i8_n128' | 'mma_i8_n256' | 'mma_bf16_n256' | 'mma_i8_n128_sts' -> tensor-pipe
         ops/s of a bare tcgen05.mma issue loop (M128, SWIZZLE_128B shared-memory operands; _sts: with producer-like
-        shared-memory stores running beside it)."""
+        shared-memory stores running beside it); 'mma2_i8_m256n256' | 'mma2_bf16_m256n256' -> the same loop issued by CTA
+        pairs (tcgen05.mma.cta_group::2, M256 x N256)."""
         v = C.c_double()
         self.check(lib().sepb_measure_peak(self._h, {"popc": 0, "dfma": 1, "tmem": 2, "tmem_pack16": 3, "mma_i8_n128": 4, "mma_i8_n256": 5,
-                                                         "mma_bf16_n256": 6, "mma_i8_n128_sts": 7}[kind], reps, C.byref(v)))
+                                                         "mma_bf16_n256": 6, "mma_i8_n128_sts": 7, "mma2_i8_m256n256": 8,
+                                                         "mma2_bf16_m256n256": 9}[kind], reps, C.byref(v)))
         return v.value
 
     def set_match_kernel(self, which: str):
@@ -267,9 +271,12 @@ class Frames:
         ctx.check(lib().sepb_frames_create(ctx._h, capacity, max_feat, C.byref(self._h)))
         ctx._children.add(self)
 
-    def upload(self, first, desc, kp2d, kp3d, count, octave=None, async_=False):
+    def upload(self, first, desc, kp2d, kp3d, count, octave=None, async_=False, lazy=False):
         """async_=True: enqueue on the copy stream and return (arrays must stay alive, ideally pinned, until
-        wait() or the next blocking call that uses the store)."""
+        wait() or the next blocking call that uses the store).
+        lazy=True (sepb_frames_bind_host_async; implies async_): only descriptors + counts are copied, kp2d / kp3d /
+        octave must be PINNED numpy arrays of exactly the store's layout and are read in place by the device for the
+        frames whose pairs reach PnP; they must stay alive and unchanged until the next upload of these slots."""
         desc = np.ascontiguousarray(desc, dtype=np.uint8)
         n = desc.shape[0]
         assert desc.shape == (n, self.max_feat, 32)
@@ -278,10 +285,17 @@ class Frames:
         count = np.ascontiguousarray(count, dtype=np.int32).reshape(n)
         if octave is not None:
             octave = np.ascontiguousarray(octave, dtype=np.int32).reshape(n, self.max_feat)
-        fn = lib().sepb_frames_upload_async if async_ else lib().sepb_frames_upload
+        fn = lib().sepb_frames_bind_host_async if lazy else (lib().sepb_frames_upload_async if async_ else lib().sepb_frames_upload)
         self.ctx.check(fn(self.ctx._h, self._h, first, n, _ptr(desc), _ptr(kp2d), _ptr(kp3d), _ptr(octave), _ptr(count)))
-        if async_:
+        if async_ or lazy:
             self._pending = (desc, kp2d, kp3d, count, octave)     # keep the host arrays alive
+        if lazy:
+            self._bound = (kp2d, kp3d, octave)                    # read in place by the device until the next upload
+
+    @property
+    def fetched_bytes(self) -> int:
+        """Bytes the device pulled from the bound host arrays since the last lazy upload (synchronises)."""
+        return int(lib().sepb_frames_fetched_bytes(self.ctx._h, self._h))
 
     def wait(self):
         self.ctx.check(lib().sepb_frames_wait(self.ctx._h, self._h))

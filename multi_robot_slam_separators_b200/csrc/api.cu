@@ -120,7 +120,10 @@ int sepb_frames_create(sepb_ctx* ctx, int capacity, int max_feat, sepb_frames** 
   cudaError_t e;
   if ((e = cudaMalloc(&f->desc, nf * 32)) != cudaSuccess || (e = cudaMalloc(&f->kp2d, nf * 8)) != cudaSuccess ||
       (e = cudaMalloc(&f->kp3d, nf * 12)) != cudaSuccess || (e = cudaMalloc(&f->octave, nf * 4)) != cudaSuccess ||
-      (e = cudaMalloc(&f->count, (size_t)capacity * 4)) != cudaSuccess) {
+      (e = cudaMalloc(&f->count, (size_t)capacity * 4)) != cudaSuccess ||
+      (e = cudaMalloc(&f->need, ((size_t)capacity + 3) / 4 * 4)) != cudaSuccess ||
+      (e = cudaMalloc(&f->have, ((size_t)capacity + 3) / 4 * 4)) != cudaSuccess ||
+      (e = cudaMalloc(&f->fetched, 8)) != cudaSuccess) {
     sepb_frames_destroy(f);
     return sepb_fail(ctx, (int)e, "cudaMalloc(frames)", __FILE__, __LINE__);
   }
@@ -131,6 +134,9 @@ int sepb_frames_create(sepb_ctx* ctx, int capacity, int max_feat, sepb_frames** 
   }
   cudaMemsetAsync(f->count, 0, (size_t)capacity * 4, ctx->stream);
   cudaMemsetAsync(f->octave, 0, nf * 4, ctx->stream);
+  cudaMemsetAsync(f->need, 0, ((size_t)capacity + 3) / 4 * 4, ctx->stream);
+  cudaMemsetAsync(f->have, 0, ((size_t)capacity + 3) / 4 * 4, ctx->stream);
+  cudaMemsetAsync(f->fetched, 0, 8, ctx->stream);
   cudaStreamSynchronize(ctx->stream);   // uploads run on the copy stream: the store must be initialised before the first one
   *out = f;
   return SEPB_OK;
@@ -150,13 +156,18 @@ void sepb_frames_destroy(sepb_frames* f) {
   cudaFree(f->kp3d);
   cudaFree(f->octave);
   cudaFree(f->count);
+  cudaFree(f->need);
+  cudaFree(f->have);
+  cudaFree(f->fetched);
   delete f;
 }
 
 int sepb_frames_size(const sepb_frames* f) { return f ? f->size : 0; }
 
+// lazy == true (sepb_frames_bind_host_async): only descriptors and counts are copied; kp2d / kp3d / octave stay in the
+// caller's pinned arrays, whose device-visible addresses are remembered for frames_fetch.cu
 static int frames_upload_impl(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc, const float* kp2d,
-                              const float* kp3d, const int32_t* octave, const int32_t* count, bool async) {
+                              const float* kp3d, const int32_t* octave, const int32_t* count, bool async, bool lazy = false) {
   if (!ctx || !f) return SEPB_E_INVALID;
   SEPB_REQUIRE(ctx, n >= 0 && first >= 0 && first + n <= f->capacity, SEPB_E_SHAPE);
   if (n == 0) return SEPB_OK;
@@ -164,14 +175,38 @@ static int frames_upload_impl(sepb_ctx* ctx, sepb_frames* f, int first, int n, c
   for (int i = 0; i < n; ++i) SEPB_REQUIRE(ctx, count[i] >= 0 && count[i] <= f->max_feat, SEPB_E_SHAPE);
   std::lock_guard<std::mutex> lk(ctx->mu);
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const float *d_kp2d = nullptr, *d_kp3d = nullptr;
+  const int32_t* d_oct = nullptr;
+  if (lazy) {
+    // the arrays must be pinned (cudaHostAlloc / cudaHostRegister): the device reads them in place
+    if (cudaHostGetDevicePointer((void**)&d_kp2d, (void*)kp2d, 0) != cudaSuccess ||
+        cudaHostGetDevicePointer((void**)&d_kp3d, (void*)kp3d, 0) != cudaSuccess ||
+        (octave && cudaHostGetDevicePointer((void**)&d_oct, (void*)octave, 0) != cudaSuccess)) {
+      cudaGetLastError();
+      return sepb_fail(ctx, SEPB_E_INVALID, "sepb_frames_bind_host_async: kp2d / kp3d / octave must be pinned host memory", __FILE__, __LINE__);
+    }
+  }
   // the copy stream must not overwrite slots a kernel enqueued earlier is still reading
   cudaStream_t cs = ctx->copy_stream;
   if (f->has_use) SEPB_CUDA(ctx, cudaStreamWaitEvent(cs, f->ev_last_use, 0));
   const size_t off = (size_t)first * f->max_feat, nf = (size_t)n * f->max_feat;
   SEPB_CUDA(ctx, cudaMemcpyAsync(f->desc + off * 32, desc, nf * 32, cudaMemcpyHostToDevice, cs));
-  SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp2d + off * 2, kp2d, nf * 8, cudaMemcpyHostToDevice, cs));
-  SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp3d + off * 3, kp3d, nf * 12, cudaMemcpyHostToDevice, cs));
-  if (octave) SEPB_CUDA(ctx, cudaMemcpyAsync(f->octave + off, octave, nf * 4, cudaMemcpyHostToDevice, cs));
+  if (!lazy) {
+    SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp2d + off * 2, kp2d, nf * 8, cudaMemcpyHostToDevice, cs));
+    SEPB_CUDA(ctx, cudaMemcpyAsync(f->kp3d + off * 3, kp3d, nf * 12, cudaMemcpyHostToDevice, cs));
+    if (octave) SEPB_CUDA(ctx, cudaMemcpyAsync(f->octave + off, octave, nf * 4, cudaMemcpyHostToDevice, cs));
+    SEPB_CUDA(ctx, cudaMemsetAsync(f->have + first, 7, (size_t)n, cs));   // everything resident: nothing to pull
+  } else {
+    f->lazy = true;
+    f->lazy_first = first;
+    f->lazy_n = n;
+    f->h_kp2d = d_kp2d;
+    f->h_kp3d = d_kp3d;
+    f->h_octave = d_oct;
+    SEPB_CUDA(ctx, cudaMemsetAsync(f->have, octave ? 0 : 4, ((size_t)f->capacity + 3) / 4 * 4, cs));
+    SEPB_CUDA(ctx, cudaMemsetAsync(f->need, 0, ((size_t)f->capacity + 3) / 4 * 4, cs));
+    SEPB_CUDA(ctx, cudaMemsetAsync(f->fetched, 0, 8, cs));
+  }
   SEPB_CUDA(ctx, cudaMemcpyAsync(f->count + first, count, (size_t)n * 4, cudaMemcpyHostToDevice, cs));
   SEPB_CUDA(ctx, cudaEventRecord(f->ev_uploaded, cs));
   f->has_upload = true;
@@ -188,6 +223,20 @@ int sepb_frames_upload(sepb_ctx* ctx, sepb_frames* f, int first, int n, const ui
 int sepb_frames_upload_async(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc, const float* kp2d,
                              const float* kp3d, const int32_t* octave, const int32_t* count) {
   return frames_upload_impl(ctx, f, first, n, desc, kp2d, kp3d, octave, count, true);
+}
+
+int sepb_frames_bind_host_async(sepb_ctx* ctx, sepb_frames* f, int first, int n, const uint8_t* desc, const float* kp2d,
+                                const float* kp3d, const int32_t* octave, const int32_t* count) {
+  return frames_upload_impl(ctx, f, first, n, desc, kp2d, kp3d, octave, count, true, true);
+}
+
+int64_t sepb_frames_fetched_bytes(sepb_ctx* ctx, const sepb_frames* f) {
+  if (!ctx || !f || !f->fetched) return -1;
+  unsigned long long v = 0;
+  cudaSetDevice(ctx->device);
+  if (cudaMemcpyAsync(&v, f->fetched, 8, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return -1;
+  if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) return -1;
+  return (int64_t)v;
 }
 
 int sepb_frames_wait(sepb_ctx* ctx, sepb_frames* f) {

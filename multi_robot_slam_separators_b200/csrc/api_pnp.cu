@@ -106,6 +106,10 @@ static int pnp_ransac_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   }
   const bool four = model_points_of(prm) == 4;
   FramesUse use(ctx, from, to);
+  // host-bound stores: pull the key points of the pairs that will run PnP (From 3-D points, To pixels)
+  rc = sepb_launch_frames_fetch(ctx, const_cast<sepb_frames*>(from), const_cast<sepb_frames*>(to), d_pairs, n_pairs, d_n_matches,
+                                prm->min_inliers, nullptr, 2, 1);
+  if (rc) return rc;
   return sepb_launch_pnp_ransac(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from,
                                 d_match_to, d_n_unique_to, four ? ctx->table4 : ctx->table, four ? ctx->table4_h : ctx->table_h,
                                 d_custom_samples, custom_h, d_guess,
@@ -154,6 +158,10 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   auto covariance = [&]() -> int {
     if (!o->covariance) return SEPB_OK;
     SEPB_REQUIRE(ctx, o->inlier_mask != nullptr, SEPB_E_INVALID);
+    // the 3-D residuals need the To frame's 3-D points of the verified pairs
+    int rcf = sepb_launch_frames_fetch(ctx, const_cast<sepb_frames*>(from), const_cast<sepb_frames*>(to), d_pairs, n_pairs, nullptr,
+                                       0, o->status, 2, 2);
+    if (rcf) return rcf;
     return sepb_launch_pose_cov(ctx, view_of(from), view_of(to), d_pairs, n_pairs, o->status, o->n_matches, o->match_from,
                                 o->match_to, o->inlier_mask, mw, o->transform, o->covariance);
   };
@@ -162,6 +170,10 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   // ---- pass 2 (stereoCamGeometricTools.cpp:153-164): guess = first result; only where the first pass succeeded
   if (d_status_pass1)
     SEPB_CUDA(ctx, cudaMemcpyAsync(d_status_pass1, o->status, (size_t)n_pairs * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  // the window matcher reads pixels, 3-D points and octaves of both frames of every pair that passed the first call
+  rc = sepb_launch_frames_fetch(ctx, const_cast<sepb_frames*>(from), const_cast<sepb_frames*>(to), d_pairs, n_pairs, nullptr, 0,
+                                o->status, 7, 7);
+  if (rc) return rc;
   rc = sepb_launch_guess_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, o->status, o->transform, pprm,
                                gprm->image_width, gprm->image_height, gprm->win_size, mprm->nndr, o->n_matches,
                                o->match_from, o->match_to, d_nu, d_guess);

@@ -71,6 +71,16 @@ struct sepb_frames {
   // asynchronous uploads: kernels wait for ev_uploaded, the next upload waits for ev_last_use
   cudaEvent_t ev_uploaded = nullptr, ev_last_use = nullptr;
   mutable bool has_upload = false, has_use = false;
+  // lazy keypoints (sepb_frames_bind_host_async, frames_fetch.cu): device-visible addresses of the caller's pinned
+  // arrays for slots [lazy_first, lazy_first + lazy_n); verification pulls the rows it needs
+  bool lazy = false;
+  int lazy_first = 0, lazy_n = 0;
+  const float* h_kp2d = nullptr;
+  const float* h_kp3d = nullptr;
+  const int32_t* h_octave = nullptr;
+  uint8_t* need = nullptr;                // [capacity rounded up to 4] bit 0 kp2d, 1 kp3d, 2 octave: wanted by the current call
+  uint8_t* have = nullptr;                // [capacity rounded up to 4] same bits: resident for the current binding
+  unsigned long long* fetched = nullptr;  // device counter: bytes pulled since the binding
 };
 
 // device view of a frame store passed by value to kernels
@@ -82,10 +92,23 @@ struct FramesView {
   const int32_t* count;
   int max_feat;
   int size;
+  // host-bound slots [lazy_first, lazy_first + lazy_n): their 3-D points are readable in place (pinned host memory
+  // mapped into the device address space) before the fetch kernel has made them resident -- K2's list compaction only
+  // asks whether the 3-D point of a matched From feature is finite
+  const float* kp3d_host;
+  int lazy_first, lazy_n;
+#ifdef __CUDACC__
+  // 3-D points of frame `slot` for a reader that may run BEFORE the pull (the matchers)
+  __device__ __forceinline__ const float* kp3d_early(int slot) const {
+    const unsigned rel = (unsigned)(slot - lazy_first);
+    return rel < (unsigned)lazy_n ? kp3d_host + (size_t)rel * max_feat * 3 : kp3d + (size_t)slot * max_feat * 3;
+  }
+#endif
 };
 
 static inline FramesView view_of(const sepb_frames* f) {
-  return FramesView{f->desc, f->kp2d, f->kp3d, f->octave, f->count, f->max_feat, f->size};
+  return FramesView{f->desc, f->kp2d, f->kp3d, f->octave, f->count, f->max_feat, f->size,
+                    f->lazy ? f->h_kp3d : nullptr, f->lazy ? f->lazy_first : 0, f->lazy ? f->lazy_n : 0};
 }
 
 // order the compute stream after pending asynchronous uploads of the frame stores a launch is about to read ...
@@ -207,6 +230,8 @@ int sepb_launch_pose_cov(sepb_ctx* ctx, FramesView from, FramesView to, const in
                          const int32_t* d_status, const int32_t* d_n_matches, const uint16_t* d_match_from,
                          const uint16_t* d_match_to, const uint32_t* d_inlier_mask, int mask_words,
                          const float* d_transform, double* d_cov);
+int sepb_launch_frames_fetch(sepb_ctx* ctx, sepb_frames* from, sepb_frames* to, const int32_t* d_pairs, int n_pairs,
+                             const int32_t* d_n_matches, int min_matches, const int32_t* d_status, int bits_from, int bits_to);
 int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H, int model_points);
 int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                            const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,

@@ -112,7 +112,7 @@ hamming_match_kernel(FramesView from, FramesView to, const int32_t* __restrict__
     }
   }
   __syncthreads();
-  const float* p3 = from.kp3d + (size_t)(valid_pair ? fi : 0) * from.max_feat * 3;
+  const float* p3 = from.kp3d_early(valid_pair ? fi : 0);
   mtail::unique_and_compact<kThreads>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
                                       (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to, n_unique_to);
 }

@@ -485,7 +485,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     K2T_STAMP(tid == 0, 3);
     return;
   }
-  const float* p3 = from.kp3d + (size_t)fi * from.max_feat * 3;
+  const float* p3 = from.kp3d_early(fi);
   mtail::unique_and_compact<kThreadsT>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
                                        (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to, n_unique_to);
   K2T_STAMP(tid == 0, 3);

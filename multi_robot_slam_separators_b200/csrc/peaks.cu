@@ -126,6 +126,70 @@ __global__ void __launch_bounds__(160, 1) mma_peak_kernel(uint32_t* out, int til
   }
 }
 
+
+// The same bare issue loop for a CTA PAIR: tcgen05.mma.cta_group::2.kind::i8, M256 (128 To rows per CTA) x N256 (each
+// CTA holds 128 of the 256 B rows) x K32.  Only the leader CTA (cluster rank 0) issues; per SM and multiply-add the
+// operand fetch is 8 KB instead of the 12 KB of the one-CTA N256 shape.  mode 1: kind::f16 (bf16) K16.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) mma_peak2_kernel(uint32_t* out, int tiles, int mode) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (umma::smem_u32(smem_raw) & 1023u)) & 1023u);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const uint32_t sA = umma::smem_u32(smem), sB = sA + 2 * 128 * 128;
+  if (threadIdx.x == 0) {
+    umma::mbar_init(&bar, 1);
+    umma::fence_mbar_init();
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(umma::smem_u32(&slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  const uint32_t tmem = slot;
+  if (warp == 0) {
+    if (rank == 0 && umma::elect_one()) {
+      const uint32_t idesc = mode == 1 ? umma::instr_desc(1, 1, 1, 256, 256) : umma::instr_desc(2, 1, 1, 256, 256);
+      for (int t = 0; t < tiles; ++t) {
+        const uint32_t d = tmem + (uint32_t)((t * 256) & 511);
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t a = umma::smem_desc_sw128(sA + (uint32_t)(kb * 128 * 128 + k * 32));
+            const uint64_t b = umma::smem_desc_sw128(sB + (uint32_t)(kb * 128 * 128 + k * 32));
+            const uint32_t acc = (kb | k) != 0;
+            if (mode == 1)
+              asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+                           "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
+            else
+              asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+                           "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
+          }
+      }
+      // completion arrives on the barrier of BOTH CTAs (same shared-memory offset)
+      asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(umma::smem_u32(&bar)),
+                   "h"((uint16_t)3) : "memory");
+    }
+    __syncwarp();
+    umma::mbar_wait(&bar, 0);
+  }
+  if (threadIdx.x == 0) out[blockIdx.x] = rank;
+  umma::tc_fence_before();
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (warp == 0) {
+    umma::tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -136,6 +200,33 @@ extern "C" {
 int sepb_measure_peak(sepb_ctx* ctx, int kind, int reps, double* ops_per_s) {
   if (!ctx || !ops_per_s) return SEPB_E_INVALID;
   SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (kind == 8 || kind == 9) {   // CTA-pair issue loop (cta_group::2): int8 / bf16, M256 x N256
+    const int tiles = 4096, blocks = ctx->sm_count & ~1;
+    const size_t smem = 4 * 128 * 128 + 1024;
+    SEPB_CUDA(ctx, cudaFuncSetAttribute(mma_peak2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    void* buf = sepb_scratch(ctx, (size_t)blocks * 4);
+    if (!buf) return (int)cudaErrorMemoryAllocation;
+    cudaEvent_t e0, e1;
+    SEPB_CUDA(ctx, cudaEventCreate(&e0));
+    SEPB_CUDA(ctx, cudaEventCreate(&e1));
+    double best = 0;
+    for (int r = 0; r < reps + 1; ++r) {
+      SEPB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+      mma_peak2_kernel<<<blocks, 128, smem, ctx->stream>>>((uint32_t*)buf, tiles, kind - 8);
+      ctx->launches++;
+      SEPB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+      SEPB_CUDA(ctx, cudaEventSynchronize(e1));
+      SEPB_CUDA(ctx, cudaGetLastError());
+      float ms = 0;
+      SEPB_CUDA(ctx, cudaEventElapsedTime(&ms, e0, e1));
+      const double ops = (double)(blocks / 2) * tiles * 8 * (2.0 * 256 * 256 * (kind == 9 ? 16.0 : 32.0)) / (ms * 1e-3);
+      if (r > 0 && ops > best) best = ops;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ops_per_s = best;
+    return SEPB_OK;
+  }
   const bool tm = kind == 2 || kind == 3, mm = kind >= 4 && kind <= 7;
   const int mma_tiles = 4096;
   const size_t mma_smem = 2 * 128 * 128 + 2 * 256 * 128 + 128 * 128 + 1024;

@@ -56,12 +56,14 @@ class SeparatorEngine:
         self._buf = {}
 
     # ---- data in (host buffers; H2D inside the C ABI) -------------------------------------
-    def add_local_keyframes(self, desc, kp2d, kp3d, count, octave=None, async_=False):
-        self.local.upload(self.n_local, desc, kp2d, kp3d, count, octave, async_=async_)
+    def add_local_keyframes(self, desc, kp2d, kp3d, count, octave=None, async_=False, lazy=False):
+        """lazy=True: host-resident keyframes (pinned arrays): descriptors travel now, key points are pulled by the device
+        for the frames whose pairs reach PnP (capi.Frames.upload)."""
+        self.local.upload(self.n_local, desc, kp2d, kp3d, count, octave, async_=async_, lazy=lazy)
         self.n_local += len(count)
 
-    def add_peer_keyframes(self, desc, kp2d, kp3d, count, octave=None, async_=False):
-        self.peer.upload(self.n_peer, desc, kp2d, kp3d, count, octave, async_=async_)
+    def add_peer_keyframes(self, desc, kp2d, kp3d, count, octave=None, async_=False, lazy=False):
+        self.peer.upload(self.n_peer, desc, kp2d, kp3d, count, octave, async_=async_, lazy=lazy)
         self.n_peer += len(count)
 
     def receive_descriptors(self, netvlad_rows):

@@ -154,3 +154,57 @@ def test_two_pass_driver(world):
             assert got_c[0, 0] != 1.0 and got_c[3, 3] != 1.0
         n2 += 1
     assert n2 == int((one["status"] == 1).sum()) and n2 >= 8     # every pair whose first call succeeded was compared
+
+
+def assert_same(got, want, tag):
+    """Every output equal; the match lists up to n_matches (what lies behind is whatever the scratch held)."""
+    for k in want:
+        if k in ("match_from", "match_to"):
+            for p, m in enumerate(want["n_matches"]):
+                assert np.array_equal(got[k][p, :m], want[k][p, :m]), (tag, k, p)
+        else:
+            assert np.array_equal(got[k], want[k], equal_nan=True), (tag, k)
+
+
+def test_lazy_keypoints_identical_to_full_upload():
+    """sepb_frames_bind_host_async: descriptors travel, key points are pulled by the device from pinned host memory for
+    the frames whose pairs reach PnP -- every output of the one-call and the two-call drivers (covariance included)
+    equals the full upload's, and only a fraction of the key points crosses the bus."""
+    import torch
+    ctx = capi.Context(0)
+    A, B = synth.make_robots(2, 48, n_feat=1000, dim=128, seed=1207)
+    A.count[3] = 700
+    B.count[5] = 300
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    hA = {k: pin(getattr(A, k)) for k in ("desc", "kp2d", "kp3d", "count", "octave")}
+    hB = {k: pin(getattr(B, k)) for k in ("desc", "kp2d", "kp3d", "count", "octave")}
+    rng = np.random.default_rng(3)
+    same = [(a, b) for a in range(48) for b in range(48) if A.place[a] == B.place[b]]
+    pairs = same + [(int(rng.integers(48)), int(rng.integers(48))) for _ in range(60)]
+    prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY)
+    gprm = capi.guess_params(synth.WIDTH, synth.HEIGHT, 20.0)
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    la, lb = capi.Frames(ctx, 48, 1000), capi.Frames(ctx, 48, 1000)
+    try:
+        want1 = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+        want2 = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gprm)
+        assert int((want1["status"] == 1).sum()) >= len(same) - 3
+        for rnd in range(2):      # the second round re-binds the same stores
+            la.upload(0, hA["desc"], hA["kp2d"], hA["kp3d"], hA["count"], hA["octave"], lazy=True)
+            lb.upload(0, hB["desc"], hB["kp2d"], hB["kp3d"], hB["count"], hB["octave"], lazy=True)
+            got1 = capi.verify_pairs(ctx, la, lb, pairs, prm)
+            pulled1 = la.fetched_bytes + lb.fetched_bytes
+            assert_same(got1, want1, rnd)
+            full = (hA["kp2d"].nbytes + hA["kp3d"].nbytes + hA["octave"].nbytes) * 2
+            assert 0 < pulled1 < full // 2
+            got2 = capi.estimate_transformations(ctx, la, lb, pairs, prm, gprm)
+            assert_same(got2, want2, rnd)
+            assert la.fetched_bytes + lb.fetched_bytes > pulled1          # the second call needs more arrays
+        # unpinned arrays are refused, loudly
+        with pytest.raises(capi.SepbError):
+            la.upload(0, A.desc, A.kp2d.copy(), A.kp3d.copy(), A.count, A.octave.copy(), lazy=True)
+    finally:
+        ctx.sync()
+        for f in (fa, fb, la, lb):
+            f.close()
+        ctx.close()

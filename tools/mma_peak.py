@@ -1,15 +1,11 @@
-"""Tensor-pipe issue rates of the MMA shapes K1 / K2T use (bare tcgen05.mma loops, one CTA per SM)."""
-import json
-import os
-import sys
+"""Developer tool: tensor-pipe issue rates of the MMA shapes the matchers use (bare tcgen05.mma loops, peaks.cu)."""
+import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from multi_robot_slam_separators_b200 import capi
-import torch
-
 ctx = capi.Context(0)
-sm = torch.cuda.get_device_properties(0).multi_processor_count
-out = {}
-for kind in ("mma_i8_n128", "mma_i8_n256", "mma_bf16_n256", "mma_i8_n128_sts"):
-    v = ctx.measure_peak(kind)
-    out[kind] = {"ops_per_s": v, "ops_per_s_per_sm": v / sm}
-print(json.dumps(out))
+for kind in ("mma_i8_n128", "mma_i8_n256", "mma_bf16_n256", "mma_i8_n128_sts", "mma2_i8_m256n256", "mma2_bf16_m256n256"):
+    try:
+        print("%-22s %.1f Tops/s" % (kind, ctx.measure_peak(kind) / 1e12), flush=True)
+    except Exception as e:
+        print(kind, "FAILED", e, flush=True)
+ctx.close()
