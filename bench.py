@@ -342,13 +342,21 @@ def run_ours(args):
     eng.ctx.sync()
     barrier()
     t0 = time.perf_counter()
+    ph = np.zeros(4)
     for s_ in range(e2e_steps):
         c, n_ = (s_ + 1) & 1, s_ & 1
+        p0 = time.perf_counter()
         descriptors(slots[n_])         # step s+1: descriptors now, keyframes behind this step's small copies
+        p1 = time.perf_counter()
         start(slots[c], c)             # step s: K1, pair list, K2 + K3 enqueued
+        p2 = time.perf_counter()
         keyframes(slots[n_])           # step s+1's keyframes travel while step s is verified
+        p3 = time.perf_counter()
         eng.ctx.sync()                 # step s's results are in the caller's buffers
+        p4 = time.perf_counter()
+        ph += (p1 - p0, p2 - p1, p3 - p2, p4 - p3)
         r_e2e = outs[c]
+    e2e_phases_ms = dict(zip(("db_append", "search_and_enqueue", "keyframes_enqueue", "wait_results"), (ph / e2e_steps * 1e3).tolist()))
     slots[n_].local.wait()             # the last submitted upload completes inside the timed region
     slots[n_].peer.wait()
     torch.cuda.synchronize()
@@ -454,7 +462,8 @@ def run_ours(args):
                 "dtype": "s8/s32 (Hamming GEMM) + f64 (PnP, NetVLAD)" if match_kernel == "tensor" else "u32+f64",
                 "data": "synthetic", "config": workload_config(args), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
-                        "steps": e2e_steps, "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified",
+                        "steps": e2e_steps, "host_phases_ms": e2e_phases_ms,
+                        "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified",
                         "upload": ("lazy key points: descriptors + counts of every frame are copied, kp2d / kp3d rows are pulled by the "
                                    "device from pinned host memory for the frames whose pairs reach PnP (sepb_frames_bind_host_async)")
                         if lazy else "full keyframes (52 B per feature)"},

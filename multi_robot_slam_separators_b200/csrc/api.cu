@@ -5,12 +5,14 @@
 
 int sepb_launch_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs, float nndr,
                       int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
-                      uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to) {
+                      uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to, const LazyPull* lazy) {
   const int opt = ctx->opt_match_kernel;
   const bool tensor = opt == SEPB_MATCH_TENSOR || (opt == SEPB_MATCH_AUTO && sepb_hamming_mma_supported(from, to));
-  return (tensor ? sepb_launch_hamming_mma : sepb_launch_hamming_match)(ctx, from, to, d_pairs, n_pairs, nndr, strict,
-                                                                      d_knn_idx, d_knn_dist, d_n_matches, d_match_from,
-                                                                      d_match_to, d_n_unique_to);
+  if (tensor)
+    return sepb_launch_hamming_mma(ctx, from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx, d_knn_dist, d_n_matches,
+                                   d_match_from, d_match_to, d_n_unique_to, lazy);
+  return sepb_launch_hamming_match(ctx, from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx, d_knn_dist, d_n_matches,
+                                   d_match_from, d_match_to, d_n_unique_to);
 }
 
 extern "C" {

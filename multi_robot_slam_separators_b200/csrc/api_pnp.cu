@@ -149,8 +149,10 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   const int mw = (from->max_feat + 31) / 32;
   // released when this function returns, i.e. after the last kernel that reads the stores (covariance, K2G) was enqueued
   FramesUse use(ctx, from, to);
+  // host-bound stores: the matcher pulls the key points of the pairs that will reach PnP while it runs
+  const LazyPull lp = sepb_lazy_pull_of(const_cast<sepb_frames*>(from), const_cast<sepb_frames*>(to), pprm->min_inliers);
   int rc = sepb_launch_match(ctx, view_of(from), view_of(to), d_pairs, n_pairs, mprm->nndr, mprm->nndr_strict,
-                                     nullptr, nullptr, o->n_matches, o->match_from, o->match_to, d_nu);
+                                     nullptr, nullptr, o->n_matches, o->match_from, o->match_to, d_nu, &lp);
   if (rc) return rc;
   rc = pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm,
                        d_custom_samples, custom_h, nullptr, nullptr, o->status, o->n_inliers, o->pose, o->transform,

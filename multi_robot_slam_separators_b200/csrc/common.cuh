@@ -106,6 +106,45 @@ struct FramesView {
 #endif
 };
 
+// host-bound stores: what a matcher needs to pull the key points of a pair that will run PnP while the rest of the
+// batch is still being matched (the PCIe reads spread over K2 instead of a fetch phase between K2 and K3)
+struct LazyPull {
+  int min_matches;                 // 0: off
+  float* from_kp3d;                // device rows / host rows / resident bits / byte counter of the From store
+  const float* from_kp3d_host;
+  uint8_t* from_have;
+  unsigned long long* from_fetched;
+  int from_first, from_n;
+  float* to_kp2d;
+  const float* to_kp2d_host;
+  uint8_t* to_have;
+  unsigned long long* to_fetched;
+  int to_first, to_n;
+};
+
+#ifdef __CUDACC__
+// CTA-wide copy of one row out of mapped host memory (16-byte loads when both sides allow it)
+__device__ __forceinline__ void sepb_pull_row(void* dst, const void* src, int bytes) {
+  if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
+    const int n16 = bytes >> 4;
+    const int4* s = reinterpret_cast<const int4*>(src);
+    int4* d = reinterpret_cast<int4*>(dst);
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) d[i] = __ldcs(s + i);
+    for (int i = (n16 << 4) + 4 * threadIdx.x; i < bytes; i += 4 * blockDim.x)
+      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
+  } else {
+    for (int i = 4 * threadIdx.x; i < bytes; i += 4 * blockDim.x)
+      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
+  }
+}
+// first CTA to ask for `bit` of a slot's row claims the copy (one lane calls; the resident bits are bytes)
+__device__ __forceinline__ bool sepb_claim_row(uint8_t* have, int slot, unsigned bit) {
+  const unsigned sh = 8u * ((unsigned)slot & 3u);
+  const unsigned old = atomicOr(reinterpret_cast<unsigned int*>(have + (slot & ~3)), bit << sh);
+  return !((old >> sh) & bit);
+}
+#endif
+
 static inline FramesView view_of(const sepb_frames* f) {
   return FramesView{f->desc, f->kp2d, f->kp3d, f->octave, f->count, f->max_feat, f->size,
                     f->lazy ? f->h_kp3d : nullptr, f->lazy ? f->lazy_first : 0, f->lazy ? f->lazy_n : 0};
@@ -216,11 +255,13 @@ int sepb_launch_hamming_match(sepb_ctx* ctx, FramesView from, FramesView to, con
 bool sepb_hamming_mma_supported(const FramesView& from, const FramesView& to);
 int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                             float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
-                            uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to);
-// dispatch on ctx->opt_match_kernel
+                            uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to,
+                            const LazyPull* lazy = nullptr);
+// dispatch on ctx->opt_match_kernel.  lazy (optional, host-bound stores): the tensor matcher pulls the key points of
+// the pairs with at least lazy->min_matches correspondences in its tail (the POPC kernel leaves that to the fetch kernels)
 int sepb_launch_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs, float nndr,
                       int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
-                      uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to);
+                      uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to, const LazyPull* lazy = nullptr);
 
 int sepb_launch_guess_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                             const int32_t* d_status1, const float* d_transform1, const sepb_pnp_params* p, int width,
@@ -230,6 +271,7 @@ int sepb_launch_pose_cov(sepb_ctx* ctx, FramesView from, FramesView to, const in
                          const int32_t* d_status, const int32_t* d_n_matches, const uint16_t* d_match_from,
                          const uint16_t* d_match_to, const uint32_t* d_inlier_mask, int mask_words,
                          const float* d_transform, double* d_cov);
+LazyPull sepb_lazy_pull_of(sepb_frames* from, sepb_frames* to, int min_matches);
 int sepb_launch_frames_fetch(sepb_ctx* ctx, sepb_frames* from, sepb_frames* to, const int32_t* d_pairs, int n_pairs,
                              const int32_t* d_n_matches, int min_matches, const int32_t* d_status, int bits_from, int bits_to);
 int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H, int model_points);

@@ -24,23 +24,6 @@ __global__ void frames_mark_kernel(const int32_t* pairs, int n_pairs, const int3
   if (need_to && bits_to) atomicOr(reinterpret_cast<unsigned int*>(need_to + (ti & ~3)), (unsigned)bits_to << (8 * (ti & 3)));
 }
 
-__device__ __forceinline__ void pull_row(void* dst, const void* src, int bytes) {
-  // rows start 16-byte aligned (row strides are multiples of 16 bytes for every supported max_feat multiple of 4;
-  // otherwise fall back to 4-byte words)
-  if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
-    const int n16 = bytes >> 4;
-    const int4* s = reinterpret_cast<const int4*>(src);
-    int4* d = reinterpret_cast<int4*>(dst);
-    for (int i = threadIdx.x; i < n16; i += blockDim.x) d[i] = __ldcs(s + i);
-    const int done = n16 << 4;
-    for (int i = done + 4 * threadIdx.x; i < bytes; i += 4 * blockDim.x)
-      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
-  } else {
-    for (int i = 4 * threadIdx.x; i < bytes; i += 4 * blockDim.x)
-      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
-  }
-}
-
 // CTA per slot of the binding: copy what is needed and not yet resident
 __global__ void __launch_bounds__(128) frames_fetch_kernel(float* kp2d, float* kp3d, int32_t* octave, const int32_t* count,
                                                            int max_feat, int first, uint8_t* need, uint8_t* have,
@@ -57,9 +40,9 @@ __global__ void __launch_bounds__(128) frames_fetch_kernel(float* kp2d, float* k
   const int n = min(max(count[slot], 0), max_feat);
   const size_t row = (size_t)slot * max_feat, hrow = (size_t)rel * max_feat;
   unsigned long long bytes = 0;
-  if ((want & 1) && h_kp2d) { pull_row(kp2d + row * 2, h_kp2d + hrow * 2, n * 8); bytes += (unsigned long long)n * 8; }
-  if ((want & 2) && h_kp3d) { pull_row(kp3d + row * 3, h_kp3d + hrow * 3, n * 12); bytes += (unsigned long long)n * 12; }
-  if ((want & 4) && h_octave) { pull_row(octave + row, h_octave + hrow, n * 4); bytes += (unsigned long long)n * 4; }
+  if ((want & 1) && h_kp2d) { sepb_pull_row(kp2d + row * 2, h_kp2d + hrow * 2, n * 8); bytes += (unsigned long long)n * 8; }
+  if ((want & 2) && h_kp3d) { sepb_pull_row(kp3d + row * 3, h_kp3d + hrow * 3, n * 12); bytes += (unsigned long long)n * 12; }
+  if ((want & 4) && h_octave) { sepb_pull_row(octave + row, h_octave + hrow, n * 4); bytes += (unsigned long long)n * 4; }
   __syncthreads();
   if (threadIdx.x == 0) {
     have[slot] |= want;
@@ -69,6 +52,21 @@ __global__ void __launch_bounds__(128) frames_fetch_kernel(float* kp2d, float* k
 }
 
 }  // namespace
+
+LazyPull sepb_lazy_pull_of(sepb_frames* from, sepb_frames* to, int min_matches) {
+  LazyPull lp{};
+  if (!(from->lazy || to->lazy) || min_matches <= 0) return lp;
+  lp.min_matches = min_matches;
+  if (from->lazy) {
+    lp.from_kp3d = from->kp3d; lp.from_kp3d_host = from->h_kp3d; lp.from_have = from->have; lp.from_fetched = from->fetched;
+    lp.from_first = from->lazy_first; lp.from_n = from->lazy_n;
+  }
+  if (to->lazy) {
+    lp.to_kp2d = to->kp2d; lp.to_kp2d_host = to->h_kp2d; lp.to_have = to->have; lp.to_fetched = to->fetched;
+    lp.to_first = to->lazy_first; lp.to_n = to->lazy_n;
+  }
+  return lp;
+}
 
 // flag + pull for one call.  bits: 1 kp2d, 2 kp3d, 4 octave.  No-op for stores that are not host-bound.
 int sepb_launch_frames_fetch(sepb_ctx* ctx, sepb_frames* from, sepb_frames* to, const int32_t* d_pairs, int n_pairs,

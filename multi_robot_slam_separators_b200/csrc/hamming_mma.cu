@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(kThreadsT, 1)
 hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs, float nndr, int strict,
                    int32_t* __restrict__ knn_idx, int32_t* __restrict__ knn_dist, int32_t* __restrict__ n_matches,
                    uint16_t* __restrict__ match_from, uint16_t* __restrict__ match_to,
-                   int32_t* __restrict__ n_unique_to) {
+                   int32_t* __restrict__ n_unique_to, const LazyPull lp) {
   using G = Geo<TN>;
   constexpr int kGroupsPerTile = G::kGroupsPerTile, kBStages = G::kBStages, CH = G::CH, kTStages = G::kTStages,
                 kTShift = G::kTShift, kBBytes = G::kBBytes, kBxBytes = G::kBxBytes;
@@ -191,6 +191,7 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   __shared__ uint32_t tmem_slot;
   __shared__ int s_scan[kThreadsT / 32];
   __shared__ int s_dropped;
+  __shared__ int s_claim[2];
 
   const int pair = blockIdx.x;
   if (pair >= n_pairs) return;
@@ -486,8 +487,27 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
     return;
   }
   const float* p3 = from.kp3d_early(fi);
-  mtail::unique_and_compact<kThreadsT>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
-                                       (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to, n_unique_to);
+  const int total = mtail::unique_and_compact<kThreadsT>(tid, nf, nt, p3, s_assigned, s_count, s_owner, s_scan, &s_dropped,
+                                                         (size_t)pair * from.max_feat, pair, n_matches, match_from, match_to,
+                                                         n_unique_to);
+  // host-bound stores: this pair will run PnP -> pull its From 3-D points and To pixels now, while the other CTAs are
+  // still matching (the first CTA that wants a row copies it; K3 is a later kernel, so every copy has landed by then)
+  if (lp.min_matches > 0 && total >= lp.min_matches) {
+    const unsigned rf = (unsigned)(fi - lp.from_first), rt = (unsigned)(ti - lp.to_first);
+    if (tid == 0) {
+      s_claim[0] = lp.from_kp3d_host && rf < (unsigned)lp.from_n && sepb_claim_row(lp.from_have, fi, 2u);
+      s_claim[1] = lp.to_kp2d_host && rt < (unsigned)lp.to_n && sepb_claim_row(lp.to_have, ti, 1u);
+    }
+    __syncthreads();
+    if (s_claim[0]) {
+      sepb_pull_row(lp.from_kp3d + (size_t)fi * from.max_feat * 3, lp.from_kp3d_host + (size_t)rf * from.max_feat * 3, nf * 12);
+      if (tid == 0) atomicAdd(lp.from_fetched, (unsigned long long)nf * 12);
+    }
+    if (s_claim[1]) {
+      sepb_pull_row(lp.to_kp2d + (size_t)ti * to.max_feat * 2, lp.to_kp2d_host + (size_t)rt * to.max_feat * 2, nt * 8);
+      if (tid == 0) atomicAdd(lp.to_fetched, (unsigned long long)nt * 8);
+    }
+  }
   K2T_STAMP(tid == 0, 3);
 }
 
@@ -512,8 +532,9 @@ bool sepb_hamming_mma_supported(const FramesView& from, const FramesView& to) { 
 
 int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                             float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
-                            uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to) {
+                            uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to, const LazyPull* lazy) {
   if (n_pairs == 0) return SEPB_OK;
+  const LazyPull lp = lazy ? *lazy : LazyPull{};
   if (!sepb_hamming_mma_supported(from, to))
     return sepb_fail(ctx, SEPB_E_SHAPE, "hamming_mma: frame too large for the tensor kernel", __FILE__, __LINE__);
   bool wide = geo_fits<256>(from, to);
@@ -528,11 +549,11 @@ int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const
   if (wide)
     hamming_mma_kernel<256><<<n_pairs, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
                                                                       d_knn_dist, d_n_matches, d_match_from, d_match_to,
-                                                                      d_n_unique_to);
+                                                                      d_n_unique_to, lp);
   else
     hamming_mma_kernel<128><<<n_pairs, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
                                                                       d_knn_dist, d_n_matches, d_match_from, d_match_to,
-                                                                      d_n_unique_to);
+                                                                      d_n_unique_to, lp);
   ctx->launches++;
   SEPB_CUDA(ctx, cudaGetLastError());
   return SEPB_OK;

@@ -14,10 +14,10 @@ __device__ __forceinline__ int nndr_assign(int i1, int d1, int i2, int d2, float
   return (strict ? (lhs < rhs) : (lhs <= rhs)) ? i1 : -1;
 }
 
-// Block-wide.  Requires: s_assigned[0..nt) final and visible (caller synchronised), s_count[0..nf) zeroed,
+// Block-wide; returns the list length.  Requires: s_assigned[0..nt) final and visible (caller synchronised), s_count[0..nf) zeroed,
 // *s_dropped == 0.  s_scan holds THREADS/32 ints.  THREADS * 32 >= max features per frame.
 template <int THREADS>
-__device__ __forceinline__ void unique_and_compact(int tid, int nf, int nt, const float* __restrict__ p3,
+__device__ __forceinline__ int unique_and_compact(int tid, int nf, int nt, const float* __restrict__ p3,
                                                    const int32_t* s_assigned, uint32_t* s_count, uint16_t* s_owner,
                                                    int* s_scan, int* s_dropped, size_t obase, int pair,
                                                    int32_t* __restrict__ n_matches, uint16_t* __restrict__ match_from,
@@ -77,6 +77,7 @@ __device__ __forceinline__ void unique_and_compact(int tid, int nf, int nt, cons
     n_matches[pair] = total;
     if (n_unique_to) n_unique_to[pair] = nt - *s_dropped;
   }
+  return total;   // the length of the correspondence list, in every thread
 }
 
 }  // namespace mtail
