@@ -42,7 +42,7 @@ def workload_config(args):
                            "unrelated frames send ~30 all-outlier correspondences into RANSAC" if args.mix == "hard" else ""),
             "keyframes_per_robot": args.frames, "features_per_frame": args.feat, "netvlad_dim": args.dim,
             "top_k": args.topk, "pairs_per_step_per_gpu": args.frames * args.topk, "ransac_iterations": args.iterations,
-            "mix": args.mix, "nndr": 0.8, "netvlad_distance": "inf (every top-k candidate is verified)",
+            "mix": args.mix, "pnp_flags": {0: "ITERATIVE (5-point EPnP sets)", 2: "P3P (4-point sets, EPnP refit)"}[args.pnp_flags], "nndr": 0.8, "netvlad_distance": "inf (every top-k candidate is verified)",
             "l2_policy": "inputs larger than L2 (feature stores 1.1 GB per GPU, 126 MB L2)",
             "partition": "independent robot pair per rank, no collective on the data path"}
 
@@ -141,7 +141,8 @@ def _cpu_verify_pair(p):
     obj, img, _, _ = matching.pnp_correspondences(pairs, A.kp3d[fa], B.kp2d[tb])
     if len(obj) < 5:
         return 0
-    ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, S["K"], S["rv0"], S["tv0"], iterations=S["iterations"])
+    ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, S["K"], S["rv0"], S["tv0"], iterations=S["iterations"],
+                                              flags=S.get("pnp_flags", 0))
     return int(ok and len(inl) >= 5)
 
 
@@ -163,7 +164,7 @@ def make_cpu_sample(args, seed, n_queries):
     rv0, _ = cv2.Rodrigues(synth.R_LOCAL.T.copy())
     return dict(q=nv_b[rows], db=nv_a, k=args.topk, A=A, B=B, a_slot={int(f): i for i, f in enumerate(need_a)},
                 b_slot={int(r): i for i, r in enumerate(rows)}, K=K, rv0=rv0.ravel(), tv0=np.zeros(3),
-                iterations=args.iterations)
+                iterations=args.iterations, pnp_flags=args.pnp_flags)
 
 
 def run_reference(args):
@@ -219,7 +220,7 @@ def run_ours(args):
     A, B = synth.make_robots(2, args.frames, n_feat=args.feat, dim=args.dim, seed=2000 + rank, **synth_kwargs(args))
     t_gen = time.time() - t0
     eng = SeparatorEngine(Camera(synth.FX, synth.FY, synth.CX, synth.CY), args.feat, args.dim, args.frames, args.frames,
-                          device=local_rank, iterations=args.iterations)
+                          device=local_rank, iterations=args.iterations, pnp_flags=args.pnp_flags)
     eng.ctx.set_match_kernel(args.match)
     match_kernel = "popc" if args.match == "popc" else "tensor"
     P = args.frames * args.topk
@@ -308,7 +309,7 @@ def run_ours(args):
     # travel on the copy stream while the current step is verified (sepb_frames_upload_async).
     e2e_steps = max(1, args.steps if args.e2e_steps <= 0 else min(args.steps, args.e2e_steps))
     eng_b = SeparatorEngine(Camera(synth.FX, synth.FY, synth.CX, synth.CY), args.feat, args.dim, args.frames, args.frames,
-                            device=local_rank, ctx=eng.ctx, iterations=args.iterations)
+                            device=local_rank, ctx=eng.ctx, iterations=args.iterations, pnp_flags=args.pnp_flags)
     slots = [eng, eng_b]
 
     def pinned(shape, dtype):
@@ -462,7 +463,8 @@ def run_ours(args):
                            "peak_source": peak_src + " (bf16 burst)", "algorithmic_flop": "2*Q*N*D",
                            "frac_of_sustained": k1_tflops / bf16_sust,
                            "note": "the 3-term split-bf16 filter issues 3x the algorithmic FLOP on the tensor pipe"}
-        k3_ops = n_ransac * iters_mean * (1.1e5 + 30.0 * m_mean)   # H_eff * (C_epnp + 30*M)
+        c_solve = 1.1e5 if args.pnp_flags == 0 else 2.5e3          # f64 ops of one 5-point EPnP / one 4-point P3P solve
+        k3_ops = n_ransac * iters_mean * (c_solve + 30.0 * m_mean)   # H_eff * (C_solve + 30*M)
         ransac_pairs_per_s = world * n_ransac / max(ms_k3 * 1e-3, 1e-12)
         rooflines["K3"] = {"kernel": "pnp_ransac_kernel (K3)", "bound": "fp64 issue", "achieved": k3_ops / max(ms_k3, 1e-9) / 1e-3,
                            "peak": dfma_peak, "unit": "f64 op/s", "frac": k3_ops / max(ms_k3, 1e-9) / 1e-3 / dfma_peak,
@@ -844,6 +846,8 @@ def main():
     ap.add_argument("--mix", default="clean", choices=["clean", "hard"],
                     help="synthetic clutter: uniform random descriptors (clean: unrelated frames produce ~no matches) or a shared "
                          "vocabulary (hard: unrelated frames reach RANSAC with all-outlier sets and burn every iteration)")
+    ap.add_argument("--pnp-flags", type=int, default=0, choices=[0, 2],
+                    help="Vis/PnPFlags: 0 = ITERATIVE (the reference's default: 5-point EPnP minimal sets), 2 = P3P (4-point sets)")
     ap.add_argument("--nn", default="tensor", choices=["exact", "tensor"],
                     help="NetVLAD search: tcgen05 split-bf16 filter + exact f64 re-rank (tensor) or full f64 scan (exact); identical results")
     ap.add_argument("--match", default="auto", choices=["auto", "popc", "tensor"],

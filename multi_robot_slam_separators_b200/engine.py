@@ -34,7 +34,8 @@ class SeparatorEngine:
 
     def __init__(self, cam: Camera, max_feat: int, dim: int, local_capacity: int, peer_capacity: int, device: int = 0,
                  iterations: int = 300, min_inliers: int = 5, reproj_error: float = 2.0, nndr: float = 0.8,
-                 db_base: int = 0, ctx: capi.Context | None = None, image_size=(1241, 376), guess_win_size: float = 20.0):
+                 db_base: int = 0, ctx: capi.Context | None = None, image_size=(1241, 376), guess_win_size: float = 20.0,
+                 pnp_flags: int = 0, refine_iterations: int = 0, minimal_model: bool = False):
         """ctx: share another engine's context (one stream, one copy stream): two engines then act as the two
         buffers of a pipeline -- the next round's keyframes upload while the current round is verified."""
         self.device = device
@@ -48,7 +49,8 @@ class SeparatorEngine:
         self.db = capi.NetvladDB(self.ctx, dim, peer_capacity, base=db_base)
         self.db_base = db_base
         self.pnp = capi.pnp_params(cam.fx, cam.fy, cam.cx, cam.cy, iterations=iterations, min_inliers=min_inliers,
-                                   reproj_error=reproj_error)
+                                   reproj_error=reproj_error, flags=pnp_flags, refine_iterations=refine_iterations,
+                                   minimal_model=minimal_model)
         self.mp = capi.MatchParams(nndr, 0)
         self.guess = capi.guess_params(image_size[0], image_size[1], guess_win_size)
         self.n_local = 0
