@@ -407,6 +407,8 @@ struct PnpQueue {          // device memory, head (ctrl, wk, slot_ready) zeroed 
   int32_t* list;           // [n_pairs] pairs that run RANSAC
   int32_t* slot_good;      // [n_workers][max_chunks][32] inlier counts
   double* slot_rt;         // [n_workers][max_chunks][12][32] R (9) | t (3), hypothesis-minor
+  double* pre_rt;          // [n_workers][12][32] poses of the NEXT pair's first hypotheses, solved by the spare lanes of a
+                           // worker's last chunk (null: off)
   int n_workers, max_chunks;   // max_chunks == 0: helping disabled
 };
 
@@ -504,18 +506,33 @@ struct WarpScratch {
 // ---- solve: lane <-> hypothesis.  h_cap: hypotheses at or past it are never consumed (their lanes redo h_cap - 1).
 // MP = model points: 5 -> EPnP, 4 -> P3P (a set without a solution gets a NaN translation: it scores no inlier, which
 // is what the skipped iteration of RANSACPointSetRegistrator::run amounts to).  rv_out (optional): the model as rvec.
+// nx (optional): the pair this worker runs next.  The lanes past h_cap -- which would only repeat hypothesis h_cap - 1 --
+// solve ITS hypotheses 0 .. instead (lane chunk0 + lane - h_cap -> hypothesis lane - (h_cap - chunk0)); a hypothesis is a
+// pure function of (pair, index), so who solves it and when changes nothing.  Their poses go to `stash` ([12][32]).
 template <int MP>
 __device__ __forceinline__ void solve_chunk(const PnpArgs& a, const PairIn& in, const WarpScratch& ws, int chunk0, int h_cap,
-                                            double* Rh, double* th, double* rv_out = nullptr) {
+                                            double* Rh, double* th, double* rv_out = nullptr, const PairIn* nx = nullptr,
+                                            double* stash = nullptr) {
   const int lane = threadIdx.x & 31;
   const cvm::Heap heap{ws.heap_base + lane};
   int h = chunk0 + lane;
+  const int useful = h_cap - chunk0;          // lanes [0, useful) belong to `in`
+  const bool spare = nx && lane >= useful;
   if (h >= h_cap) h = h_cap - 1;
   float o[3 * MP], im[2 * MP];
-  for (int i = 0; i < MP; ++i) {
-    const int s = a.custom_samples ? a.custom_samples[((size_t)in.pair * a.custom_h + h) * MP + i]
-                                   : a.table[((size_t)in.M * a.prm.table_h + h) * MP + i];
-    in.cr.load(min(max(s, 0), in.M - 1), o + 3 * i, im + 2 * i);
+  if (spare) {
+    const int hn = lane - useful;
+    for (int i = 0; i < MP; ++i) {
+      const int s = a.custom_samples ? a.custom_samples[((size_t)nx->pair * a.custom_h + hn) * MP + i]
+                                     : a.table[((size_t)nx->M * a.prm.table_h + hn) * MP + i];
+      nx->cr.load_global(min(max(s, 0), nx->M - 1), o + 3 * i, im + 2 * i);
+    }
+  } else {
+    for (int i = 0; i < MP; ++i) {
+      const int s = a.custom_samples ? a.custom_samples[((size_t)in.pair * a.custom_h + h) * MP + i]
+                                     : a.table[((size_t)in.M * a.prm.table_h + h) * MP + i];
+      in.cr.load(min(max(s, 0), in.M - 1), o + 3 * i, im + 2 * i);
+    }
   }
   __syncwarp();   // every lane has read its samples from the staging area before a solve overwrites it
   double R0[9], rv[3];
@@ -537,6 +554,13 @@ __device__ __forceinline__ void solve_chunk(const PnpArgs& a, const PairIn& in, 
   if (!solved) th[0] = th[1] = th[2] = __longlong_as_double(0x7FF8000000000000LL);
   if (rv_out)
     for (int i = 0; i < 3; ++i) rv_out[i] = rv[i];
+  if (spare) {
+    const int hn = lane - useful;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) stash[i * 32 + hn] = Rh[i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) stash[(9 + i) * 32 + hn] = th[i];
+  }
   __syncwarp();
   in.cr.stage(ws.stage_buf, in.M);   // the solve overwrote the staging area
 }
@@ -570,15 +594,17 @@ __device__ __forceinline__ int score_one(const PnpArgs& a, const PairIn& in, con
 // a whole chunk for somebody else's scan: solve, score every hypothesis, leave counts and poses in the owner's slot
 template <int MP>
 __device__ __noinline__ void chunk_to_slot(const PnpArgs& a, const PnpQueue& q, const PairIn& in, const WarpScratch& ws,
-                                           int owner, int cc, uint32_t* cand) {
+                                           int owner, int cc, int h_off, uint32_t* cand) {
   const int lane = threadIdx.x & 31;
   double Rh[9], th[3];
-  solve_chunk<MP>(a, in, ws, cc * kSolveLanes, a.prm.iterations, Rh, th);
+  // h_off: the pair's first h_off hypotheses were solved ahead of time by its owner's previous pair; chunk cc of the
+  // pair covers hypotheses h_off + 32 cc ..
+  solve_chunk<MP>(a, in, ws, h_off + cc * kSolveLanes, a.prm.iterations, Rh, th);
   K3_T0(t_s);
   int mygood = 0;
   for (int k = 0; k < kSolveLanes; ++k) {
     // the owner's published bound never undercuts its live iteration count: what lies past it is never consumed
-    if (cc * kSolveLanes + k >= ld_volatile_warp(q.wk + 4 * owner + 2)) break;
+    if (h_off + cc * kSolveLanes + k >= ld_volatile_warp(q.wk + 4 * owner + 2)) break;
     double R[9], t[3];
 #pragma unroll
     for (int i = 0; i < 9; ++i) R[i] = __shfl_sync(0xFFFFFFFFu, Rh[i], k);
@@ -604,8 +630,14 @@ __device__ __noinline__ void chunk_to_slot(const PnpArgs& a, const PnpQueue& q, 
 
 // One keyframe pair, one warp.  worker >= 0: persistent kernel (chunks are claimed from the owner's counter and may
 // arrive from helpers); worker < 0: the warp runs every chunk itself.
+// pre: this pair's hypotheses [0, pre) are already solved (poses in the worker's stash).  next_pair / next_pre (persistent
+// kernel): when the pair's LAST chunk has spare lanes, the worker pops its next pair early and those lanes solve its first
+// hypotheses (*next_pair: -1 nothing popped, -2 the list is exhausted, else the pair; *next_pre: how many were solved).
+// The spare lanes exist because a chunk costs the same whatever the number of useful lanes; the average pair wastes
+// half a chunk of ~2.9 that way.
 template <int MP>
-__device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, int worker, int pair, const WarpScratch& ws) {
+__device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, int worker, int pair, const WarpScratch& ws,
+                                         int pre = 0, int* next_pair = nullptr, int* next_pre = nullptr) {
   const PnpKernelParams& prm = a.prm;
   const int lane = threadIdx.x & 31;
   const cvm::Heap heap{ws.heap_base + lane};
@@ -656,19 +688,48 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
   bool best_in_smem = true;    // the mask of the best hypothesis is in s_mask[cur] (else: re-score it from its slot)
   const bool queued = worker >= 0 && q.max_chunks > 0;
   int32_t* wk = queued ? q.wk + 4 * worker : nullptr;
+  const int h_off = pre;   // chunk c of this pair covers hypotheses h_off + 32 c ..
+  double* stash = (worker >= 0 && q.pre_rt) ? q.pre_rt + (size_t)worker * 12 * 32 : nullptr;
   if (queued) {
     if (lane == 0) {
       st_volatile(wk + 0, pair);
       st_volatile(wk + 1, 0);
       st_volatile(wk + 2, niters);
       __threadfence();
-      st_volatile(wk + 3, 1);
+      st_volatile(wk + 3, 1 | (h_off << 1));   // accepting help; helpers need the hypothesis offset of chunk 0
     }
     __syncwarp();
   }
   cr.stage(ws.stage_buf, M);
+  if (pre > 0) {
+    // ---- the hypotheses solved ahead of time: score them first, in order, like any chunk
+    double Rh[9], th[3];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) Rh[i] = lane < pre ? stash[i * 32 + lane] : 0.0;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) th[i] = lane < pre ? stash[(9 + i) * 32 + lane] : 0.0;
+    for (int k = 0; k < pre; ++k) {
+      hk = k;
+      if (hk >= niters) break;
+      double R[9], t[3];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) R[i] = __shfl_sync(0xFFFFFFFFu, Rh[i], k);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) t[i] = __shfl_sync(0xFFFFFFFFu, th[i], k);
+      const int good = score_one(a, in, R, t, s_mask + (cur ^ 1) * kMaskWords);
+      if (good > max(best_good, MP - 1)) {
+        cur ^= 1;
+        best_good = good;
+        best_h = hk;
+        best_in_smem = true;
+        niters = cvm::ransac_update_num_iters(prm.confidence, (double)(M - good) / M, MP, niters);
+      }
+      hk = hk + 1;
+    }
+    if (queued && lane == 0) st_volatile(wk + 2, niters);
+  }
   int c_next = 0;   // chunks below it have been consumed
-  while (c_next * kSolveLanes < niters) {
+  while (h_off + c_next * kSolveLanes < niters) {
     int my = c_next;
     if (queued) {
       if (lane == 0) my = atomicAdd(wk + 1, 1);
@@ -676,9 +737,31 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
     }
     if (my == c_next) {
       // ---- nobody is helping: solve, then score in RANSAC order with the live early exit
-      const int chunk = my * kSolveLanes;
+      const int chunk = h_off + my * kSolveLanes;
       double Rh[9], th[3];
-      solve_chunk<MP>(a, in, ws, chunk, niters, Rh, th);
+      // last chunk with spare lanes: pop the next pair now and let them solve its first hypotheses.  This only happens
+      // while the list is not exhausted, i.e. before any helper exists, and this pair needs no further chunk, so the
+      // "helped owners are on their last pair" rule of the slots still holds.
+      PairIn nx;
+      const PairIn* nxp = nullptr;
+      const int useful = niters - chunk;
+      if (stash && next_pair && *next_pair == -1 && useful < kSolveLanes) {
+        int slot = 0;
+        if (lane == 0) slot = atomicAdd(&q.ctrl[0], 1);
+        slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
+        if (slot >= q.ctrl[1]) {
+          *next_pair = -2;
+        } else {
+          *next_pair = q.list[slot];
+          nx = load_pair(a, *next_pair, nullptr);
+          if (nx.M > MP && prm.iterations >= kSolveLanes) {   // a pair that runs the RANSAC loop (not the 4 / 5 point cases)
+            nxp = &nx;
+            *next_pre = kSolveLanes - useful;
+          }
+          if (queued && lane == 0) st_volatile(wk + 3, 0);   // this is the last chunk: no help wanted any more
+        }
+      }
+      solve_chunk<MP>(a, in, ws, chunk, niters, Rh, th, nullptr, nxp, stash);
       K3_T0(t_s);
       for (int k = 0; k < kSolveLanes; ++k) {
         hk = chunk + k;
@@ -705,14 +788,14 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
       c_next = my + 1;
     } else {
       // ---- helpers hold chunks c_next .. my-1: do chunk `my` the way they do, then scan everything in order
-      if (my * kSolveLanes < niters) chunk_to_slot<MP>(a, q, in, ws, worker, my, s_mask + (cur ^ 1) * kMaskWords);
-      for (int cc = c_next; cc <= my && cc * kSolveLanes < niters; ++cc) {
+      if (h_off + my * kSolveLanes < niters) chunk_to_slot<MP>(a, q, in, ws, worker, my, h_off, s_mask + (cur ^ 1) * kMaskWords);
+      for (int cc = c_next; cc <= my && h_off + cc * kSolveLanes < niters; ++cc) {
         const size_t slot = (size_t)worker * q.max_chunks + cc;
         while (ld_volatile_warp(q.slot_ready + slot) == 0) __nanosleep(200);
         __threadfence();
         const int gk = *reinterpret_cast<const volatile int32_t*>(q.slot_good + slot * 32 + lane);
         for (int k = 0; k < kSolveLanes; ++k) {
-          hk = cc * kSolveLanes + k;
+          hk = h_off + cc * kSolveLanes + k;
           if (hk >= niters) break;
           const int good = __shfl_sync(0xFFFFFFFFu, gk, k);
           if (good > max(best_good, MP - 1)) {
@@ -742,8 +825,8 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
     return;
   }
   if (!best_in_smem) {   // the winner came out of a slot: its mask is one more scoring pass
-    const size_t slot = (size_t)worker * q.max_chunks + best_h / kSolveLanes;
-    const int k = best_h % kSolveLanes;
+    const size_t slot = (size_t)worker * q.max_chunks + (best_h - h_off) / kSolveLanes;
+    const int k = (best_h - h_off) % kSolveLanes;
     double R[9], t[3];
 #pragma unroll
     for (int i = 0; i < 9; ++i) R[i] = *reinterpret_cast<const volatile double*>(q.slot_rt + (slot * 12 + i) * 32 + k);
@@ -833,12 +916,24 @@ __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(P
   const int worker = blockIdx.x * kPersistWarps + (threadIdx.x >> 5);
   const int n_listed = q.ctrl[1];
   // ---- owner: pairs off the list until it is empty
+  int nxt = -1, npre = 0;   // pair popped early by the previous run_pair and how many of its hypotheses are solved
   for (;;) {
-    int slot = 0;
-    if (lane == 0) slot = atomicAdd(&q.ctrl[0], 1);
-    slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
-    if (slot >= n_listed) break;
-    run_pair<MP>(a, q, worker, q.list[slot], ws);
+    int pair, pre = 0;
+    if (nxt >= 0) {
+      pair = nxt;
+      pre = npre;
+    } else if (nxt == -2) {
+      break;
+    } else {
+      int slot = 0;
+      if (lane == 0) slot = atomicAdd(&q.ctrl[0], 1);
+      slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
+      if (slot >= n_listed) break;
+      pair = q.list[slot];
+    }
+    nxt = -1;
+    npre = 0;
+    run_pair<MP>(a, q, worker, pair, ws, pre, &nxt, &npre);
     __syncwarp();
     if (lane == 0) {
       __threadfence();
@@ -863,7 +958,7 @@ __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(P
       asm volatile("ld.volatile.global.v4.s32 {%0, %1, %2, %3}, [%4];"
                    : "=r"(w4.x), "=r"(w4.y), "=r"(w4.z), "=r"(w4.w)
                    : "l"(q.wk + 4 * i));
-      const int rem = w4.w ? w4.z - w4.y * kSolveLanes : 0;
+      const int rem = w4.w ? w4.z - ((w4.w >> 1) + w4.y * kSolveLanes) : 0;
       if (rem > best_rem) {
         best_rem = rem;
         best_w = i;
@@ -889,14 +984,14 @@ __global__ void __launch_bounds__(kWarp * kPersistWarps, 1) pnp_persist_kernel(P
     if (lane == 0) cc = atomicAdd(q.wk + 4 * best_w + 1, 1);
     cc = __shfl_sync(0xFFFFFFFFu, cc, 0);
     // the owner only waits for chunks below its live iteration count (<= the bound read here) while it accepts help
-    if (cc >= q.max_chunks || cc * kSolveLanes >= ld_volatile_warp(q.wk + 4 * best_w + 2) ||
-        !ld_volatile_warp(q.wk + 4 * best_w + 3))
-      continue;
+    const int w3 = ld_volatile_warp(q.wk + 4 * best_w + 3);
+    const int h_off = w3 >> 1;
+    if (cc >= q.max_chunks || !w3 || h_off + cc * kSolveLanes >= ld_volatile_warp(q.wk + 4 * best_w + 2)) continue;
     __threadfence();
     const int pair = ld_volatile_warp(q.wk + 4 * best_w);
     const PairIn in = load_pair(a, pair, ws.stage_buf);
     in.cr.stage(ws.stage_buf, in.M);
-    chunk_to_slot<MP>(a, q, in, ws, best_w, cc, ws.s_mask);
+    chunk_to_slot<MP>(a, q, in, ws, best_w, cc, h_off, ws.s_mask);
   }
 }
 
@@ -997,7 +1092,9 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   const size_t n_good = (size_t)n_workers * max_chunks * 32;
   size_t n_ints = n_head + (size_t)n_pairs + n_good;
   n_ints = (n_ints + 3) & ~(size_t)3;
-  const size_t want = n_ints + (size_t)n_workers * max_chunks * 12 * 32 * 2;   // doubles counted as two ints
+  const bool presolve = persistent && max_chunks > 0 && !sepb_dev_env("SEPB_K3_NO_PRESOLVE");
+  const size_t n_slot_rt = (size_t)n_workers * max_chunks * 12 * 32;
+  const size_t want = n_ints + (n_slot_rt + (presolve ? (size_t)n_workers * 12 * 32 : 0)) * 2;   // doubles counted as two ints
   if (want > ctx->k3_order_cap) {
     if (ctx->k3_order) {
       cudaStreamSynchronize(ctx->stream);
@@ -1016,6 +1113,7 @@ int sepb_launch_pnp_ransac(sepb_ctx* ctx, FramesView from, FramesView to, const 
   q.list = q.ctrl + n_head;
   q.slot_good = q.list + n_pairs;
   q.slot_rt = reinterpret_cast<double*>(ctx->k3_order + n_ints);
+  q.pre_rt = presolve ? q.slot_rt + n_slot_rt : nullptr;
   q.n_workers = n_workers;
   q.max_chunks = max_chunks;
   SEPB_CUDA(ctx, cudaMemsetAsync(q.ctrl, 0, n_head * sizeof(int32_t), ctx->stream));
