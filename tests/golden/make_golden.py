@@ -110,7 +110,62 @@ def golden_pnp_ransac():
     np.savez_compressed(os.path.join(OUT, "pnp_ransac.npz"), **out)
 
 
+def golden_p3p():
+    """cv2 at the call sites of the P3P / AP3P flag path and of exactly four correspondences
+    (R/src/myRegistrationVis.cpp:103,1084 -> cv::solvePnPRansac): per-set solvePnP(SOLVEPNP_P3P), the n-point EPnP
+    refit on f64 inputs, whole solvePnPRansac(flags=SOLVEPNP_P3P) runs, and (oracle/pnp.py:refine_model on top of cv2
+    calls) the Vis/PnPRefineIterations loop."""
+    rng = np.random.default_rng(105)
+    fx, fy, cx, cy = 500.0, 510.0, 320.0, 240.0
+    K = pnp.K_matrix(fx, fy, cx, cy)
+
+    def problem(n, outl, noise):
+        obj = rng.uniform(-2, 2, (n, 3)).astype(np.float32)
+        obj[:, 2] += 6
+        rv, tv = rng.normal(0, 0.3, 3), rng.normal(0, 0.5, 3)
+        img, _ = cv2.projectPoints(obj.astype(np.float64), rv, tv, K, None)
+        img = img.reshape(-1, 2).astype(np.float32) + rng.normal(0, noise, (n, 2)).astype(np.float32)
+        k = int(n * outl)
+        img[:k] += rng.uniform(-60, 60, (k, 2)).astype(np.float32)
+        return obj, img
+
+    out = dict(K=K)
+    # 4-point sets
+    o4, i4, ok4, r4, t4 = [], [], [], [], []
+    for _ in range(64):
+        obj, img = problem(4, 0.0, float(rng.uniform(0, 1.5)))
+        ok, rv, tv = cv2.solvePnP(obj, img, K, None, flags=cv2.SOLVEPNP_P3P)
+        ok = bool(ok) and bool(np.all(np.isfinite(rv))) and bool(np.all(np.isfinite(tv)))
+        o4.append(obj); i4.append(img); ok4.append(ok)
+        r4.append(rv.ravel() if ok else np.zeros(3)); t4.append(tv.ravel() if ok else np.zeros(3))
+    out.update(p3p_obj=np.array(o4), p3p_img=np.array(i4), p3p_ok=np.array(ok4), p3p_rvec=np.array(r4), p3p_tvec=np.array(t4))
+    # n-point EPnP on f64 inputs (the refit of the P3P-flag path)
+    ns = [4, 5, 6, 9, 33, 120, 400]
+    for j, n in enumerate(ns):
+        obj, img = problem(n, 0.0, 0.5)
+        o64, i64 = obj.astype(np.float64), img.astype(np.float64)
+        ok, rv, tv = cv2.solvePnP(o64, i64, K, None, flags=cv2.SOLVEPNP_EPNP)
+        out.update({f"epnpn_obj{j}": o64, f"epnpn_img{j}": i64, f"epnpn_rvec{j}": rv.ravel(), f"epnpn_tvec{j}": tv.ravel()})
+    out["epnpn_n"] = len(ns)
+    # whole RANSAC runs with the P3P flag, and the refine loop after the default-flag RANSAC
+    rv0, tv0 = np.zeros(3), np.zeros(3)
+    nr = 8
+    for j in range(nr):
+        obj, img = problem(int(rng.integers(12, 260)), float(rng.uniform(0.1, 0.5)), 0.5)
+        ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, K, rv0, tv0, iterations=200, flags=cv2.SOLVEPNP_P3P)
+        out.update({f"rs_obj{j}": obj, f"rs_img{j}": img, f"rs_ok{j}": ok, f"rs_rvec{j}": rv, f"rs_tvec{j}": tv, f"rs_inl{j}": inl})
+        ok, rv, tv, inl = pnp.cv_solve_pnp_ransac(obj, img, K, rv0, tv0, iterations=200)
+        if ok and len(inl) >= 5:
+            rv, tv, inl = pnp.refine_model(obj, img, K, rv, tv, inl, 5, 5)
+        out.update({f"rf_ok{j}": ok, f"rf_rvec{j}": rv, f"rf_tvec{j}": tv, f"rf_inl{j}": inl})
+    out["rs_n"] = nr
+    np.savez_compressed(os.path.join(OUT, "p3p.npz"), **out)
+
+
 if __name__ == "__main__":
-    golden_svd(); golden_hamming(); golden_netvlad(); golden_epnp(); golden_pnp_ransac()
+    if len(sys.argv) > 1 and sys.argv[1] == "p3p":      # round 2: only the new file (the others stay byte-identical)
+        golden_p3p()
+    else:
+        golden_svd(); golden_hamming(); golden_netvlad(); golden_epnp(); golden_pnp_ransac(); golden_p3p()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
