@@ -308,8 +308,17 @@ def run_ours(args):
     # reads the results back (D2H).  Two engines on one context act as a double buffer: the next step's keyframes
     # travel on the copy stream while the current step is verified (sepb_frames_upload_async).
     e2e_steps = max(1, args.steps if args.e2e_steps <= 0 else min(args.steps, args.e2e_steps))
+    # the place-recognition databases of the two slots move to a second context whose stream has the device's highest
+    # priority: the search of step s+1 (K1 + its small copies) then runs WHILE step s is verified -- its thread blocks
+    # are dispatched ahead of the pending blocks of the K2 grid -- instead of behind it
+    sctx = capi.Context(local_rank, high_priority=True) if args.e2e_search == "overlap" else eng.ctx
     eng_b = SeparatorEngine(Camera(synth.FX, synth.FY, synth.CX, synth.CY), args.feat, args.dim, args.frames, args.frames,
-                            device=local_rank, ctx=eng.ctx, iterations=args.iterations, pnp_flags=args.pnp_flags)
+                            device=local_rank, ctx=eng.ctx, iterations=args.iterations, pnp_flags=args.pnp_flags,
+                            search_ctx=sctx)
+    if sctx is not eng.ctx:
+        eng.db.close()
+        eng.db = capi.NetvladDB(sctx, args.dim, args.frames)
+        eng.search_ctx = sctx
     slots = [eng, eng_b]
 
     def pinned(shape, dtype):
@@ -340,9 +349,9 @@ def run_ours(args):
         capi.verify_pairs(e.ctx, e.peer, e.local, pairs_pin[slot], e.pnp, want_lists=False, out=outs[slot], async_=True)
 
     # Software pipeline over two slots (engines on one context = double-buffered stores and databases).  Step s:
-    #   verify(s) enqueued -> keyframes(s+1) on the copy stream -> descriptors(s+1) + search(s+1), whose device work is
-    #   queued behind verify(s) on the compute stream, so the blocking search returns when step s's results are in the
-    #   caller's buffers AND step s+1's candidates are known; the GPU only idles for the host time between the two.
+    #   verify(s) enqueued -> keyframes(s+1) on the copy stream -> descriptors(s+1) + search(s+1) on the search context
+    #   (own high-priority stream: concurrent with verify(s); with --e2e-search serial: same stream, behind it) -> wait for
+    #   step s's results.  The GPU only idles for the host time between the end of verify(s) and the enqueue of verify(s+1).
     for sl, e in enumerate(slots):
         descriptors(e)
         keyframes(e)
@@ -364,10 +373,9 @@ def run_ours(args):
         keyframes(slots[n_])           # step s+1's keyframes travel while step s is verified
         p2 = time.perf_counter()
         if s_ + 1 < e2e_steps:
-            descriptors(slots[n_])     # step s+1: peer descriptors and candidate search, behind verify(s) on the stream
+            descriptors(slots[n_])     # step s+1: peer descriptors and candidate search
             search(slots[n_], n_)
-        else:
-            eng.ctx.sync()
+        eng.ctx.sync()                 # step s's results are in the caller's buffers
         p3 = time.perf_counter()
         ph += (p1 - p0, p2 - p1, p3 - p2)
         r_e2e = outs[c]
@@ -479,7 +487,8 @@ def run_ours(args):
                 "data": "synthetic", "config": workload_config(args), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
                         "steps": e2e_steps, "host_phases_ms": e2e_phases_ms,
-                        "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified",
+                        "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified; its candidate search runs "
+                                    + ("on a high-priority second stream, concurrently" if args.e2e_search == "overlap" else "behind it on the same stream"),
                         "upload": ("lazy key points: descriptors + counts of every frame are copied, kp2d / kp3d rows are pulled by the "
                                    "device from pinned host memory for the frames whose pairs reach PnP (sepb_frames_bind_host_async)")
                         if lazy else "full keyframes (52 B per feature)"},
@@ -854,6 +863,9 @@ def main():
                     help="Hamming matcher kernel: tcgen05 int8 GEMM (tensor), POPC pipe (popc); identical results")
     ap.add_argument("--e2e-upload", default="lazy", choices=["lazy", "full"],
                     help="end-to-end leg: how keyframes reach the device (identical results)")
+    ap.add_argument("--e2e-search", default="overlap", choices=["overlap", "serial"],
+                    help="end-to-end leg: the next step's candidate search on a high-priority second context (overlap) or "
+                         "queued behind the verification on the same stream (serial)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (0 = --steps)")
     ap.add_argument("--cpu-queries", type=int, default=200)
     ap.add_argument("--no-cpu-baseline", action="store_true")

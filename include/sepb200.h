@@ -45,6 +45,10 @@ typedef struct sepb_group sepb_group;    /* the devices of one box + their NCCL 
 
 /* ---- context -------------------------------------------------------------------------- */
 SEPB_API int sepb_ctx_create(int device, sepb_ctx** out);
+/* Same, with the streams at the device's highest priority: a context for short, latency-bound work (the place-recognition
+ * search of the NEXT request round) whose thread blocks are dispatched ahead of the pending blocks of a long verification
+ * batch running on another context of the same device. */
+SEPB_API int sepb_ctx_create_priority(int device, sepb_ctx** out);
 SEPB_API void sepb_ctx_destroy(sepb_ctx* ctx);
 SEPB_API const char* sepb_last_error(const sepb_ctx* ctx);
 SEPB_API void* sepb_ctx_stream(const sepb_ctx* ctx);           /* cudaStream_t */

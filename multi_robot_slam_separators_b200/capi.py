@@ -73,6 +73,8 @@ def _declare(L):
     vp, i32, i64 = C.c_void_p, C.c_int, C.c_int64
     L.sepb_ctx_create.argtypes = [i32, C.POINTER(vp)]
     L.sepb_ctx_create.restype = i32
+    L.sepb_ctx_create_priority.argtypes = [i32, C.POINTER(vp)]
+    L.sepb_ctx_create_priority.restype = i32
     L.sepb_ctx_destroy.argtypes = [vp]
     L.sepb_ctx_destroy.restype = None
     L.sepb_last_error.argtypes = [vp]
@@ -194,14 +196,15 @@ OPT_MATCH_TILE = 3
 
 
 class Context:
-    def __init__(self, device: int = 0, _borrowed=None):
-        """_borrowed: handle of a context owned by a sepb_group (close() then only closes the children)."""
+    def __init__(self, device: int = 0, _borrowed=None, high_priority: bool = False):
+        """_borrowed: handle of a context owned by a sepb_group (close() then only closes the children).
+        high_priority: streams at the device's highest priority (short searches that must overtake a long batch)."""
         self._owned = _borrowed is None
         if _borrowed is not None:
             self._h = C.c_void_p(_borrowed)
         else:
             self._h = C.c_void_p()
-            rc = lib().sepb_ctx_create(device, C.byref(self._h))
+            rc = (lib().sepb_ctx_create_priority if high_priority else lib().sepb_ctx_create)(device, C.byref(self._h))
             if rc != 0:
                 raise SepbError(f"sepb_ctx_create(device={device}) failed with code {rc} (CUDA device required)")
         # stores / databases created on this context: they hold a raw pointer to it, so close() destroys them first

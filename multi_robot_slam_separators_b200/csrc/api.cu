@@ -17,7 +17,14 @@ int sepb_launch_match(sepb_ctx* ctx, FramesView from, FramesView to, const int32
 
 extern "C" {
 
-int sepb_ctx_create(int device, sepb_ctx** out) {
+static int ctx_create_impl(int device, bool high_priority, sepb_ctx** out);
+
+int sepb_ctx_create(int device, sepb_ctx** out) { return ctx_create_impl(device, false, out); }
+int sepb_ctx_create_priority(int device, sepb_ctx** out) { return ctx_create_impl(device, true, out); }
+
+}  // extern "C"
+
+static int ctx_create_impl(int device, bool high_priority, sepb_ctx** out) {
   if (!out) return SEPB_E_INVALID;
   *out = nullptr;
   int n = 0;
@@ -34,8 +41,10 @@ int sepb_ctx_create(int device, sepb_ctx** out) {
   if (!c) return (int)cudaErrorMemoryAllocation;
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
-  e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
-  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  int prio_lo = 0, prio_hi = 0;   // numerically lower = more urgent
+  if (high_priority) cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+  e = cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, high_priority ? prio_hi : 0);
+  if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->copy_stream, cudaStreamNonBlocking, high_priority ? prio_hi : 0);
   if (e != cudaSuccess) {
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -44,6 +53,8 @@ int sepb_ctx_create(int device, sepb_ctx** out) {
   *out = c;
   return SEPB_OK;
 }
+
+extern "C" {
 
 void sepb_ctx_destroy(sepb_ctx* ctx) {
   if (!ctx) return;

@@ -35,7 +35,8 @@ class SeparatorEngine:
     def __init__(self, cam: Camera, max_feat: int, dim: int, local_capacity: int, peer_capacity: int, device: int = 0,
                  iterations: int = 300, min_inliers: int = 5, reproj_error: float = 2.0, nndr: float = 0.8,
                  db_base: int = 0, ctx: capi.Context | None = None, image_size=(1241, 376), guess_win_size: float = 20.0,
-                 pnp_flags: int = 0, refine_iterations: int = 0, minimal_model: bool = False):
+                 pnp_flags: int = 0, refine_iterations: int = 0, minimal_model: bool = False,
+                 search_ctx: capi.Context | None = None):
         """ctx: share another engine's context (one stream, one copy stream): two engines then act as the two
         buffers of a pipeline -- the next round's keyframes upload while the current round is verified."""
         self.device = device
@@ -46,7 +47,10 @@ class SeparatorEngine:
         self.max_feat, self.dim = max_feat, dim
         self.local = capi.Frames(self.ctx, local_capacity, max_feat)
         self.peer = capi.Frames(self.ctx, peer_capacity, max_feat)
-        self.db = capi.NetvladDB(self.ctx, dim, peer_capacity, base=db_base)
+        # search_ctx: the NetVLAD database lives on another context of the same device (its own, typically high-priority,
+        # stream), so the candidate search of the next round runs while this context verifies the current one
+        self.search_ctx = search_ctx if search_ctx is not None else self.ctx
+        self.db = capi.NetvladDB(self.search_ctx, dim, peer_capacity, base=db_base)
         self.db_base = db_base
         self.pnp = capi.pnp_params(cam.fx, cam.fy, cam.cx, cam.cy, iterations=iterations, min_inliers=min_inliers,
                                    reproj_error=reproj_error, flags=pnp_flags, refine_iterations=refine_iterations,
@@ -91,9 +95,11 @@ class SeparatorEngine:
         idx = self._tensor("nn_idx", (Q, k), torch.int32)
         dist = self._tensor("nn_dist", (Q, k), torch.float64)
         rm = C.c_void_p(row_mask.data_ptr()) if row_mask is not None else None
-        self.ctx.check(capi.lib().sepb_netvlad_topk_dev(self.ctx._h, self.db._h, C.c_void_p(d_queries.data_ptr()), Q, k,
+        self.search_ctx.check(capi.lib().sepb_netvlad_topk_dev(self.search_ctx._h, self.db._h, C.c_void_p(d_queries.data_ptr()), Q, k,
                                                         mode, rm, None, None, C.c_void_p(idx.data_ptr()),
                                                         C.c_void_p(dist.data_ptr())))
+        if self.search_ctx is not self.ctx:
+            self.search_ctx.sync()      # the verification stream reads idx next
         return idx, dist
 
     def pairs_from_candidates(self, idx: torch.Tensor, base: int | None = None):
