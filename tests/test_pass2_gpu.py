@@ -208,3 +208,44 @@ def test_lazy_keypoints_identical_to_full_upload():
         for f in (fa, fb, la, lb):
             f.close()
         ctx.close()
+
+
+def test_lazy_keypoints_partial_binding_and_popc_matcher():
+    """A binding that covers only the upper slots of a store (the lower ones were uploaded whole), the POPC matcher (which
+    leaves the pulls to the fetch kernels instead of doing them in its tail), and a store used as both From and To."""
+    import torch
+    ctx = capi.Context(0)
+    A, B = synth.make_robots(2, 32, n_feat=1000, dim=128, seed=1311)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    rng = np.random.default_rng(4)
+    same = [(a, b) for a in range(32) for b in range(32) if A.place[a] == B.place[b]]
+    pairs = same + [(int(rng.integers(32)), int(rng.integers(32))) for _ in range(40)]
+    prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY)
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    la, lb = capi.Frames(ctx, 32, 1000), capi.Frames(ctx, 32, 1000)
+    h = 12                                            # slots [0, h) uploaded whole, [h, 32) host-bound
+    hi = {k: pin(getattr(A, k)[h:]) for k in ("desc", "kp2d", "kp3d", "count", "octave")}
+    hb = {k: pin(getattr(B, k)) for k in ("desc", "kp2d", "kp3d", "count", "octave")}
+    try:
+        for kernel in ("tensor", "popc"):
+            ctx.set_match_kernel(kernel)
+            want = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+            la.upload(0, A.desc[:h], A.kp2d[:h], A.kp3d[:h], A.count[:h], A.octave[:h])
+            la.upload(h, hi["desc"], hi["kp2d"], hi["kp3d"], hi["count"], hi["octave"], lazy=True)
+            lb.upload(0, hb["desc"], hb["kp2d"], hb["kp3d"], hb["count"], hb["octave"], lazy=True)
+            got = capi.verify_pairs(ctx, la, lb, pairs, prm)
+            assert_same(got, want, kernel)
+            assert la.fetched_bytes > 0 and lb.fetched_bytes > 0
+            # one store on both sides: a robot's own keyframes against each other
+            self_pairs = [(i, (i + 1) % 32) for i in range(32)] + [(i, i) for i in range(0, 32, 5)]
+            want_s = capi.verify_pairs(ctx, fb, fb, self_pairs, prm)
+            lb.upload(0, hb["desc"], hb["kp2d"], hb["kp3d"], hb["count"], hb["octave"], lazy=True)
+            got_s = capi.verify_pairs(ctx, lb, lb, self_pairs, prm)
+            assert_same(got_s, want_s, kernel + "/self")
+            assert int((want_s["status"] == 1).sum()) >= 6
+    finally:
+        ctx.set_match_kernel("auto")
+        ctx.sync()
+        for f in (fa, fb, la, lb):
+            f.close()
+        ctx.close()
