@@ -181,6 +181,10 @@ __device__ __noinline__ void lm_accumulate(const Corr& cr, const uint32_t* mask,
   }
 }
 
+#ifndef SEPB_LM_WARP_SVD
+#define SEPB_LM_WARP_SVD 1   // 0 (developer A/B): every lane runs the serial 6 x 6 SVD on its own copy
+#endif
+#if !SEPB_LM_WARP_SVD
 // CvLevMarq::step(): (JtJ with diag *= 1 + lambda) x = JtErr by SVD; param = prev - x
 __device__ __noinline__ void lm_step(cvm::Heap h, const double* JtJ, const double* JtE, int lambda_lg10, const double* prev,
                         double* param) {
@@ -200,8 +204,6 @@ __device__ __noinline__ void lm_step(cvm::Heap h, const double* JtJ, const doubl
   for (int i = 0; i < 6; ++i) param[i] = prev[i] - x[i];
 }
 
-#ifndef SEPB_LM_WARP_SVD
-#define SEPB_LM_WARP_SVD 1   // 0 (developer A/B): every lane runs the serial 6 x 6 SVD on its own copy
 #endif
 // CvLevMarq::step() for the whole warp: every lane holds the same normal equations and needs the new parameters.
 // h0 = lane 0's scratch slice: ONE copy of the 6 x 6 problem, its Jacobi sweeps spread over lanes (jacobi_svd6_warp).
@@ -240,15 +242,7 @@ __device__ __forceinline__ void lm_step_warp(cvm::Heap h, cvm::Heap h0, const do
 
 // solvePnP(points under `mask`, SOLVEPNP_ITERATIVE, useExtrinsicGuess) == CvLevMarq started at `param`; whole warp,
 // every lane ends with the same refined [rvec | tvec] in `param`
-#ifndef SEPB_K3_LM_INLINE
-#define SEPB_K3_LM_INLINE 0   // developer A/B
-#endif
-#if SEPB_K3_LM_INLINE
-__device__ __forceinline__
-#else
-__device__ __noinline__
-#endif
-void lm_refit(const Corr& cr, const uint32_t* mask, int M, const cvm::Intrinsics& K, cvm::Heap heap,
+__device__ __noinline__ void lm_refit(const Corr& cr, const uint32_t* mask, int M, const cvm::Intrinsics& K, cvm::Heap heap,
                                       cvm::Heap h0, double* param) {
   double prev[6], JtJ[21], JtE[6];
   for (int i = 0; i < 6; ++i) prev[i] = param[i];
@@ -649,10 +643,7 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
   if (out_mask)
     for (int w = lane; w < a.mask_words; w += 32) out_mask[w] = 0;
 
-#ifndef SEPB_K3_NO_FOUR
-#define SEPB_K3_NO_FOUR 0   // developer A/B
-#endif
-  if (!SEPB_K3_NO_FOUR && M == 4) {  // count == 4: cv::solvePnPRansac turns to ONE P3P solve over the four, whatever the flags; all inliers
+  if (M == 4) {  // count == 4: cv::solvePnPRansac turns to ONE P3P solve over the four, whatever the flags; all inliers
     float o[12], im[8];
     for (int i = 0; i < 4; ++i) cr.load_global(i, o + 3 * i, im + 2 * i);
     double R[9], p6[6];
@@ -841,10 +832,7 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
 
   double param[6];
   int final_good = best_good;
-#ifndef SEPB_K3_NO_MINIMAL
-#define SEPB_K3_NO_MINIMAL 0   // developer A/B
-#endif
-  if (!SEPB_K3_NO_MINIMAL && prm.minimal_model) {
+  if (prm.minimal_model) {
     // OpenCV 3.2 (the reference image's version): solvePnPRansac hands back the winning minimal-set model itself
     double Rh[9], th[3], rv[3];
     solve_chunk<MP>(a, in, ws, best_h, best_h + 1, Rh, th, rv);   // every lane redoes hypothesis best_h
@@ -876,10 +864,7 @@ __device__ __forceinline__ void run_pair(const PnpArgs& a, const PnpQueue& q, in
     // ---- refit: solvePnP(inliers, ITERATIVE, useExtrinsicGuess) == CvLevMarq from the caller's guess
     for (int i = 0; i < 6; ++i) param[i] = in.g[i];
     lm_refit(cr, best, M, prm.K, heap, cvm::Heap{ws.heap_base}, param);
-#ifndef SEPB_K3_NO_REFINE
-#define SEPB_K3_NO_REFINE 0   // developer A/B
-#endif
-    if (!SEPB_K3_NO_REFINE && prm.refine_iterations > 0 && best_good >= prm.min_inliers) {
+    if (prm.refine_iterations > 0 && best_good >= prm.min_inliers) {
       const uint32_t* fin = best;
       final_good = refine_model(cr, M, prm, heap, cvm::Heap{ws.heap_base}, s_mask + cur * kMaskWords,
                                 s_mask + (cur ^ 1) * kMaskWords, best_good, param, &fin);
