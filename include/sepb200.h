@@ -75,6 +75,13 @@ SEPB_API int64_t sepb_ctx_launch_count(const sepb_ctx* ctx);
 /* accumulator tile width of the tensor matcher: 0 (default) = 256 columns whenever the To frames fit its shared-memory
  * budget (up to ~1400 features), else 128; 128 forces the narrow geometry.  Identical results. */
 #define SEPB_OPT_MATCH_TILE 3
+/* how the tensor matcher walks a batch (identical results):
+ *   SEPB_MATCH_SCHED_PERSISTENT  (default) one CTA per SM runs through its share of the pairs; pair p's tail (ratio test,
+ *                                uniqueness, list compaction) overlaps pair p + 1's first tiles
+ *   SEPB_MATCH_SCHED_PER_PAIR    one CTA per pair */
+#define SEPB_OPT_MATCH_SCHEDULER 4
+#define SEPB_MATCH_SCHED_PERSISTENT 0
+#define SEPB_MATCH_SCHED_PER_PAIR 1
 SEPB_API int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value);
 SEPB_API int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value);
 

@@ -193,6 +193,7 @@ def _ptr(a):
 OPT_MATCH_KERNEL = 1
 OPT_PNP_SCHEDULER = 2
 OPT_MATCH_TILE = 3
+OPT_MATCH_SCHEDULER = 4
 
 
 class Context:
@@ -244,6 +245,11 @@ class Context:
     def set_match_tile(self, width: int):
         """Accumulator tile of the tensor matcher: 0 = widest that fits (256 columns up to ~1400 features), 128 = narrow."""
         self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_TILE, int(width)))
+
+    def set_match_scheduler(self, which: str):
+        """Tensor matcher: 'persistent' (default: one CTA per SM runs through its pairs, tails overlap the next pair's
+        first tiles) | 'per_pair' (one CTA per pair); identical results."""
+        self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_SCHEDULER, {"persistent": 0, "per_pair": 1}[which]))
 
     def set_pnp_scheduler(self, which: str):
         """'persistent' (default: persistent CTAs, device work list, idle warps compute chunks of running pairs) |

@@ -98,6 +98,11 @@ int sepb_ctx_set_option(sepb_ctx* ctx, int option, int value) {
     ctx->opt_match_tile = value == 256 ? 0 : value;
     return SEPB_OK;
   }
+  if (option == SEPB_OPT_MATCH_SCHEDULER) {
+    SEPB_REQUIRE(ctx, value == SEPB_MATCH_SCHED_PERSISTENT || value == SEPB_MATCH_SCHED_PER_PAIR, SEPB_E_INVALID);
+    ctx->opt_match_sched = value;
+    return SEPB_OK;
+  }
   return sepb_fail(ctx, SEPB_E_INVALID, "unknown option", __FILE__, __LINE__);
 }
 
@@ -113,6 +118,10 @@ int sepb_ctx_get_option(const sepb_ctx* ctx, int option, int* value) {
   }
   if (option == SEPB_OPT_MATCH_TILE) {
     *value = ctx->opt_match_tile;
+    return SEPB_OK;
+  }
+  if (option == SEPB_OPT_MATCH_SCHEDULER) {
+    *value = ctx->opt_match_sched;
     return SEPB_OK;
   }
   return SEPB_E_INVALID;

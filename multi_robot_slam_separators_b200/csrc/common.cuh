@@ -34,9 +34,11 @@ struct sepb_ctx {
   size_t k3_order_cap = 0;
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
   size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_hamming_mma_smem_wide = 0, cfg_guess_smem = 0;
+  size_t cfg_hamming_mma_psmem = 0, cfg_hamming_mma_psmem_wide = 0;
   int opt_match_kernel = SEPB_MATCH_AUTO;
   int opt_match_tile = 0;       // 0: widest K2T accumulator tile that fits, 128: force the narrow geometry
   int opt_pnp_sched = SEPB_PNP_SCHED_PERSISTENT;
+  int opt_match_sched = SEPB_MATCH_SCHED_PERSISTENT;
   int opt_nn_mode = -1;  // reserved
   bool cfg_pnp = false, cfg_exact = false, cfg_gemm = false;
 };

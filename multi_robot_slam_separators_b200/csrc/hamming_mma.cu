@@ -511,6 +511,422 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
   K2T_STAMP(tid == 0, 3);
 }
 
+
+// ---- persistent form ---------------------------------------------------------------------------------------------
+// One CTA per SM walks the pairs blockIdx.x, blockIdx.x + gridDim.x, ...; the three roles run through the SAME pair
+// sequence on their own, coupled only by the operand / accumulator rings (whose phases simply keep counting across
+// pairs).  What the one-CTA-per-pair kernel pays per pair in the open -- setup (TMEM allocation, barrier and index-block
+// initialisation), the expansion of the first To tile and From stage before the first MMA, and the tail after the last
+// one (15 % of a 1000 x 1000 pair) -- overlaps here: while the eight epilogue warps run pair p's tail (ratio test,
+// uniqueness, compaction: on 16-bit scratch of its own, the operand tiles belong to the next pair by then), the
+// producers have expanded pair p + 1's first tiles and the MMA warp fills both TMEM stages with them.
+__device__ __forceinline__ void bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+constexpr int kEpiThreads = kEpiWarps * 32;   // the tail's 256 threads (named barrier 1)
+
+struct PairGeom {
+  int fi, ti, nf, nt;
+};
+__device__ __forceinline__ PairGeom pair_geom(const FramesView& from, const FramesView& to, const int32_t* pairs, int pair) {
+  PairGeom g;
+  g.fi = pairs[2 * pair];
+  g.ti = pairs[2 * pair + 1];
+  const bool valid = g.fi >= 0 && g.fi < from.size && g.ti >= 0 && g.ti < to.size;
+  if (!valid) g.fi = g.ti = 0;
+  g.nf = valid ? min(from.count[g.fi], from.max_feat) : 0;
+  g.nt = valid ? min(to.count[g.ti], to.max_feat) : 0;
+  return g;
+}
+__device__ __forceinline__ void pull_row_n(void* dst, const void* src, int bytes, int tid, int nthreads) {
+  if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
+    const int n16 = bytes >> 4;
+    const int4* s = reinterpret_cast<const int4*>(src);
+    int4* d = reinterpret_cast<int4*>(dst);
+    for (int i = tid; i < n16; i += nthreads) d[i] = __ldcs(s + i);
+    for (int i = (n16 << 4) + 4 * tid; i < bytes; i += 4 * nthreads)
+      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
+  } else {
+    for (int i = 4 * tid; i < bytes; i += 4 * nthreads)
+      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
+  }
+}
+
+template <int TN>
+__global__ void __launch_bounds__(kThreadsT, 1)
+hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs, float nndr, int strict,
+                           int32_t* __restrict__ knn_idx, int32_t* __restrict__ knn_dist, int32_t* __restrict__ n_matches,
+                           uint16_t* __restrict__ match_from, uint16_t* __restrict__ match_to,
+                           int32_t* __restrict__ n_unique_to, const LazyPull lp) {
+  using G = Geo<TN>;
+  constexpr int kGroupsPerTile = G::kGroupsPerTile, kBStages = G::kBStages, CH = G::CH, kTStages = G::kTStages,
+                kTShift = G::kTShift, kBBytes = G::kBBytes, kBxBytes = G::kBxBytes;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (umma::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sB = smem;                                  // [2 K-blocks][CH][128]
+  uint8_t* sA = sB + kBBytes;                          // [2 buffers][2 K-blocks][TM][128]
+  uint8_t* sBx = sA + 2 * kABytes;                     // [CH/8][2][8][16]
+  uint8_t* sAx = sBx + kBxBytes;                       // [TM/8][2][8][16]
+  uint32_t* s_top = reinterpret_cast<uint32_t*>(sAx + kAxBytes);  // [2][to.max_feat][2] keys
+  // the tail's own scratch (16-bit: To rows and From rows are < 65536)
+  int16_t* s_asg = reinterpret_cast<int16_t*>(s_top + 4 * (size_t)to.max_feat);   // [to.max_feat] From row or -1
+  uint16_t* s_cnt = reinterpret_cast<uint16_t*>(s_asg + ((to.max_feat + 1) & ~1));  // [from.max_feat] uses of a From row
+  uint16_t* s_own = s_cnt + ((from.max_feat + 1) & ~1);                            // [from.max_feat] its To row
+  __shared__ uint64_t bar_a_full[2], bar_a_empty[2], bar_b_full[kBStages], bar_b_empty[kBStages], bar_t_full[kTStages],
+      bar_t_empty[kTStages];
+  __shared__ uint32_t tmem_slot;
+  __shared__ int s_scan[kEpiWarps];
+  __shared__ int s_dropped, s_any;
+  __shared__ int s_claim[2];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // ---- setup, once per CTA ---------------------------------------------------------------------------
+  for (int i = tid; i < 4 * to.max_feat; i += kThreadsT) s_top[i] = kNoneKey;
+  for (int i = tid; i < (kBxBytes + kAxBytes) / 16; i += kThreadsT)
+    reinterpret_cast<uint4*>(sBx)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  for (int r = tid; r < CH; r += kThreadsT) {
+    const int col = r & (kHalf - 1);
+    uint8_t* p = sBx + (r >> 3) * 128 + (r & 7) * 16;
+    p[0] = (uint8_t)(col >> 6);
+    p[1] = (uint8_t)(col & 63);
+  }
+  for (int r = tid; r < TM; r += kThreadsT)
+    *reinterpret_cast<uint32_t*>(sAx + (r >> 3) * 256 + (r & 7) * 16) = 0x8080FFC0u;  // (-64, -1, -128, -128)
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      umma::mbar_init(&bar_a_full[s], kProdThreads);
+      umma::mbar_init(&bar_a_empty[s], 1);
+    }
+    for (int s = 0; s < kBStages; ++s) {
+      umma::mbar_init(&bar_b_full[s], kProdThreads);
+      umma::mbar_init(&bar_b_empty[s], 1);
+    }
+    for (int s = 0; s < kTStages; ++s) {
+      umma::mbar_init(&bar_t_full[s], 1);
+      umma::mbar_init(&bar_t_empty[s], 4 * kGroupsPerTile);
+    }
+    umma::fence_mbar_init();
+    s_dropped = 0;
+    s_any = 0;
+  }
+  if (warp == kMmaWarp) umma::tmem_alloc(&tmem_slot, 512);
+  umma::fence_proxy_async();
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp >= kProdWarp0) {
+    // ---- producers: run ahead through the pair sequence, held back only by the operand rings --------------------
+    const int p = tid - kProdWarp0 * 32;
+    const uint32_t sB_a = umma::smem_u32(sB), sA_a = umma::smem_u32(sA);
+    int it = 0;                 // To tiles expanded so far (all pairs): buffer it & 1, use count it >> 1
+    int ub[kBStages];           // fills of From stage j so far
+#pragma unroll
+    for (int j = 0; j < kBStages; ++j) ub[j] = 0;
+    for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+      const PairGeom pg = pair_geom(from, to, pairs, pair);
+      const int nf = pg.nf, nt = pg.nt;
+      if (nt == 0 || nf == 0) continue;
+      const uint4* g_train = reinterpret_cast<const uint4*>(from.desc + (size_t)pg.fi * from.max_feat * 32);
+      const uint4* g_query = reinterpret_cast<const uint4*>(to.desc + (size_t)pg.ti * to.max_feat * 32);
+      const int n_chunks = (nf + CH - 1) / CH, n_mt = (nt + TM - 1) / TM;
+      for (int c = 0; c < n_chunks; ++c) {
+        const int rows = min(CH, nf - c * CH);
+        const int rows_pad = (rows + 31) & ~31;
+        for (int m = 0; m < n_mt; ++m, ++it) {
+          const int s = it & 1;
+          const int row = m * TM + p;
+          uint4 qa, qb;
+          if (row < nt) {
+            qa = __ldg(g_query + 2 * (size_t)row);
+            qb = __ldg(g_query + 2 * (size_t)row + 1);
+          }
+          umma::mbar_wait(&bar_a_empty[s], (uint32_t)(((it >> 1) & 1) ^ 1));
+          if (row < nt) expand_row(sA_a + (uint32_t)(s * kABytes), TM, p, qa, qb);
+          umma::fence_proxy_async();
+          umma::mbar_arrive(&bar_a_full[s]);
+          if (m == 0) {
+#pragma unroll
+            for (int j = 0; j < kBStages; ++j) {
+              if (j * TN >= rows) break;
+              uint4 ta[kGroupsPerTile], tb[kGroupsPerTile];
+#pragma unroll
+              for (int h = 0; h < kGroupsPerTile; ++h) {
+                const int r = j * TN + h * kHalf + p;
+                if (r < rows) {
+                  ta[h] = __ldg(g_train + 2 * (size_t)(c * CH + r));
+                  tb[h] = __ldg(g_train + 2 * (size_t)(c * CH + r) + 1);
+                }
+              }
+              umma::mbar_wait(&bar_b_empty[j], (uint32_t)((ub[j] & 1) ^ 1));
+#pragma unroll
+              for (int h = 0; h < kGroupsPerTile; ++h) {
+                const int r = j * TN + h * kHalf + p;
+                uint8_t* px = sBx + (r >> 3) * 128 + (r & 7) * 16;
+                if (r < rows) {
+                  expand_row(sB_a, CH, r, ta[h], tb[h]);
+                  px[2] = 0;      // a row of an earlier pair may have left the padding code here
+                  px[3] = 0;
+                } else if (r < rows_pad) {
+                  zero_row(sB_a, CH, r);
+                  px[2] = 127;
+                  px[3] = 127;
+                }
+              }
+              umma::fence_proxy_async();
+              umma::mbar_arrive(&bar_b_full[j]);
+              ++ub[j];
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == kMmaWarp) {
+    // ---- MMA issuer --------------------------------------------------------------------------------------------
+    const uint32_t a_lo = ((umma::smem_u32(sA) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t b_lo = ((umma::smem_u32(sB) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t sw_hi = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
+    const uint32_t il_hi = (uint32_t)(256 >> 4) | (1u << 14);
+    const uint32_t ilb_hi = (uint32_t)(128 >> 4) | (1u << 14);
+    const uint32_t ax_lo = ((umma::smem_u32(sAx) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
+    const uint32_t bx_lo = ((umma::smem_u32(sBx) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16);
+    auto desc = [](uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; };
+    int it = 0;
+    uint32_t g = 0;
+    int ub[kBStages];
+#pragma unroll
+    for (int j = 0; j < kBStages; ++j) ub[j] = 0;
+    for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+      const PairGeom pg = pair_geom(from, to, pairs, pair);
+      const int nf = pg.nf, nt = pg.nt;
+      if (nt == 0 || nf == 0) continue;
+      const int n_chunks = (nf + CH - 1) / CH, n_mt = (nt + TM - 1) / TM;
+      for (int c = 0; c < n_chunks; ++c) {
+        const int rows = min(CH, nf - c * CH);
+        for (int m = 0; m < n_mt; ++m, ++it) {
+          const int s = it & 1;
+          umma::mbar_wait(&bar_a_full[s], (uint32_t)((it >> 1) & 1));
+          const uint32_t a_s = a_lo + (uint32_t)((s * kABytes) >> 4);
+#pragma unroll
+          for (int j = 0; j < kBStages; ++j) {
+            const int ncols = min(TN, rows - j * TN);
+            if (ncols <= 0) break;
+            if (m == 0) umma::mbar_wait(&bar_b_full[j], (uint32_t)(ub[j] & 1));
+            const uint32_t st = g & (kTStages - 1);
+            umma::mbar_wait(&bar_t_empty[st], ((g >> kTShift) & 1) ^ 1);
+            umma::tc_fence_after();
+            if (umma::elect_one()) {
+              const uint32_t idesc = umma::instr_desc(2, 1, 1, TM, (uint32_t)((ncols + 31) & ~31));
+              const uint32_t d = tmem + st * TN;
+#pragma unroll
+              for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  umma::mma_i8(d, desc(a_s + (uint32_t)((kb * TM * 128 + k * 32) >> 4), sw_hi),
+                               desc(b_lo + (uint32_t)((kb * CH * 128 + j * TN * 128 + k * 32) >> 4), sw_hi), idesc,
+                               (kb | k) != 0);
+              umma::mma_i8(d, desc(ax_lo, il_hi), desc(bx_lo + (uint32_t)((j * TN * 16) >> 4), ilb_hi), idesc, true);
+              umma::mma_commit(&bar_t_full[st]);
+              if (m == n_mt - 1) umma::mma_commit(&bar_b_empty[j]);
+            }
+            __syncwarp();
+            ++g;
+          }
+          if (umma::elect_one()) umma::mma_commit(&bar_a_empty[s]);
+          __syncwarp();
+        }
+#pragma unroll
+        for (int j = 0; j < kBStages; ++j)
+          if (j * TN < rows) ++ub[j];
+      }
+    }
+  } else {
+    // ---- epilogue warps: drain the accumulator tiles of a pair, then run its tail -------------------------------
+    const int grp = warp >> 2, lq = warp & 3;
+    uint32_t g = 0;
+    for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+      const PairGeom pg = pair_geom(from, to, pairs, pair);
+      const int nf = pg.nf, nt = pg.nt, fi = pg.fi, ti = pg.ti;
+      if (nt == 0 || nf == 0) {   // nothing to multiply (the other roles skip the pair as well)
+        for (int qi = tid; qi < nt; qi += kEpiThreads) {
+          const size_t o = ((size_t)pair * to.max_feat + qi) * 2;
+          if (knn_idx) knn_idx[o] = knn_idx[o + 1] = -1;
+          if (knn_dist) knn_dist[o] = knn_dist[o + 1] = -1;
+        }
+        if (tid == 0) {
+          n_matches[pair] = 0;
+          if (n_unique_to) n_unique_to[pair] = nt;
+        }
+        continue;
+      }
+      const int n_chunks = (nf + CH - 1) / CH, n_mt = (nt + TM - 1) / TM;
+      for (int c = 0; c < n_chunks; ++c) {
+        const int rows = min(CH, nf - c * CH);
+        for (int m = 0; m < n_mt; ++m) {
+          for (int j = 0; j * TN < rows; ++j, ++g) {
+            if (kGroupsPerTile == 1 && (int)(g & 1) != grp) continue;
+            const int off = kGroupsPerTile == 1 ? 0 : grp * kHalf;
+            const int ncols = max(0, min(kHalf, rows - j * TN - off));
+            const int nch = (ncols + 31) >> 5;
+            const uint32_t st = g & (kTStages - 1);
+            const uint32_t taddr = tmem + ((uint32_t)(lq * 32) << 16) + st * TN + off;
+            umma::mbar_wait(&bar_t_full[st], (g >> kTShift) & 1);
+            umma::tc_fence_after();
+            uint32_t m1[2] = {kNone2, kNone2}, m2[2] = {kNone2, kNone2};
+            uint32_t r0[16], r1[16], r2[16], r3[16];
+            if (nch > 0) umma::tmem_ld32_pack16(taddr, r0);
+            if (nch > 1) umma::tmem_ld32_pack16(taddr + 32u, r1);
+            if (nch > 2) umma::tmem_ld32_pack16(taddr + 64u, r2);
+            if (nch > 3) umma::tmem_ld32_pack16(taddr + 96u, r3);
+            umma::tmem_ld_wait();
+            umma::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&bar_t_empty[st]);
+            if (nch > 0) scan32(r0, m1, m2);
+            if (nch > 1) scan32(r1, m1, m2);
+            if (nch > 2) scan32(r2, m1, m2);
+            if (nch > 3) scan32(r3, m1, m2);
+            merge2(m1[0], m2[0], m1[1], m2[1]);
+            int v1 = (int)(int16_t)(m1[0] & 0xFFFFu), v2 = (int)(int16_t)(m2[0] & 0xFFFFu);
+            {
+              const int w1 = (int)(int16_t)(m1[0] >> 16), w2 = (int)(int16_t)(m2[0] >> 16);
+              const int lo = min(v1, w1);
+              v1 = max(v1, w1);
+              v2 = max(lo, max(v2, w2));
+            }
+            const int row = m * TM + lq * 32 + lane;
+            if (row < nt) {
+              uint32_t* slot = s_top + ((size_t)grp * to.max_feat + row) * 2;
+              uint32_t k1 = slot[0], k2 = slot[1];
+              merge_min(k1, k2, acc_to_key(v1, c * CH + j * TN + off), acc_to_key(v2, c * CH + j * TN + off));
+              slot[0] = k1;
+              slot[1] = k2;
+            }
+          }
+        }
+      }
+      // ---- tail of this pair, on the 256 epilogue threads (the other warps are already in the next pair) -----------
+      bar_sync(1, kEpiThreads);
+      for (int i = tid; i < (nf + 1) / 2; i += kEpiThreads) reinterpret_cast<uint32_t*>(s_cnt)[i] = 0;
+      int any_assigned = 0;
+      for (int qi = tid; qi < nt; qi += kEpiThreads) {
+        uint32_t* t0 = s_top + (size_t)qi * 2;
+        uint32_t* t1 = s_top + ((size_t)to.max_feat + qi) * 2;
+        uint32_t k1 = t0[0], k2 = t0[1];
+        merge_min(k1, k2, t1[0], t1[1]);
+        t0[0] = t0[1] = t1[0] = t1[1] = kNoneKey;   // ready for the next pair
+        const int i1 = k1 == kNoneKey ? -1 : (int)(k1 & 0xFFFFu), d1 = k1 == kNoneKey ? -1 : (int)(k1 >> 16);
+        const int i2 = k2 == kNoneKey ? -1 : (int)(k2 & 0xFFFFu), d2 = k2 == kNoneKey ? -1 : (int)(k2 >> 16);
+        const size_t o = ((size_t)pair * to.max_feat + qi) * 2;
+        if (knn_idx) {
+          knn_idx[o] = i1;
+          knn_idx[o + 1] = i2;
+        }
+        if (knn_dist) {
+          knn_dist[o] = d1;
+          knn_dist[o + 1] = d2;
+        }
+        const int as = mtail::nndr_assign(i1, d1, i2, d2, nndr, strict);
+        s_asg[qi] = (int16_t)as;
+        any_assigned |= as >= 0;
+      }
+      if (__any_sync(0xFFFFFFFFu, any_assigned) && lane == 0) atomicOr(&s_any, 1);
+      bar_sync(1, kEpiThreads);
+      if (!s_any) {   // no To row passed the ratio test (most non-matching pairs): empty list
+        if (tid == 0) {
+          n_matches[pair] = 0;
+          if (n_unique_to) n_unique_to[pair] = nt;
+        }
+        continue;
+      }
+      // To rows claiming the same From row are dropped (:882-894); 16-bit counters, two per word
+      for (int qi = tid; qi < nt; qi += kEpiThreads) {
+        const int a = s_asg[qi];
+        if (a >= 0) {
+          atomicAdd(reinterpret_cast<unsigned int*>(s_cnt) + (a >> 1), 1u << (16 * (a & 1)));
+          s_own[a] = (uint16_t)qi;   // only read back where the count is 1 (single writer)
+        }
+      }
+      bar_sync(1, kEpiThreads);
+      const float* p3 = from.kp3d_early(fi);
+      const int chunk = (nf + kEpiThreads - 1) / kEpiThreads;
+      const int lo = min(nf, tid * chunk), hi = min(nf, lo + chunk);
+      int local = 0, dropped = 0;
+      uint32_t keep_mask = 0;  // chunk <= 32
+      for (int i = lo; i < hi; ++i) {
+        const uint32_t cnt = s_cnt[i];
+        if (cnt >= 2) dropped += (int)cnt;
+        if (cnt == 1) {
+          const float x = p3[3 * i], y = p3[3 * i + 1], z = p3[3 * i + 2];
+          if (isfinite(x) && isfinite(y) && isfinite(z)) {
+            keep_mask |= 1u << (i - lo);
+            ++local;
+          }
+        }
+      }
+      if (dropped) atomicAdd(&s_dropped, dropped);
+      int incl = local;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane == 31) s_scan[warp] = incl;
+      bar_sync(1, kEpiThreads);
+      int base = 0, total = 0;
+#pragma unroll
+      for (int w = 0; w < kEpiWarps; ++w) {
+        const int v = s_scan[w];
+        if (w < warp) base += v;
+        total += v;
+      }
+      const size_t obase = (size_t)pair * from.max_feat;
+      int pos = base + incl - local;
+      for (int i = lo; i < hi; ++i) {
+        if (keep_mask & (1u << (i - lo))) {
+          if (match_from) match_from[obase + pos] = (uint16_t)i;
+          if (match_to) match_to[obase + pos] = s_own[i];
+          ++pos;
+        }
+      }
+      const bool pull = lp.min_matches > 0 && total >= lp.min_matches;
+      const unsigned rf = (unsigned)(fi - lp.from_first), rt = (unsigned)(ti - lp.to_first);
+      if (tid == 0) {
+        n_matches[pair] = total;
+        if (n_unique_to) n_unique_to[pair] = nt - s_dropped;
+        s_dropped = 0;
+        s_any = 0;
+        if (pull) {
+          s_claim[0] = lp.from_kp3d_host && rf < (unsigned)lp.from_n && sepb_claim_row(lp.from_have, fi, 2u);
+          s_claim[1] = lp.to_kp2d_host && rt < (unsigned)lp.to_n && sepb_claim_row(lp.to_have, ti, 1u);
+        }
+      }
+      bar_sync(1, kEpiThreads);   // also: s_scan / s_any / s_dropped are free again
+      if (pull) {
+        if (s_claim[0]) {
+          pull_row_n(lp.from_kp3d + (size_t)fi * from.max_feat * 3, lp.from_kp3d_host + (size_t)rf * from.max_feat * 3, nf * 12,
+                     tid, kEpiThreads);
+          if (tid == 0) atomicAdd(lp.from_fetched, (unsigned long long)nf * 12);
+        }
+        if (s_claim[1]) {
+          pull_row_n(lp.to_kp2d + (size_t)ti * to.max_feat * 2, lp.to_kp2d_host + (size_t)rt * to.max_feat * 2, nt * 8, tid,
+                     kEpiThreads);
+          if (tid == 0) atomicAdd(lp.to_fetched, (unsigned long long)nt * 8);
+        }
+        bar_sync(1, kEpiThreads);   // s_claim is read before the next pair's tail may rewrite it
+      }
+    }
+  }
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    umma::tc_fence_after();
+    umma::tmem_dealloc(tmem, 512);
+  }
+}
+
 }  // namespace
 
 #ifdef SEPB_K2T_TRACE
@@ -530,6 +946,16 @@ static bool geo_fits(const FramesView& from, const FramesView& to) {
 
 bool sepb_hamming_mma_supported(const FramesView& from, const FramesView& to) { return geo_fits<128>(from, to); }
 
+// the persistent form needs the tail's own scratch on top of the operand tiles
+template <int TN>
+static size_t persist_smem(const FramesView& from, const FramesView& to) {
+  return Geo<TN>::smem(to.max_feat) + 2 * (size_t)((to.max_feat + 1) & ~1) + 4 * (size_t)((from.max_feat + 1) & ~1) + 16;
+}
+template <int TN>
+static bool persist_fits(const FramesView& from, const FramesView& to) {
+  return geo_fits<TN>(from, to) && persist_smem<TN>(from, to) + 512 <= 232448;
+}
+
 int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
                             float nndr, int strict, int32_t* d_knn_idx, int32_t* d_knn_dist, int32_t* d_n_matches,
                             uint16_t* d_match_from, uint16_t* d_match_to, int32_t* d_n_unique_to, const LazyPull* lazy) {
@@ -539,6 +965,33 @@ int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const
     return sepb_fail(ctx, SEPB_E_SHAPE, "hamming_mma: frame too large for the tensor kernel", __FILE__, __LINE__);
   bool wide = geo_fits<256>(from, to);
   if (ctx->opt_match_tile == 128) wide = false;   // SEPB_OPT_MATCH_TILE: the narrow geometry on request (tests, A/B)
+  // SEPB_OPT_MATCH_SCHEDULER: persistent CTAs (default) whenever the tail's scratch fits beside the operand tiles
+  bool persist = ctx->opt_match_sched == SEPB_MATCH_SCHED_PERSISTENT &&
+                 (wide ? persist_fits<256>(from, to) : persist_fits<128>(from, to));
+#ifdef SEPB_K2T_TRACE
+  persist = false;   // the timeline build instruments the one-CTA-per-pair kernel
+#endif
+  if (persist) {
+    const size_t smem = wide ? persist_smem<256>(from, to) : persist_smem<128>(from, to);
+    size_t& cfg = wide ? ctx->cfg_hamming_mma_psmem_wide : ctx->cfg_hamming_mma_psmem;
+    if (smem > cfg) {
+      SEPB_CUDA(ctx, wide ? cudaFuncSetAttribute(hamming_mma_persist_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                          : cudaFuncSetAttribute(hamming_mma_persist_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      cfg = smem;
+    }
+    const int ctas = n_pairs < ctx->sm_count ? n_pairs : ctx->sm_count;
+    if (wide)
+      hamming_mma_persist_kernel<256><<<ctas, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
+                                                                               d_knn_dist, d_n_matches, d_match_from, d_match_to,
+                                                                               d_n_unique_to, lp);
+    else
+      hamming_mma_persist_kernel<128><<<ctas, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
+                                                                               d_knn_dist, d_n_matches, d_match_from, d_match_to,
+                                                                               d_n_unique_to, lp);
+    ctx->launches++;
+    SEPB_CUDA(ctx, cudaGetLastError());
+    return SEPB_OK;
+  }
   const size_t smem = wide ? Geo<256>::smem(to.max_feat) : Geo<128>::smem(to.max_feat);
   size_t& cfg = wide ? ctx->cfg_hamming_mma_smem_wide : ctx->cfg_hamming_mma_smem;
   if (smem > cfg) {

@@ -121,14 +121,18 @@ def test_tensor_kernel_equals_popc_kernel_full_size():
     every output (2-NN indices, distances, correspondence lists) over a few hundred 1000x1000 pairs."""
     A, B = synth.make_robots(2, 48, n_feat=1000, dim=128, seed=2002)
     rng = np.random.default_rng(11)
-    pairs = rng.integers(0, 48, (256, 2)).astype(np.int32)
+    A.count[5], A.count[9], B.count[7], B.count[11] = 0, 333, 0, 129      # ragged and empty frames inside the batch
+    pairs = rng.integers(0, 48, (700, 2)).astype(np.int32)             # > 4 pairs per CTA of the persistent kernel
     outs = []
     # the tensor kernel in both accumulator-tile geometries (the launch takes the 256-column one for these frames;
-    # SEPB_OPT_MATCH_TILE = 128 forces the geometry used for longer To frames)
-    for which, tn in (("popc", 0), ("tensor", 0), ("tensor", 128)):
+    # SEPB_OPT_MATCH_TILE = 128 forces the geometry used for longer To frames) and both schedulers (persistent CTAs
+    # walking their share of the pairs -- the default -- and one CTA per pair)
+    for which, tn, sched in (("popc", 0, "persistent"), ("tensor", 0, "persistent"), ("tensor", 128, "persistent"),
+                             ("tensor", 0, "per_pair"), ("tensor", 128, "per_pair")):
         c = capi.Context(0)
         c.set_match_kernel(which)
         c.set_match_tile(tn)
+        c.set_match_scheduler(sched)
         fa, fb = capi.frames_from_robot(c, A), capi.frames_from_robot(c, B)
         outs.append(capi.match_pairs(c, fa, fb, pairs, nndr=0.8))
         fa.close(); fb.close(); c.close()
