@@ -73,7 +73,7 @@ SEPB_API int64_t sepb_ctx_launch_count(const sepb_ctx* ctx);
 #define SEPB_PNP_SCHED_PERSISTENT 0
 #define SEPB_PNP_SCHED_PER_PAIR 1
 /* accumulator tile width of the tensor matcher: 0 (default) = 256 columns whenever the To frames fit its shared-memory
- * budget (up to ~1400 features), else 128; 128 forces the narrow geometry.  Identical results. */
+ * budget (To frames up to ~1400 features), else 128; 128 forces the narrow geometry.  Identical results. */
 #define SEPB_OPT_MATCH_TILE 3
 /* how the tensor matcher walks a batch (identical results):
  *   SEPB_MATCH_SCHED_PERSISTENT  (default) one CTA per SM runs through its share of the pairs; pair p's tail (ratio test,
