@@ -39,6 +39,14 @@ void* sh_geo_create(void* dev, double fx, double fy, double cx, double cy, int w
   return new GeometricTools(*static_cast<Device*>(dev), cam, min_inliers, max_feat);
 }
 void sh_geo_destroy(void* g) { delete static_cast<GeometricTools*>(g); }
+// Vis/PnPFlags, Vis/PnPRefineIterations, the OpenCV 3.2 return convention, the camera's localTransform (NULL keeps it)
+void sh_geo_configure(void* g, int pnp_flags, int refine_iterations, int opencv32, const double* local_R9, const double* local_t3) {
+  GeometricTools* gt = static_cast<GeometricTools*>(g);
+  if (local_R9 && local_t3) gt->setLocalTransform(local_R9, local_t3);
+  gt->setPnPFlags(pnp_flags);
+  gt->setPnPRefineIterations(refine_iterations);
+  gt->setOpenCV32Semantics(opencv32 != 0);
+}
 
 // returns res.success; pose7 = position xyz + orientation xyzw
 int sh_geo_estimate(void* g, const uint8_t* descF, int nF, const float* kp2F, const int32_t* octF, const float* kp3F,

@@ -26,6 +26,8 @@ def load():
     L.sh_geo_create.restype = vp
     L.sh_geo_create.argtypes = [vp, f64, f64, f64, f64, i32, i32, i32, i32]
     L.sh_geo_destroy.argtypes = [vp]
+    L.sh_geo_configure.argtypes = [vp, i32, i32, i32, vp, vp]
+    L.sh_geo_configure.restype = None
     L.sh_geo_estimate.argtypes = [vp, vp, i32, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp]
     L.sh_pr_create.restype = vp
     L.sh_pr_create.argtypes = [vp, i32, f64, i32, i32]
@@ -119,6 +121,40 @@ def test_estimate_transformation_matches_batch_path():
         assert w >= 0 and abs(x * x + y * y + z * z + w * w - 1) < 1e-6 and np.abs(Rq - T[:, :3]).max() < 1e-6
         assert np.array_equal(cov, ref["covariance"][k].reshape(6, 6))
     assert n_ok >= 5
+    L.sh_geo_destroy(geo); L.sh_device_destroy(dev)
+    fa.close(); fb.close(); ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("flags,refine,cv32", [(2, 0, 0), (0, 3, 0), (0, 0, 1)])
+def test_estimate_transformation_solver_options(flags, refine, cv32):
+    """The handler's Vis/PnPFlags / Vis/PnPRefineIterations / OpenCV-3.2 switches reach the kernels: same answers as the
+    batch C ABI with the same sepb_pnp_params, and different from the default where the option matters."""
+    from multi_robot_slam_separators_b200 import capi
+    L = load()
+    N = 24
+    A, B = synth.make_robots(2, N, n_feat=1000, dim=8, seed=322, overlap=0.5)
+    pairs = [(o, l) for l in range(N) for o in range(N) if A.place[o] == B.place[l]][:5]
+    ctx = capi.Context(0)
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    gp = capi.guess_params(synth.WIDTH, synth.HEIGHT)
+    prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY, flags=flags, refine_iterations=refine, minimal_model=bool(cv32))
+    ref = capi.estimate_transformations(ctx, fa, fb, np.array(pairs, np.int32), prm, gp, 0.8)
+    base = capi.estimate_transformations(ctx, fa, fb, np.array(pairs, np.int32),
+                                         capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY), gp, 0.8)
+    dev = L.sh_device_create(0)
+    geo = L.sh_geo_create(dev, synth.FX, synth.FY, synth.CX, synth.CY, synth.WIDTH, synth.HEIGHT, 5, 1000)
+    L.sh_geo_configure(geo, flags, refine, cv32, None, None)
+    n_ok = n_diff = 0
+    for k, (o, l) in enumerate(pairs):
+        ok, pose, cov, inl, mat = estimate(L, geo, A, o, B, l)
+        assert ok == int(ref["status"][k] == 1)
+        if ok:
+            n_ok += 1
+            T = ref["transform"][k].reshape(3, 4).astype(np.float64)
+            assert np.array_equal(pose[:3], T[:, 3]) and inl == ref["n_inliers"][k] and mat == ref["n_matches"][k]
+            n_diff += int(not np.array_equal(ref["transform"][k], base["transform"][k]))
+    assert n_ok >= 4 and n_diff >= 1
     L.sh_geo_destroy(geo); L.sh_device_destroy(dev)
     fa.close(); fb.close(); ctx.close()
 
