@@ -232,7 +232,8 @@ SEPB_API void sepb_pnp_set_guess(sepb_pnp_params* p, const double* guess3x4);
 #define SEPB_PNP_TOO_FEW 0     /* fewer than min_inliers (or than a minimal set of) correspondences: null transform, no RANSAC */
 #define SEPB_PNP_OK 1          /* transform valid (success=true in EstTransform.srv) */
 #define SEPB_PNP_NO_MODEL 2    /* RANSAC found no hypothesis with more inliers than a minimal set has points */
-#define SEPB_PNP_FEW_INLIERS 3 /* inliers < min_inliers */
+#define SEPB_PNP_FEW_INLIERS 3 /* inliers < min_inliers (after RANSAC, or after bundle adjustment dropped its outliers) */
+#define SEPB_PNP_BA_FAILED 4   /* bundle adjustment diverged (NaN / huge chi2): null transform, R/src/myRegistrationVis.cpp:1367-1370 */
 
 /* Outputs (device or host according to the entry point):
  *   status[P] i32, n_inliers[P] i32, pose[P][6] f64 (rvec, tvec of the To camera w.r.t. From base),
@@ -314,6 +315,47 @@ SEPB_API int sepb_estimate_transformations_dev(sepb_ctx* ctx, const sepb_frames*
                                                const int32_t* d_pairs, int n_pairs, const sepb_match_params* mprm,
                                                const sepb_pnp_params* pprm, const sepb_guess_params* gprm,
                                                const sepb_verify_out* d_out, int32_t* d_status_pass1);
+
+/* ---- 2-view bundle adjustment after PnP (Vis/BundleAdjustment = 1) ---------------------------------
+ * R/src/myRegistrationVis.cpp:1192-1370: when a pose was found, RTAB-Map's OptimizerG2O::optimizeBA refines it over
+ * two cameras (From fixed, To free) and the inliers' 3-D points (free, starting at the From frame's points), with the
+ * pixels of both frames as stereo (u, v, u - baseline * fx / depth) or mono edges under a Huber kernel and the PnP
+ * result as a camera-to-camera edge weighted by covariance^-1; 5 + `iterations` Levenberg-Marquardt iterations, edges
+ * whose chi2 exceeds the kernel's delta after each stage drop their inlier; the refined pose replaces the transform,
+ * fewer than min_inliers remaining inliers (SEPB_PNP_FEW_INLIERS) or a diverged optimisation (SEPB_PNP_BA_FAILED) null
+ * it.  g2o and RTAB-Map are not vendored by the reference: the algorithm is restated from their published sources
+ * (oracle/ba.py), parity against the reference's binaries is unpinned.  cvsba (type 2) is not built. */
+typedef struct sepb_ba_params {
+  int32_t type;                /* Vis/BundleAdjustment: 0 = off, 1 = g2o-style (the only one built) */
+  int32_t iterations;          /* Optimizer/Iterations of the second stage, 20 */
+  double pixel_variance;       /* g2o/PixelVariance, 1.0 */
+  double robust_kernel_delta;  /* g2o/RobustKernelDelta, 8.0; <= 0: no kernel, one stage of `iterations`, no outliers */
+  double baseline;             /* what VertexCam::setKcam receives: stereo baseline [m] * fy / fx (:1247-1252, Tx = -baseline * fy);
+                                * <= 0: every edge is a mono edge */
+  int32_t variance_ignored;    /* Optimizer/VarianceIgnored: 1 = identity information on the camera-to-camera edge */
+  int32_t reserved_;
+} sepb_ba_params;
+SEPB_API void sepb_ba_params_init(sepb_ba_params* b, double baseline);
+/* consulted by sepb_verify_pairs* / sepb_estimate_transformations*: with type == 1 every PnP of those calls (both
+ * passes of the two-call driver) is followed by its covariance and the bundle adjustment, as in the reference where
+ * the block sits inside computeTransformationImpl.  The _dev forms then need inlier_mask and covariance in d_out.
+ * NULL or type == 0 switches it off (the default). */
+SEPB_API int sepb_ctx_set_bundle_adjustment(sepb_ctx* ctx, const sepb_ba_params* b);
+/* the block alone, device buffers, asynchronous on the ctx stream.  In: pairs, match lists, covariance [P][36] (may be
+ * NULL: identity), and the PnP results it updates IN PLACE for the pairs with status SEPB_PNP_OK: status, n_inliers,
+ * pose, transform, inlier_mask.  d_stats (optional, [P][4] f64): iterations run, final robust chi2, inliers dropped,
+ * final lambda.  Key points of both frames must be resident (host-bound stores: bind + verify first). */
+SEPB_API int sepb_bundle_adjust_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                                    int n_pairs, const int32_t* d_n_matches, const uint16_t* d_match_from,
+                                    const uint16_t* d_match_to, const double* d_covariance, const sepb_pnp_params* pprm,
+                                    const sepb_ba_params* bprm, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
+                                    float* d_transform, uint32_t* d_inlier_mask, int mask_words, double* d_stats);
+/* same on host buffers (synchronous) */
+SEPB_API int sepb_bundle_adjust_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                                      int n_pairs, const int32_t* n_matches, const uint16_t* match_from,
+                                      const uint16_t* match_to, const double* covariance, const sepb_pnp_params* pprm,
+                                      const sepb_ba_params* bprm, int32_t* status, int32_t* n_inliers, double* pose,
+                                      float* transform, uint32_t* inlier_mask, int mask_words, double* stats);
 
 /* ---- multi-GPU: row-sharded NetVLAD database over NVLink / NVSwitch ---------------------------------
  * SURVEY.md 8e / BASELINE.json configs[2]: the peer database (received_descriptors, R/scripts/data_handler.py:300-301,

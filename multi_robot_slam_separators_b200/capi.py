@@ -49,6 +49,12 @@ class GuessParams(C.Structure):
     _fields_ = [("image_width", C.c_int32), ("image_height", C.c_int32), ("win_size", C.c_float)]
 
 
+class BaParams(C.Structure):
+    _fields_ = [("type", C.c_int32), ("iterations", C.c_int32), ("pixel_variance", C.c_double),
+                ("robust_kernel_delta", C.c_double), ("baseline", C.c_double), ("variance_ignored", C.c_int32),
+                ("reserved_", C.c_int32)]
+
+
 class VerifyOut(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("status", "n_matches", "n_inliers", "pose", "transform", "match_from",
                                           "match_to", "inlier_mask", "best_hyp", "iters_run", "covariance")]
@@ -67,6 +73,15 @@ def pnp_params(fx, fy, cx, cy, iterations=300, min_inliers=5, reproj_error=2.0, 
         g = np.ascontiguousarray(np.asarray(guess, dtype=np.float64)[:3, :4])
         lib().sepb_pnp_set_guess(C.byref(p), _ptr(g))
     return p
+
+
+def ba_params(baseline, iterations=20, pixel_variance=1.0, robust_kernel_delta=8.0, variance_ignored=False):
+    """sepb_ba_params: Vis/BundleAdjustment = 1 with RTAB-Map's defaults; `baseline` = stereo baseline * fy / fx [m]."""
+    b = BaParams()
+    lib().sepb_ba_params_init(C.byref(b), baseline)
+    b.iterations, b.pixel_variance, b.robust_kernel_delta = iterations, pixel_variance, robust_kernel_delta
+    b.variance_ignored = int(variance_ignored)
+    return b
 
 
 def _declare(L):
@@ -154,6 +169,15 @@ def _declare(L):
     for name in ("sepb_match_pairs", "sepb_match_pairs_dev"):
         f = getattr(L, name)
         f.argtypes = [vp, vp, vp, vp, i32, C.POINTER(MatchParams), vp, vp, vp, vp, vp, vp]
+        f.restype = i32
+    L.sepb_ba_params_init.argtypes = [C.POINTER(BaParams), C.c_double]
+    L.sepb_ba_params_init.restype = None
+    L.sepb_ctx_set_bundle_adjustment.argtypes = [vp, C.POINTER(BaParams)]
+    L.sepb_ctx_set_bundle_adjustment.restype = i32
+    for name in ("sepb_bundle_adjust_pairs", "sepb_bundle_adjust_dev"):
+        f = getattr(L, name)
+        f.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, vp, C.POINTER(PnpParams), C.POINTER(BaParams), vp, vp, vp, vp, vp,
+                      i32, vp]
         f.restype = i32
     L.sepb_group_create.argtypes = [i32, vp, C.POINTER(vp)]
     L.sepb_group_create.restype = i32
@@ -250,6 +274,10 @@ class Context:
         """Tensor matcher: 'persistent' (default: one CTA per SM runs through its pairs, tails overlap the next pair's
         first tiles) | 'per_pair' (one CTA per pair); identical results."""
         self.check(lib().sepb_ctx_set_option(self._h, OPT_MATCH_SCHEDULER, {"persistent": 0, "per_pair": 1}[which]))
+
+    def set_bundle_adjustment(self, ba: "BaParams | None"):
+        """Vis/BundleAdjustment for verify_pairs / estimate_transformations on this context (None: off, the default)."""
+        self.check(lib().sepb_ctx_set_bundle_adjustment(self._h, C.byref(ba) if ba is not None else None))
 
     def set_pnp_scheduler(self, which: str):
         """'persistent' (default: persistent CTAs, device work list, idle warps compute chunks of running pairs) |
@@ -384,6 +412,23 @@ def verify_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, pn
     ctx.check(fn(ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, C.byref(mp), C.byref(pnp), _ptr(cs), ch,
                  C.byref(out)))
     return res
+
+
+def bundle_adjust_pairs(ctx: Context, frames_from: Frames, frames_to: Frames, pairs, res, pnp: PnpParams, ba: BaParams,
+                        use_covariance=True):
+    """sepb_bundle_adjust_pairs on a COPY of the verify_pairs result `res` (needs its match lists, masks and, with
+    use_covariance, its covariance): returns the updated status / n_inliers / pose / transform / inlier_mask + stats."""
+    pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+    P = pairs.shape[0]
+    out = {k: np.ascontiguousarray(res[k]).copy() for k in ("status", "n_inliers", "pose", "transform", "inlier_mask")}
+    out["stats"] = np.zeros((P, 4), np.float64)
+    cov = np.ascontiguousarray(res["covariance"], dtype=np.float64) if use_covariance else None
+    ctx.check(lib().sepb_bundle_adjust_pairs(
+        ctx._h, frames_from._h, frames_to._h, _ptr(pairs), P, _ptr(np.ascontiguousarray(res["n_matches"], dtype=np.int32)),
+        _ptr(np.ascontiguousarray(res["match_from"])), _ptr(np.ascontiguousarray(res["match_to"])), _ptr(cov),
+        C.byref(pnp), C.byref(ba), _ptr(out["status"]), _ptr(out["n_inliers"]), _ptr(out["pose"]), _ptr(out["transform"]),
+        _ptr(out["inlier_mask"]), out["inlier_mask"].shape[1], _ptr(out["stats"])))
+    return out
 
 
 def guess_params(width, height, win_size=20.0):

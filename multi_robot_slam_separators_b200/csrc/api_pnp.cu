@@ -157,6 +157,18 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   rc = pnp_ransac_impl(ctx, from, to, d_pairs, n_pairs, o->n_matches, o->match_from, o->match_to, d_nu, pprm,
                        d_custom_samples, custom_h, nullptr, nullptr, o->status, o->n_inliers, o->pose, o->transform,
                        o->inlier_mask, mw, o->best_hyp, o->iters_run);
+  const bool ba = ctx->ba.type == 1;
+  if (ba) SEPB_REQUIRE(ctx, o->inlier_mask && o->covariance, SEPB_E_INVALID);
+  // myRegistrationVis.cpp:1192-1370: the PnP result, its covariance and the inliers go through the 2-view bundle adjustment
+  auto bundle = [&]() -> int {
+    if (!ba) return SEPB_OK;
+    int rcf = sepb_launch_frames_fetch(ctx, const_cast<sepb_frames*>(from), const_cast<sepb_frames*>(to), d_pairs, n_pairs, nullptr,
+                                       0, o->status, 3, 3);
+    if (rcf) return rcf;
+    return sepb_launch_bundle_adjust(ctx, view_of(from), view_of(to), d_pairs, n_pairs, o->n_matches, o->match_from,
+                                     o->match_to, o->covariance, pprm, &ctx->ba, o->status, o->n_inliers, o->pose,
+                                     o->transform, o->inlier_mask, mw, nullptr);
+  };
   auto covariance = [&]() -> int {
     if (!o->covariance) return SEPB_OK;
     SEPB_REQUIRE(ctx, o->inlier_mask != nullptr, SEPB_E_INVALID);
@@ -168,7 +180,12 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
                                 o->match_to, o->inlier_mask, mw, o->transform, o->covariance);
   };
   if (rc) return rc;
-  if (!gprm) return covariance();
+  if (!gprm || ba) {
+    rc = covariance();
+    if (rc) return rc;
+    rc = bundle();
+    if (rc || !gprm) return rc;
+  }
   // ---- pass 2 (stereoCamGeometricTools.cpp:153-164): guess = first result; only where the first pass succeeded
   if (d_status_pass1)
     SEPB_CUDA(ctx, cudaMemcpyAsync(d_status_pass1, o->status, (size_t)n_pairs * 4, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -184,7 +201,9 @@ static int verify_dev_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
                        d_guess, o->status, o->status, o->n_inliers, o->pose, o->transform, o->inlier_mask, mw, o->best_hyp,
                        o->iters_run);
   if (rc) return rc;
-  return covariance();
+  rc = covariance();
+  if (rc) return rc;
+  return bundle();
 }
 
 int sepb_verify_pairs_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
@@ -222,7 +241,8 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   const size_t b_pairs = align_up(P * 8, 256), b_i = align_up(P * 4, 256), b_pose = align_up(P * 48, 256),
                b_T = align_up(P * 48, 256), b_m = align_up(P * F * 2, 256), b_mask = align_up(P * MW * 4, 256),
                b_cs = custom_samples ? align_up(P * custom_h * model_points_of(pprm) * 4, 256) : 0;
-  const size_t b_cov = out->covariance ? align_up(P * 288, 256) : 0;
+  const bool want_cov = out->covariance || ctx->ba.type == 1;
+  const size_t b_cov = want_cov ? align_up(P * 288, 256) : 0;
   const size_t total = b_nu + b_pairs + 6 * b_i + b_pose + b_T + 2 * b_m + b_mask + b_cs + b_cov;
   uint8_t* s = (uint8_t*)sepb_scratch(ctx, total);
   if (!s) return (int)cudaErrorMemoryAllocation;
@@ -240,7 +260,7 @@ static int verify_pairs_impl(sepb_ctx* ctx, const sepb_frames* from, const sepb_
   d.match_from = (uint16_t*)s; s += b_m;
   d.match_to = (uint16_t*)s; s += b_m;
   d.inlier_mask = (uint32_t*)s; s += b_mask;
-  if (out->covariance) { d.covariance = (double*)s; s += b_cov; }
+  if (want_cov) { d.covariance = (double*)s; s += b_cov; }
   int32_t* d_cs = nullptr;
   if (custom_samples) {
     d_cs = (int32_t*)s;
@@ -322,6 +342,121 @@ int sepb_guess_match_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_fr
   SEPB_CUDA(ctx, cudaMemcpyAsync(match_from, d_mf, P * F * 2, cudaMemcpyDeviceToHost, ctx->stream));
   SEPB_CUDA(ctx, cudaMemcpyAsync(match_to, d_mt, P * F * 2, cudaMemcpyDeviceToHost, ctx->stream));
   if (guess_out) SEPB_CUDA(ctx, cudaMemcpyAsync(guess_out, d_g, P * 48, cudaMemcpyDeviceToHost, ctx->stream));
+  SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SEPB_OK;
+}
+
+void sepb_ba_params_init(sepb_ba_params* b, double baseline) {
+  if (!b) return;
+  b->type = 1;
+  b->iterations = 20;
+  b->pixel_variance = 1.0;
+  b->robust_kernel_delta = 8.0;
+  b->baseline = baseline;
+  b->variance_ignored = 0;
+  b->reserved_ = 0;
+}
+
+static int check_ba_params(sepb_ctx* ctx, const sepb_ba_params* b) {
+  SEPB_REQUIRE(ctx, b->type == 1, SEPB_E_INVALID);   // 2 = cvsba: not built
+  SEPB_REQUIRE(ctx, b->iterations >= 1 && b->iterations <= 1000 && b->pixel_variance > 0, SEPB_E_INVALID);
+  return SEPB_OK;
+}
+
+int sepb_ctx_set_bundle_adjustment(sepb_ctx* ctx, const sepb_ba_params* b) {
+  if (!ctx) return SEPB_E_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!b || b->type == 0) {
+    ctx->ba = sepb_ba_params{};
+    return SEPB_OK;
+  }
+  int rc = check_ba_params(ctx, b);
+  if (rc) return rc;
+  ctx->ba = *b;
+  return SEPB_OK;
+}
+
+int sepb_bundle_adjust_dev(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* d_pairs,
+                           int n_pairs, const int32_t* d_n_matches, const uint16_t* d_match_from,
+                           const uint16_t* d_match_to, const double* d_covariance, const sepb_pnp_params* pprm,
+                           const sepb_ba_params* bprm, int32_t* d_status, int32_t* d_n_inliers, double* d_pose,
+                           float* d_transform, uint32_t* d_inlier_mask, int mask_words, double* d_stats) {
+  if (!ctx || !from || !to || !pprm || !bprm) return SEPB_E_INVALID;
+  SEPB_REQUIRE(ctx, n_pairs >= 0, SEPB_E_SHAPE);
+  if (n_pairs == 0) return SEPB_OK;
+  SEPB_REQUIRE(ctx, d_pairs && d_n_matches && d_match_from && d_match_to && d_status && d_n_inliers && d_pose &&
+                        d_transform && d_inlier_mask, SEPB_E_INVALID);
+  SEPB_REQUIRE(ctx, mask_words * 32 >= from->max_feat, SEPB_E_SHAPE);
+  int rc = check_pnp_params(ctx, pprm);
+  if (rc) return rc;
+  rc = check_ba_params(ctx, bprm);
+  if (rc) return rc;
+  SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  FramesUse use(ctx, from, to);
+  rc = sepb_launch_frames_fetch(ctx, const_cast<sepb_frames*>(from), const_cast<sepb_frames*>(to), d_pairs, n_pairs, nullptr, 0,
+                                d_status, 3, 3);
+  if (rc) return rc;
+  return sepb_launch_bundle_adjust(ctx, view_of(from), view_of(to), d_pairs, n_pairs, d_n_matches, d_match_from, d_match_to,
+                                   d_covariance, pprm, bprm, d_status, d_n_inliers, d_pose, d_transform, d_inlier_mask,
+                                   mask_words, d_stats);
+}
+
+int sepb_bundle_adjust_pairs(sepb_ctx* ctx, const sepb_frames* from, const sepb_frames* to, const int32_t* pairs,
+                             int n_pairs, const int32_t* n_matches, const uint16_t* match_from, const uint16_t* match_to,
+                             const double* covariance, const sepb_pnp_params* pprm, const sepb_ba_params* bprm,
+                             int32_t* status, int32_t* n_inliers, double* pose, float* transform, uint32_t* inlier_mask,
+                             int mask_words, double* stats) {
+  if (!ctx || !from || !to || !pprm || !bprm) return SEPB_E_INVALID;
+  SEPB_REQUIRE(ctx, n_pairs >= 0, SEPB_E_SHAPE);
+  if (n_pairs == 0) return SEPB_OK;
+  SEPB_REQUIRE(ctx, pairs && n_matches && match_from && match_to && status && n_inliers && pose && transform &&
+                        inlier_mask, SEPB_E_INVALID);
+  for (int i = 0; i < n_pairs; ++i)
+    SEPB_REQUIRE(ctx, pairs[2 * i] >= 0 && pairs[2 * i] < from->size && pairs[2 * i + 1] >= 0 &&
+                          pairs[2 * i + 1] < to->size && n_matches[i] >= 0 && n_matches[i] <= from->max_feat, SEPB_E_SHAPE);
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t P = (size_t)n_pairs, F = (size_t)from->max_feat, MW = (size_t)mask_words;
+  const size_t b_pairs = align_up(P * 8, 256), b_i = align_up(P * 4, 256), b_pose = align_up(P * 48, 256),
+               b_T = align_up(P * 48, 256), b_m = align_up(P * F * 2, 256), b_mask = align_up(P * MW * 4, 256),
+               b_cov = align_up(P * 288, 256), b_st = align_up(P * 32, 256);
+  uint8_t* s = (uint8_t*)sepb_scratch(ctx, b_pairs + 3 * b_i + b_pose + b_T + 2 * b_m + b_mask + b_cov + b_st);
+  if (!s) return (int)cudaErrorMemoryAllocation;
+  int32_t* d_pairs = (int32_t*)s; s += b_pairs;
+  int32_t* d_nm = (int32_t*)s; s += b_i;
+  int32_t* d_st = (int32_t*)s; s += b_i;
+  int32_t* d_ni = (int32_t*)s; s += b_i;
+  double* d_pose = (double*)s; s += b_pose;
+  float* d_T = (float*)s; s += b_T;
+  uint16_t* d_mf = (uint16_t*)s; s += b_m;
+  uint16_t* d_mt = (uint16_t*)s; s += b_m;
+  uint32_t* d_mask = (uint32_t*)s; s += b_mask;
+  double* d_cov = (double*)s; s += b_cov;
+  double* d_stats = (double*)s;
+#define H2D(dst, src, bytes) SEPB_CUDA(ctx, cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyHostToDevice, ctx->stream))
+  H2D(d_pairs, pairs, P * 8);
+  H2D(d_nm, n_matches, P * 4);
+  H2D(d_st, status, P * 4);
+  H2D(d_ni, n_inliers, P * 4);
+  H2D(d_pose, pose, P * 48);
+  H2D(d_T, transform, P * 48);
+  H2D(d_mf, match_from, P * F * 2);
+  H2D(d_mt, match_to, P * F * 2);
+  H2D(d_mask, inlier_mask, P * MW * 4);
+  if (covariance) H2D(d_cov, covariance, P * 288);
+#undef H2D
+  SEPB_CUDA(ctx, cudaMemsetAsync(d_stats, 0, P * 32, ctx->stream));
+  int rc = sepb_bundle_adjust_dev(ctx, from, to, d_pairs, n_pairs, d_nm, d_mf, d_mt, covariance ? d_cov : nullptr, pprm, bprm,
+                                  d_st, d_ni, d_pose, d_T, d_mask, mask_words, d_stats);
+  if (rc) return rc;
+#define D2H(dst, src, bytes) SEPB_CUDA(ctx, cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, ctx->stream))
+  D2H(status, d_st, P * 4);
+  D2H(n_inliers, d_ni, P * 4);
+  D2H(pose, d_pose, P * 48);
+  D2H(transform, d_T, P * 48);
+  D2H(inlier_mask, d_mask, P * MW * 4);
+  if (stats) D2H(stats, d_stats, P * 32);
+#undef D2H
   SEPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SEPB_OK;
 }

@@ -34,7 +34,8 @@ struct sepb_ctx {
   size_t k3_order_cap = 0;
   // per-device kernel attribute bookkeeping (cudaFuncSetAttribute is per device)
   size_t cfg_hamming_smem = 0, cfg_hamming_mma_smem = 0, cfg_hamming_mma_smem_wide = 0, cfg_guess_smem = 0;
-  size_t cfg_hamming_mma_psmem = 0, cfg_hamming_mma_psmem_wide = 0;
+  size_t cfg_hamming_mma_psmem = 0, cfg_hamming_mma_psmem_wide = 0, cfg_ba_smem = 0;
+  sepb_ba_params ba{};          // ba.type == 0: no bundle adjustment after PnP (sepb_ctx_set_bundle_adjustment)
   int opt_match_kernel = SEPB_MATCH_AUTO;
   int opt_match_tile = 0;       // 0: widest K2T accumulator tile that fits, 128: force the narrow geometry
   int opt_pnp_sched = SEPB_PNP_SCHED_PERSISTENT;
@@ -274,6 +275,11 @@ int sepb_launch_pose_cov(sepb_ctx* ctx, FramesView from, FramesView to, const in
                          const uint16_t* d_match_to, const uint32_t* d_inlier_mask, int mask_words,
                          const float* d_transform, double* d_cov);
 LazyPull sepb_lazy_pull_of(sepb_frames* from, sepb_frames* to, int min_matches);
+int sepb_launch_bundle_adjust(sepb_ctx* ctx, FramesView from, FramesView to, const int32_t* d_pairs, int n_pairs,
+                              const int32_t* d_n_matches, const uint16_t* d_match_from, const uint16_t* d_match_to,
+                              const double* d_cov, const sepb_pnp_params* pprm, const sepb_ba_params* bprm,
+                              int32_t* d_status, int32_t* d_n_inliers, double* d_pose, float* d_transform,
+                              uint32_t* d_inlier_mask, int mask_words, double* d_stats);
 int sepb_launch_frames_fetch(sepb_ctx* ctx, sepb_frames* from, sepb_frames* to, const int32_t* d_pairs, int n_pairs,
                              const int32_t* d_n_matches, int min_matches, const int32_t* d_status, int bits_from, int bits_to);
 int sepb_launch_sample_table(sepb_ctx* ctx, uint16_t* d_table, int max_count, int H, int model_points);

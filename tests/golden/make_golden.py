@@ -162,8 +162,33 @@ def golden_p3p():
     np.savez_compressed(os.path.join(OUT, "p3p.npz"), **out)
 
 
+def golden_ba():
+    """oracle/ba.py on the seeded problems of tests/ba_problems.py.  NOT a pin against the reference (g2o / RTAB-Map are
+    not installed here, see the oracle's header): a regression fixture for the restated algorithm, which
+    tests/test_oracle_ba.py checks against scipy.optimize.least_squares, and the known answers the CUDA kernel is held to."""
+    from tests import ba_problems as bp
+    from oracle import ba
+    out = {}
+    cases = bp.default_set()
+    for i, (seed, n, kw) in enumerate(cases):
+        pr = bp.make(seed, n, **kw)
+        ok, T, kept, res = ba.bundle_adjust_pair(pr["T0"], pr["kp2d_from"], pr["kp3d_from"], pr["kp2d_to"], pr["kp3d_to"],
+                                                 (bp.FX, bp.FY, bp.CX, bp.CY), bp.BASELINE, bp.LOCAL_R, pr["local_t"],
+                                                 pr["cov"], 5)
+        for k in ("T0", "kp2d_from", "kp3d_from", "kp2d_to", "kp3d_to", "cov", "local_t"):
+            out[f"{k}_{i}"] = pr[k]
+        out[f"ok_{i}"] = np.array(ok)
+        out[f"T_{i}"] = T
+        out[f"kept_{i}"] = kept
+        out[f"chi2_{i}"] = np.array(res["chi2"])
+        out[f"iterations_{i}"] = np.array(res["iterations"])
+    np.savez(os.path.join(OUT, "ba.npz"), n=len(cases), **out)
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "p3p":      # round 2: only the new file (the others stay byte-identical)
+    if len(sys.argv) > 1 and sys.argv[1] == "ba":       # round 2: only the new file
+        golden_ba()
+    elif len(sys.argv) > 1 and sys.argv[1] == "p3p":      # round 2: only the new file (the others stay byte-identical)
         golden_p3p()
     else:
         golden_svd(); golden_hamming(); golden_netvlad(); golden_epnp(); golden_pnp_ransac(); golden_p3p()
