@@ -48,6 +48,11 @@ void sh_geo_configure(void* g, int pnp_flags, int refine_iterations, int opencv3
   gt->setOpenCV32Semantics(opencv32 != 0);
 }
 
+// Vis/BundleAdjustment (0 off, 1 g2o-style) with the stereo baseline in metres; 1 on success
+int sh_geo_bundle_adjustment(void* g, int type, double stereo_baseline) {
+  return static_cast<GeometricTools*>(g)->setBundleAdjustment(type, stereo_baseline) ? 1 : 0;
+}
+
 // returns res.success; pose7 = position xyz + orientation xyzw
 int sh_geo_estimate(void* g, const uint8_t* descF, int nF, const float* kp2F, const int32_t* octF, const float* kp3F,
                     const uint8_t* descT, int nT, const float* kp2T, const int32_t* octT, const float* kp3T, double* pose7,

@@ -75,6 +75,7 @@ int main(int argc, char** argv) {
   int min_inliers = 5, dims = 128, max_nb = 20, device = 0;
   int pnp_flags = 0, pnp_refine_iterations = 0;
   bool opencv32_semantics = false;
+  int bundle_adjustment = 0;   // RTAB-Map's default is 1 when it was built with g2o; opt in here (parity unpinned)
   double distance = 0.13;
   if (!n.getParam("frame_id", frame_id)) ROS_ERROR("Couldn't find frame ID");
   if (!n.getParam("separators_min_inliers", min_inliers)) ROS_ERROR("Couldn't find separators_min_inliers param");
@@ -85,6 +86,7 @@ int main(int argc, char** argv) {
   n.getParam("Vis/PnPFlags", pnp_flags);                         // R/src/myRegistrationVis.cpp:103
   n.getParam("Vis/PnPRefineIterations", pnp_refine_iterations);  // :104
   n.getParam("sepb_opencv32_semantics", opencv32_semantics);
+  n.getParam("Vis/BundleAdjustment", bundle_adjustment);        // :113
 
   // ---- camera model: left camera_info (rectified: P holds fx, fy, cx, cy) + tf frame_id <- camera frame, as
   //      stereoCameraModelFromROS builds cam_.left() and its localTransform (stereoCamGeometricTools.cpp:38-77)
@@ -122,6 +124,12 @@ int main(int argc, char** argv) {
   geo.setPnPFlags(pnp_flags);
   geo.setPnPRefineIterations(pnp_refine_iterations);
   geo.setOpenCV32Semantics(opencv32_semantics);
+  if (bundle_adjustment != 0) {
+    // StereoCameraModel::baseline() = -right.Tx / right.fx (right camera_info: P[3] = Tx)
+    const double baseline = info_r->P[0] != 0 ? -info_r->P[3] / info_r->P[0] : 0.0;
+    if (!geo.setBundleAdjustment(bundle_adjustment, baseline))
+      ROS_ERROR("separators_b200: Vis/BundleAdjustment = %d is not available (1 = g2o-style only); running without", bundle_adjustment);
+  }
   sepb_host::PlaceRecognition place(dev, dims, distance, max_nb);
   ros::ServiceClient add_seps = n.serviceClient<mrs::ReceiveSeparators>("add_separators_pose_graph");
 

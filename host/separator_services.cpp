@@ -68,6 +68,20 @@ GeometricTools::GeometricTools(Device& dev, const CameraModel& cam, int min_inli
   oct_.resize(max_feat_);
 }
 
+bool GeometricTools::setBundleAdjustment(int type, double stereo_baseline, int iterations, double pixel_variance,
+                                         double robust_kernel_delta) {
+  if (!dev_.ok()) return false;
+  if (type == 0) return sepb_ctx_set_bundle_adjustment(dev_.ctx(), nullptr) == SEPB_OK;
+  sepb_ba_params b;
+  // myRegistrationVis.cpp:1247-1252: Tx = -baseline * fy, and VertexCam::setKcam gets -Tx / fx
+  sepb_ba_params_init(&b, stereo_baseline * pnp_.fy / pnp_.fx);
+  b.type = type;
+  b.iterations = iterations;
+  b.pixel_variance = pixel_variance;
+  b.robust_kernel_delta = robust_kernel_delta;
+  return sepb_ctx_set_bundle_adjustment(dev_.ctx(), &b) == SEPB_OK;
+}
+
 GeometricTools::~GeometricTools() {
   sepb_frames_destroy(from_);
   sepb_frames_destroy(to_);

@@ -63,6 +63,11 @@ class GeometricTools {
   void setPnPFlags(int flags) { pnp_.flags = flags; }        // Vis/PnPFlags: 0 ITERATIVE, 2 P3P, 5 AP3P (myRegistrationVis.cpp:103)
   void setPnPRefineIterations(int n) { pnp_.refine_iterations = n; }   // Vis/PnPRefineIterations (:104)
   void setOpenCV32Semantics(bool on) { pnp_.minimal_model = on ? 1 : 0; }   // return the minimal-set model (OpenCV 3.2)
+  // Vis/BundleAdjustment (myRegistrationVis.cpp:113,1192-1370): 0 = off (default here), 1 = the g2o-style 2-view
+  // adjustment after every PnP of the call; `stereo_baseline` [m] is StereoCameraModel::baseline() (right camera_info:
+  // -P[3] / P[0]).  The setting lives on the shared device context.  False for an unsupported type (2 = cvsba).
+  bool setBundleAdjustment(int type, double stereo_baseline, int iterations = 20, double pixel_variance = 1.0,
+                           double robust_kernel_delta = 8.0);
 
   // Always returns true (the ROS convention: the response is valid); failure of the computation is in-band:
   // res.success = false with a zero pose (MsgConversion.cpp:77-80).  Never throws, never aborts: malformed

@@ -160,6 +160,43 @@ def test_estimate_transformation_solver_options(flags, refine, cv32):
 
 
 @pytest.mark.gpu
+def test_estimate_transformation_with_bundle_adjustment():
+    """Vis/BundleAdjustment = 1 on the handler (GeometricTools::setBundleAdjustment): the service answers what the batch
+    C ABI gives with sepb_ctx_set_bundle_adjustment -- the adjusted pose of the second call and its inlier count."""
+    from multi_robot_slam_separators_b200 import capi
+    L = load()
+    L.sh_geo_bundle_adjustment.argtypes = [C.c_void_p, C.c_int32, C.c_double]
+    L.sh_geo_bundle_adjustment.restype = C.c_int32
+    N = 24
+    A, B = synth.make_robots(2, N, n_feat=1000, dim=8, seed=322, overlap=0.5)
+    pairs = [(o, l) for l in range(N) for o in range(N) if A.place[o] == B.place[l]][:5]
+    ctx = capi.Context(0)
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    gp = capi.guess_params(synth.WIDTH, synth.HEIGHT)
+    prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY)
+    base = capi.estimate_transformations(ctx, fa, fb, np.array(pairs, np.int32), prm, gp, 0.8)
+    ctx.set_bundle_adjustment(capi.ba_params(synth.BASELINE * synth.FY / synth.FX))
+    ref = capi.estimate_transformations(ctx, fa, fb, np.array(pairs, np.int32), prm, gp, 0.8)
+    dev = L.sh_device_create(0)
+    geo = L.sh_geo_create(dev, synth.FX, synth.FY, synth.CX, synth.CY, synth.WIDTH, synth.HEIGHT, 5, 1000)
+    assert L.sh_geo_bundle_adjustment(geo, 2, synth.BASELINE) == 0        # cvsba: not built, refused
+    assert L.sh_geo_bundle_adjustment(geo, 1, synth.BASELINE) == 1
+    n_ok = n_diff = 0
+    for k, (o, l) in enumerate(pairs):
+        ok, pose, cov, inl, mat = estimate(L, geo, A, o, B, l)
+        assert ok == int(ref["status"][k] == 1)
+        if ok:
+            n_ok += 1
+            T = ref["transform"][k].reshape(3, 4).astype(np.float64)
+            assert np.array_equal(pose[:3], T[:, 3]) and inl == ref["n_inliers"][k] and mat == ref["n_matches"][k]
+            n_diff += int(not np.array_equal(ref["transform"][k], base["transform"][k]))
+    assert n_ok >= 4 and n_diff >= 1
+    assert L.sh_geo_bundle_adjustment(geo, 0, 0.0) == 1
+    L.sh_geo_destroy(geo); L.sh_device_destroy(dev)
+    fa.close(); fb.close(); ctx.close()
+
+
+@pytest.mark.gpu
 def test_find_matches_compute_and_receive_separators():
     from oracle import find_matches as fm
     L = load()
