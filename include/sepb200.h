@@ -174,6 +174,20 @@ SEPB_API int sepb_netvlad_topk(sepb_ctx* ctx, const sepb_db* db, const double* q
 SEPB_API int sepb_netvlad_topk_dev(sepb_ctx* ctx, const sepb_db* db, const double* d_queries, int nq, int k, int mode,
                                    const uint8_t* d_row_mask, const int32_t* d_ign_start, const int32_t* d_ign_col,
                                    int32_t* d_out_idx, double* d_out_dist);
+/* Allocation-free variant of sepb_netvlad_topk_dev(mode = SEPB_NN_EXACT).  It has NO counterpart in the reference: it
+ * was added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments and bit-identical results; the per-split
+ * partial lists of the two-pass scan live in a fixed 8 MiB device array inside the library (held by every GPU that
+ * loads it until the process exits) instead of the context's grow-only scratch, and the call performs no cudaMalloc /
+ * cudaFree / allocating library call.  Limit: align256(splits * nq * k * 8) + align256(splits * nq * k * 4) <= 8 MiB,
+ * with splits = clamp(ceil(2 * SMs / ceil(nq / 128)), 1, min(64, ceil(db size / 32))); beyond it the call returns
+ * SEPB_E_SHAPE and sepb_last_error() says so (on 148 SMs: every nq fits for k <= 9, every nq <= 6 241 for k <= 16; the
+ * calls refused are 10 <= k <= 16 with some nq in 6 242 .. 37 760 -- split those into smaller batches).  The first call on a device resolves the array's device address (cudaGetSymbolAddress, no allocation) and
+ * the launch attributes: make one call, nq = 0 is enough, before a capture starts.  All calls on a device share the
+ * array: calls that overlap on the GPU (two streams, contexts or host threads) race -- serialise them. */
+SEPB_API int sepb_netvlad_topk_exact_static_dev(sepb_ctx* ctx, const sepb_db* db, const double* d_queries, int nq, int k,
+                                                const uint8_t* d_row_mask, const int32_t* d_ign_start,
+                                                const int32_t* d_ign_col, int32_t* d_out_idx, double* d_out_dist);
 /* Test / profiling hook of the K1 filter (netvlad_gemm.cu): the SEPB_NN_TENSOR search on host queries, plus
  * out_v [nq][db size] f32 = the raw filter values ||d||^2 - 2 q.d of the tcgen05 GEMM (NULL to skip) and
  * stats[4] = {candidates re-ranked in f64, rows proven complete by the filter, rows sent to the exact scan, 0}.

@@ -145,6 +145,8 @@ def _declare(L):
     L.sepb_netvlad_topk.restype = i32
     L.sepb_netvlad_topk_dev.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp, vp]
     L.sepb_netvlad_topk_dev.restype = i32
+    L.sepb_netvlad_topk_exact_static_dev.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp, vp]
+    L.sepb_netvlad_topk_exact_static_dev.restype = i32
     L.sepb_netvlad_filter_debug.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp]
     L.sepb_netvlad_filter_debug.restype = i32
     L.sepb_topk_merge_dev.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
@@ -523,6 +525,15 @@ class NetvladDB:
         self.ctx.check(lib().sepb_netvlad_topk(self.ctx._h, self._h, _ptr(q), nq, k, mode, _ptr(rm), _ptr(ign),
                                                0 if ign is None else ign.shape[0], _ptr(idx), _ptr(dist)))
         return idx, dist
+
+    def topk_exact_static_dev(self, d_queries: int, nq: int, k: int, d_out_idx: int, d_out_dist: int, d_row_mask: int = 0,
+                              d_ign_start: int = 0, d_ign_col: int = 0):
+        """sepb_netvlad_topk_exact_static_dev: the exact search on DEVICE pointers (integers) with the partial lists in
+        the library's fixed 8 MiB device array -- no allocation inside the call.  Asynchronous on the context's stream;
+        overlapping calls on one device race on that array."""
+        p = lambda a: C.c_void_p(a) if a else None  # noqa: E731
+        self.ctx.check(lib().sepb_netvlad_topk_exact_static_dev(self.ctx._h, self._h, p(d_queries), nq, k, p(d_row_mask),
+                                                                p(d_ign_start), p(d_ign_col), p(d_out_idx), p(d_out_dist)))
 
     def filter_debug(self, queries, k=5, want_v=True):
         """K1 tensor-core filter with its raw values exposed (tests / profiling):

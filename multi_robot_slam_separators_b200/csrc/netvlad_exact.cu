@@ -215,3 +215,69 @@ int sepb_launch_topk_merge(sepb_ctx* ctx, const int32_t* d_in_idx, const double*
   SEPB_CUDA(ctx, cudaGetLastError());
   return SEPB_OK;
 }
+
+// ---- allocation-free variant of the exact search ----------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  sepb_netvlad_topk_dev takes the per-split
+// partial lists of the two-pass scan from the context's grow-only scratch (cudaMalloc on growth); here they live in a
+// file-scope device array of fixed size that every GPU loading the library holds until exit.
+//   * The array's name is only a host-side stand-in in host code: its device address is taken once per device, with that
+//     device current, by cudaGetSymbolAddress, and that pointer is what the kernels receive.
+//   * Every call shares the array, and it keeps the last call's contents.  Nothing in it has to start at zero: the merge
+//     reads exactly the [splits][nq][k] slots the scan of the SAME call has written, so nothing is cleared.
+//   * Calls that overlap on the GPU (two streams / contexts / host threads on one device) race on it.
+constexpr size_t kStaticScratchBytes = size_t(8) << 20;   // 8 MiB per device: splits * nq * k * 12 bytes (+ alignment)
+static __device__ __align__(256) unsigned char g_exact_static_scratch[kStaticScratchBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[kMaxDevices] = {};   // device address of g_exact_static_scratch, per device
+}  // namespace
+
+extern "C" int sepb_netvlad_topk_exact_static_dev(sepb_ctx* ctx, const sepb_db* db, const double* d_q, int nq, int k,
+                                                  const uint8_t* d_row_mask, const int32_t* d_ign_start,
+                                                  const int32_t* d_ign_col, int32_t* d_out_idx, double* d_out_dist) {
+  if (!ctx || !db) return SEPB_E_INVALID;
+  SEPB_REQUIRE(ctx, nq >= 0 && k >= 1 && k <= KMAX, SEPB_E_SHAPE);
+  SEPB_REQUIRE(ctx, ctx->device >= 0 && ctx->device < kMaxDevices, SEPB_E_STATE);
+  SEPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  unsigned char* base_ptr = nullptr;
+  {
+    // set-up, once per device (a call with nq == 0 does only this, e.g. before a graph capture starts)
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[ctx->device]) {
+      void* p = nullptr;
+      SEPB_CUDA(ctx, cudaGetSymbolAddress(&p, g_exact_static_scratch));
+      g_static_ptr[ctx->device] = static_cast<unsigned char*>(p);
+    }
+    base_ptr = g_static_ptr[ctx->device];
+  }
+  if (nq == 0) return SEPB_OK;
+  SEPB_REQUIRE(ctx, d_q && d_out_idx && d_out_dist, SEPB_E_INVALID);
+  // same database split as sepb_netvlad_topk_dev (api_netvlad.cu:exact_splits): identical launches, identical results
+  const int row_blocks = (nq + QB - 1) / QB;
+  int splits = (2 * ctx->sm_count + row_blocks - 1) / row_blocks;
+  const int tiles = (db->size + NB - 1) / NB;
+  splits = splits < 64 ? splits : 64;
+  splits = splits < tiles ? splits : tiles;
+  splits = splits > 1 ? splits : 1;
+  int32_t* part_i = nullptr;
+  double* part_d = nullptr;
+  if (splits > 1) {
+    const size_t b_d = align_up((size_t)splits * nq * k * 8, 256), b_i = align_up((size_t)splits * nq * k * 4, 256);
+    if (b_d + b_i > kStaticScratchBytes) {
+      char msg[256];
+      snprintf(msg, sizeof msg,
+               "sepb_netvlad_topk_exact_static_dev: %d splits x %d queries x k = %d need %zu bytes of partial lists, "
+               "the static scratch holds %zu (use sepb_netvlad_topk_dev or fewer queries per call)",
+               splits, nq, k, b_d + b_i, kStaticScratchBytes);
+      return sepb_fail(ctx, SEPB_E_SHAPE, msg, __FILE__, __LINE__);
+    }
+    part_d = reinterpret_cast<double*>(base_ptr);
+    part_i = reinterpret_cast<int32_t*>(base_ptr + b_d);
+  }
+  return sepb_launch_netvlad_exact(ctx, d_q, nq, db->rows, db->size, db->dim, k, db->base, d_row_mask,
+                                   db->has_mask ? db->col_mask : nullptr, d_ign_start, d_ign_col, splits, part_i, part_d,
+                                   d_out_idx, d_out_dist, nullptr, nullptr);
+}
