@@ -302,6 +302,12 @@ def run_ours(args):
     ms_verify = timed(lambda: eng.verify_dev(pairs), 10)
     ms_two_pass = timed(lambda: eng.verify_dev(pairs, two_pass=True), 3)   # + second call of estimate_transformation
     ms_k3 = max(ms_verify - ms_k2, 0.0)
+    # Vis/BundleAdjustment = 1 (off by default, outside the timed step): the same verification with the
+    # 2-view bundle adjustment after PnP
+    eng.ctx.set_bundle_adjustment(capi.ba_params(synth.BASELINE * synth.FY / synth.FX))
+    ms_verify_ba = timed(lambda: eng.verify_dev(pairs), 3)
+    n_ok_ba = int((eng.verify_dev(pairs)["status"] == 1).sum().item())
+    eng.ctx.set_bundle_adjustment(None)
 
     # ---- end to end through the host-buffer C ABI -------------------------------------------
     # Every step copies BOTH robots' keyframes + descriptors from pinned host memory (H2D), searches, verifies and
@@ -502,6 +508,9 @@ def run_ours(args):
                 "two_pass": {"ms_verify": ms_two_pass, "pairs_per_s": world * P / ((ms_k1 + ms_two_pass) * 1e-3),
                              "note": "whole estimate_transformation service call: K2 + K3, then K2G + K3 seeded with the first result "
                                      "(R/src/stereoCamGeometricTools.cpp:141-164); rank-0 timing x n_gpus"},
+                "bundle_adjustment": {"ms_verify": ms_verify_ba, "ms_ba": max(ms_verify_ba - ms_verify, 0.0), "verified_ok": n_ok_ba,
+                                      "note": "not in the timed step: verification with Vis/BundleAdjustment = 1 (5 + 20 LM iterations per "
+                                              "verified pair, R/src/myRegistrationVis.cpp:1192-1370); rank-0 timing"},
                 "nn_queries_per_s": args.frames / (ms_k1 * 1e-3), "nn_mode": args.nn, "match_kernel": match_kernel,
                 "verified_ok_per_step": n_ok, "pairs_with_ransac_per_step": n_ransac, "ransac_iters_mean": iters_mean, "matches_per_ransac_pair_mean": m_mean,
                 "ransac_pairs_per_s": ransac_pairs_per_s,

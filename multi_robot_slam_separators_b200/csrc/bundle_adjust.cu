@@ -19,7 +19,13 @@
 
 namespace {
 
-constexpr int kThreadsB = 128;
+#ifndef SEPB_BA_MIN_BLOCKS
+#define SEPB_BA_MIN_BLOCKS 1   // resident CTAs per SM the register allocation aims at (section 4.2 of DESIGN.md)
+#endif
+#ifndef SEPB_BA_THREADS
+#define SEPB_BA_THREADS 128
+#endif
+constexpr int kThreadsB = SEPB_BA_THREADS;
 constexpr int kWarpsB = kThreadsB / 32;
 constexpr double kHuge = 1.7976931348623157e308;
 
@@ -322,32 +328,45 @@ struct Ctl {
   int qmax, ok, again, stop, cur, fail, iters;
 };
 
-__device__ void link_terms(Ctl& c) {
-  // numeric Jacobian as BaseBinaryEdge::linearizeOplus does it: central differences, step 1e-9
-  double e[6], J[36];
-  link_error(c.link_inv, c.cam1_inv, c.c2.p, e);
-  for (int d = 0; d < 6; ++d) {
-    double u[6] = {0, 0, 0, 0, 0, 0}, ep[6], em[6];
-    u[d] = 1e-9;
-    link_error(c.link_inv, c.cam1_inv, se3_update(c.c2.p, u), ep);
-    u[d] = -1e-9;
-    link_error(c.link_inv, c.cam1_inv, se3_update(c.c2.p, u), em);
-    for (int r = 0; r < 6; ++r) J[6 * r + d] = (ep[r] - em[r]) * (1.0 / 2e-9);
-  }
-  int k = 0;
-  for (int i = 0; i < 6; ++i) {
-    for (int j = i; j < 6; ++j, ++k) {
-      double s = 0;
-      for (int r = 0; r < 6; ++r) s += J[6 * r + i] * c.info[r] * J[6 * r + j];
-      c.Al[k] = s;
+// The link edge's share of the camera block at c2, by the whole CTA: numeric Jacobian as BaseBinaryEdge::linearizeOplus
+// does it (central differences, step 1e-9) -- threads 0..12 evaluate the error at c2 and at its twelve perturbations,
+// threads 0..27 each assemble one entry of J^T Omega J (21), -J^T Omega e (6) and e^T Omega e.  Ends with a barrier.
+__device__ void link_terms(Ctl& c, double* s_le /*[13][6]*/) {
+  const int tid = threadIdx.x;
+  if (tid < 13) {
+    double e[6];
+    if (tid == 0) {
+      link_error(c.link_inv, c.cam1_inv, c.c2.p, e);
+    } else {
+      double u[6] = {0, 0, 0, 0, 0, 0};
+      u[(tid - 1) >> 1] = (tid & 1) ? 1e-9 : -1e-9;     // 1, 2: +/- step of dimension 0; 3, 4: dimension 1; ...
+      link_error(c.link_inv, c.cam1_inv, se3_update(c.c2.p, u), e);
     }
-    double s = 0;
-    for (int r = 0; r < 6; ++r) s += J[6 * r + i] * c.info[r] * e[r];
-    c.bcl[i] = -s;
+    for (int r = 0; r < 6; ++r) s_le[6 * tid + r] = e[r];
   }
-  double s = 0;
-  for (int r = 0; r < 6; ++r) s += e[r] * c.info[r] * e[r];
-  c.chil = s;
+  __syncthreads();
+  if (tid < 28) {
+    // J[r][d] = (e_plus[d][r] - e_minus[d][r]) / 2e-9
+    auto J = [&](int r, int d) { return (s_le[6 * (1 + 2 * d) + r] - s_le[6 * (2 + 2 * d) + r]) * (1.0 / 2e-9); };
+    if (tid < 21) {
+      int i = 0, k = tid;
+      while (k >= 6 - i) { k -= 6 - i; ++i; }
+      const int j = i + k;
+      double sum = 0;
+      for (int r = 0; r < 6; ++r) sum += J(r, i) * c.info[r] * J(r, j);
+      c.Al[tid] = sum;
+    } else if (tid < 27) {
+      const int i = tid - 21;
+      double sum = 0;
+      for (int r = 0; r < 6; ++r) sum += J(r, i) * c.info[r] * s_le[r];
+      c.bcl[i] = -sum;
+    } else {
+      double sum = 0;
+      for (int r = 0; r < 6; ++r) sum += s_le[r] * c.info[r] * s_le[r];
+      c.chil = sum;
+    }
+  }
+  __syncthreads();
 }
 
 __device__ double link_chi(const Ctl& c, const Se3& cam2) {
@@ -364,7 +383,7 @@ __device__ __forceinline__ float depth_in_camera(const BaKernelParams& P, const 
   return __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r0, p[0]), __fmul_rn(r1, p[1])), __fmul_rn(r2, p[2])), tz);
 }
 
-__global__ void __launch_bounds__(kThreadsB)
+__global__ void __launch_bounds__(kThreadsB, SEPB_BA_MIN_BLOCKS)
 bundle_adjust_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs,
                      const int32_t* __restrict__ n_matches, const uint16_t* __restrict__ match_from,
                      const uint16_t* __restrict__ match_to, const double* __restrict__ cov, BaKernelParams P,
@@ -374,6 +393,7 @@ bundle_adjust_kernel(FramesView from, FramesView to, const int32_t* __restrict__
   extern __shared__ __align__(16) unsigned char s_raw[];
   __shared__ Ctl ctl;
   __shared__ double s_red[kWarpsB * 34];
+  __shared__ double s_le[13 * 6];
   __shared__ int s_off[64 + 1];
   const int pair = blockIdx.x, tid = threadIdx.x;
   if (pair >= n_pairs || status[pair] != 1) return;
@@ -481,8 +501,8 @@ bundle_adjust_kernel(FramesView from, FramesView to, const int32_t* __restrict__
     // ---- SparseOptimizer::optimize(n_iter) with OptimizationAlgorithmLevenberg
 #pragma unroll 1
     for (int it = 0; it < n_iter; ++it) {
+      link_terms(ctl, s_le);
       if (tid == 0) {
-        link_terms(ctl);
         ctl.qmax = 0;
         ctl.rho = 0;
       }
