@@ -126,19 +126,53 @@ struct LazyPull {
 };
 
 #ifdef __CUDACC__
-// CTA-wide copy of one row out of mapped host memory (16-byte loads when both sides allow it)
-__device__ __forceinline__ void sepb_pull_row(void* dst, const void* src, int bytes) {
-  if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
-    const int n16 = bytes >> 4;
-    const int4* s = reinterpret_cast<const int4*>(src);
-    int4* d = reinterpret_cast<int4*>(dst);
-    for (int i = threadIdx.x; i < n16; i += blockDim.x) d[i] = __ldcs(s + i);
-    for (int i = (n16 << 4) + 4 * threadIdx.x; i < bytes; i += 4 * blockDim.x)
-      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
+// Copy of up to two rows out of mapped host memory by `nthreads` threads (row B may be empty).  A load from host memory
+// is a PCIe round trip (microseconds; tens of them while a bulk cudaMemcpyAsync saturates the bus), so every 16-byte
+// load of a batch -- U per thread, both rows in one index space -- is issued before the first store: a 12 KB + 8 KB
+// pair of rows costs 256 threads ONE round trip instead of five dependent ones.
+template <int U = 8>
+__device__ __forceinline__ void sepb_pull_rows(void* dA, const void* sA, int bytesA, void* dB, const void* sB, int bytesB,
+                                               int tid, int nthreads) {
+  if (((((uintptr_t)dA | (uintptr_t)sA) & 15) == 0) && (bytesB == 0 || ((((uintptr_t)dB | (uintptr_t)sB) & 15) == 0))) {
+    const int nA = bytesA >> 4, nB = bytesB >> 4, n = nA + nB;
+    const int4* a16 = reinterpret_cast<const int4*>(sA);
+    const int4* b16 = reinterpret_cast<const int4*>(sB);
+    int4* da16 = reinterpret_cast<int4*>(dA);
+    int4* db16 = reinterpret_cast<int4*>(dB);
+    // the (< 16 byte) ends of the rows: one word per thread, loaded up front as well
+    const int wA = (bytesA & 15) >> 2, wB = (bytesB & 15) >> 2;
+    int32_t tail = 0;
+    const bool tail_a = tid < wA, tail_b = !tail_a && tid >= 4 && tid - 4 < wB;
+    if (tail_a) tail = reinterpret_cast<const int32_t*>(sA)[4 * nA + tid];
+    if (tail_b) tail = reinterpret_cast<const int32_t*>(sB)[4 * nB + tid - 4];
+    for (int base = 0; base < n; base += U * nthreads) {
+      int4 v[U];
+#pragma unroll
+      for (int j = 0; j < U; ++j) {
+        const int i = base + j * nthreads + tid;
+        if (i < n) v[j] = __ldcs(i < nA ? a16 + i : b16 + (i - nA));
+      }
+#pragma unroll
+      for (int j = 0; j < U; ++j) {
+        const int i = base + j * nthreads + tid;
+        if (i < n) {
+          if (i < nA) da16[i] = v[j];
+          else db16[i - nA] = v[j];
+        }
+      }
+    }
+    if (tail_a) reinterpret_cast<int32_t*>(dA)[4 * nA + tid] = tail;
+    if (tail_b) reinterpret_cast<int32_t*>(dB)[4 * nB + tid - 4] = tail;
   } else {
-    for (int i = 4 * threadIdx.x; i < bytes; i += 4 * blockDim.x)
-      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
+    for (int i = 4 * tid; i < bytesA; i += 4 * nthreads)
+      *reinterpret_cast<int32_t*>((char*)dA + i) = *reinterpret_cast<const int32_t*>((const char*)sA + i);
+    for (int i = 4 * tid; i < bytesB; i += 4 * nthreads)
+      *reinterpret_cast<int32_t*>((char*)dB + i) = *reinterpret_cast<const int32_t*>((const char*)sB + i);
   }
+}
+// CTA-wide copy of one row
+__device__ __forceinline__ void sepb_pull_row(void* dst, const void* src, int bytes) {
+  sepb_pull_rows(dst, src, bytes, nullptr, nullptr, 0, threadIdx.x, blockDim.x);
 }
 // first CTA to ask for `bit` of a slot's row claims the copy (one lane calls; the resident bits are bytes)
 __device__ __forceinline__ bool sepb_claim_row(uint8_t* have, int slot, unsigned bit) {

@@ -40,8 +40,16 @@ __global__ void __launch_bounds__(128) frames_fetch_kernel(float* kp2d, float* k
   const int n = min(max(count[slot], 0), max_feat);
   const size_t row = (size_t)slot * max_feat, hrow = (size_t)rel * max_feat;
   unsigned long long bytes = 0;
-  if ((want & 1) && h_kp2d) { sepb_pull_row(kp2d + row * 2, h_kp2d + hrow * 2, n * 8); bytes += (unsigned long long)n * 8; }
-  if ((want & 2) && h_kp3d) { sepb_pull_row(kp3d + row * 3, h_kp3d + hrow * 3, n * 12); bytes += (unsigned long long)n * 12; }
+  {
+    // pixels and 3-D points in one batch of loads (one PCIe round trip for both rows at F = 1000)
+    const int b2 = ((want & 1) && h_kp2d) ? n * 8 : 0, b3 = ((want & 2) && h_kp3d) ? n * 12 : 0;
+    if (b3)
+      sepb_pull_rows(kp3d + row * 3, h_kp3d + hrow * 3, b3, kp2d + row * 2, h_kp2d ? h_kp2d + hrow * 2 : nullptr, b2, threadIdx.x,
+                     blockDim.x);
+    else if (b2)
+      sepb_pull_row(kp2d + row * 2, h_kp2d + hrow * 2, b2);
+    bytes += (unsigned long long)b2 + (unsigned long long)b3;
+  }
   if ((want & 4) && h_octave) { sepb_pull_row(octave + row, h_octave + hrow, n * 4); bytes += (unsigned long long)n * 4; }
   __syncthreads();
   if (threadIdx.x == 0) {

@@ -499,13 +499,13 @@ hamming_mma_kernel(FramesView from, FramesView to, const int32_t* __restrict__ p
       s_claim[1] = lp.to_kp2d_host && rt < (unsigned)lp.to_n && sepb_claim_row(lp.to_have, ti, 1u);
     }
     __syncthreads();
-    if (s_claim[0]) {
-      sepb_pull_row(lp.from_kp3d + (size_t)fi * from.max_feat * 3, lp.from_kp3d_host + (size_t)rf * from.max_feat * 3, nf * 12);
-      if (tid == 0) atomicAdd(lp.from_fetched, (unsigned long long)nf * 12);
-    }
-    if (s_claim[1]) {
-      sepb_pull_row(lp.to_kp2d + (size_t)ti * to.max_feat * 2, lp.to_kp2d_host + (size_t)rt * to.max_feat * 2, nt * 8);
-      if (tid == 0) atomicAdd(lp.to_fetched, (unsigned long long)nt * 8);
+    const int bf = s_claim[0] ? nf * 12 : 0, bt = s_claim[1] ? nt * 8 : 0;
+    if (bf | bt) {
+      sepb_pull_rows<5>(lp.from_kp3d + (size_t)fi * from.max_feat * 3, bf ? lp.from_kp3d_host + (size_t)rf * from.max_feat * 3 : nullptr,
+                     bf, lp.to_kp2d + (size_t)ti * to.max_feat * 2, bt ? lp.to_kp2d_host + (size_t)rt * to.max_feat * 2 : nullptr, bt,
+                     tid, kThreadsT);
+      if (tid == 0 && bf) atomicAdd(lp.from_fetched, (unsigned long long)bf);
+      if (tid == 0 && bt) atomicAdd(lp.to_fetched, (unsigned long long)bt);
     }
   }
   K2T_STAMP(tid == 0, 3);
@@ -538,20 +538,6 @@ __device__ __forceinline__ PairGeom pair_geom(const FramesView& from, const Fram
   g.nt = valid ? min(to.count[g.ti], to.max_feat) : 0;
   return g;
 }
-__device__ __forceinline__ void pull_row_n(void* dst, const void* src, int bytes, int tid, int nthreads) {
-  if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
-    const int n16 = bytes >> 4;
-    const int4* s = reinterpret_cast<const int4*>(src);
-    int4* d = reinterpret_cast<int4*>(dst);
-    for (int i = tid; i < n16; i += nthreads) d[i] = __ldcs(s + i);
-    for (int i = (n16 << 4) + 4 * tid; i < bytes; i += 4 * nthreads)
-      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
-  } else {
-    for (int i = 4 * tid; i < bytes; i += 4 * nthreads)
-      *reinterpret_cast<int32_t*>((char*)dst + i) = *reinterpret_cast<const int32_t*>((const char*)src + i);
-  }
-}
-
 template <int TN>
 __global__ void __launch_bounds__(kThreadsT, 1)
 hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs, float nndr, int strict,
@@ -905,15 +891,15 @@ hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __rest
       }
       bar_sync(1, kEpiThreads);   // also: s_scan / s_any / s_dropped are free again
       if (pull) {
-        if (s_claim[0]) {
-          pull_row_n(lp.from_kp3d + (size_t)fi * from.max_feat * 3, lp.from_kp3d_host + (size_t)rf * from.max_feat * 3, nf * 12,
-                     tid, kEpiThreads);
-          if (tid == 0) atomicAdd(lp.from_fetched, (unsigned long long)nf * 12);
-        }
-        if (s_claim[1]) {
-          pull_row_n(lp.to_kp2d + (size_t)ti * to.max_feat * 2, lp.to_kp2d_host + (size_t)rt * to.max_feat * 2, nt * 8, tid,
-                     kEpiThreads);
-          if (tid == 0) atomicAdd(lp.to_fetched, (unsigned long long)nt * 8);
+        // both rows in one batch of loads: one PCIe round trip on the epilogue's critical path, not five
+        const int bf = s_claim[0] ? nf * 12 : 0, bt = s_claim[1] ? nt * 8 : 0;
+        if (bf | bt) {
+          sepb_pull_rows<5>(lp.from_kp3d + (size_t)fi * from.max_feat * 3,
+                         bf ? lp.from_kp3d_host + (size_t)rf * from.max_feat * 3 : nullptr, bf,
+                         lp.to_kp2d + (size_t)ti * to.max_feat * 2,
+                         bt ? lp.to_kp2d_host + (size_t)rt * to.max_feat * 2 : nullptr, bt, tid, kEpiThreads);
+          if (tid == 0 && bf) atomicAdd(lp.from_fetched, (unsigned long long)bf);
+          if (tid == 0 && bt) atomicAdd(lp.to_fetched, (unsigned long long)bt);
         }
         bar_sync(1, kEpiThreads);   // s_claim is read before the next pair's tail may rewrite it
       }
