@@ -524,6 +524,19 @@ __device__ __forceinline__ void bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 constexpr int kEpiThreads = kEpiWarps * 32;   // the tail's 256 threads (named barrier 1)
+// Host-bound stores (LazyPull): three more warps of the persistent CTA copy the key-point rows of the pairs that will run
+// PnP out of mapped host memory.  A load over PCIe takes microseconds on a quiet bus and ~100 us while the next step's bulk
+// upload saturates it -- several pairs' worth of matching -- so the epilogue only posts (row, length) requests to a small
+// ring in shared memory and goes on; the pullers drain it (12 loads of 16 bytes per lane in flight: 18 KB per SM) and finish what is
+// left when the pair loop ends.  K3 is a later kernel: every copy has landed by then.  A full ring falls back to the
+// inline copy by the epilogue's 256 threads.
+constexpr int kPullWarps = 3;
+constexpr int kPullWarp0 = kProdWarp0 + kProdWarps;
+constexpr int kThreadsP = kThreadsT + kPullWarps * 32;   // 512
+constexpr int kPullQ = 24;                               // ring entries (8 bytes each; static shared memory must stay <= 512 B)
+static_assert(kPullQ % kPullWarps == 0, "request j belongs to puller j % kPullWarps, also after the ring wraps");
+__device__ __forceinline__ int ld_vol(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+__device__ __forceinline__ void st_vol(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
 
 struct PairGeom {
   int fi, ti, nf, nt;
@@ -539,7 +552,7 @@ __device__ __forceinline__ PairGeom pair_geom(const FramesView& from, const Fram
   return g;
 }
 template <int TN>
-__global__ void __launch_bounds__(kThreadsT, 1)
+__global__ void __launch_bounds__(kThreadsP, 1)
 hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __restrict__ pairs, int n_pairs, float nndr, int strict,
                            int32_t* __restrict__ knn_idx, int32_t* __restrict__ knn_dist, int32_t* __restrict__ n_matches,
                            uint16_t* __restrict__ match_from, uint16_t* __restrict__ match_to,
@@ -564,20 +577,22 @@ hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __rest
   __shared__ int s_scan[kEpiWarps];
   __shared__ int s_dropped, s_any;
   __shared__ int s_claim[2];
+  __shared__ int2 s_pq[kPullQ];              // pull requests: {row kind << 31 | slot, features}
+  __shared__ int s_phead, s_pdone, s_ptail[kPullWarps];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   // ---- setup, once per CTA ---------------------------------------------------------------------------
-  for (int i = tid; i < 4 * to.max_feat; i += kThreadsT) s_top[i] = kNoneKey;
-  for (int i = tid; i < (kBxBytes + kAxBytes) / 16; i += kThreadsT)
+  for (int i = tid; i < 4 * to.max_feat; i += kThreadsP) s_top[i] = kNoneKey;
+  for (int i = tid; i < (kBxBytes + kAxBytes) / 16; i += kThreadsP)
     reinterpret_cast<uint4*>(sBx)[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
-  for (int r = tid; r < CH; r += kThreadsT) {
+  for (int r = tid; r < CH; r += kThreadsP) {
     const int col = r & (kHalf - 1);
     uint8_t* p = sBx + (r >> 3) * 128 + (r & 7) * 16;
     p[0] = (uint8_t)(col >> 6);
     p[1] = (uint8_t)(col & 63);
   }
-  for (int r = tid; r < TM; r += kThreadsT)
+  for (int r = tid; r < TM; r += kThreadsP)
     *reinterpret_cast<uint32_t*>(sAx + (r >> 3) * 256 + (r & 7) * 16) = 0x8080FFC0u;  // (-64, -1, -128, -128)
   if (tid == 0) {
     for (int s = 0; s < 2; ++s) {
@@ -595,6 +610,9 @@ hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __rest
     umma::fence_mbar_init();
     s_dropped = 0;
     s_any = 0;
+    s_phead = 0;
+    s_pdone = 0;
+    for (int w = 0; w < kPullWarps; ++w) s_ptail[w] = w;   // next request puller w consumes
   }
   if (warp == kMmaWarp) umma::tmem_alloc(&tmem_slot, 512);
   umma::fence_proxy_async();
@@ -603,7 +621,35 @@ hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __rest
   umma::tc_fence_after();
   const uint32_t tmem = tmem_slot;
 
-  if (warp >= kProdWarp0) {
+  if (warp >= kPullWarp0) {
+    // ---- pullers: copy the requested rows out of mapped host memory --------------------------------------------
+    const int w = warp - kPullWarp0;
+    for (int next = w;; next += kPullWarps) {
+      bool have = false;
+      while (true) {
+        if (ld_vol(&s_phead) > next) { have = true; break; }
+        if (ld_vol(&s_pdone)) { have = ld_vol(&s_phead) > next; break; }
+        __nanosleep(256);
+      }
+      if (!have) break;
+      __threadfence_block();
+      const int2 rq = s_pq[next % kPullQ];
+      const int slot = rq.x & 0x7fffffff, n = rq.y;
+      if (rq.x < 0) {   // To pixels
+        const unsigned rel = (unsigned)(slot - lp.to_first);
+        sepb_pull_rows<12>(lp.to_kp2d + (size_t)slot * to.max_feat * 2, lp.to_kp2d_host + (size_t)rel * to.max_feat * 2, n * 8,
+                           nullptr, nullptr, 0, lane, 32);
+        if (lane == 0) atomicAdd(lp.to_fetched, (unsigned long long)n * 8);
+      } else {          // From 3-D points
+        const unsigned rel = (unsigned)(slot - lp.from_first);
+        sepb_pull_rows<12>(lp.from_kp3d + (size_t)slot * from.max_feat * 3, lp.from_kp3d_host + (size_t)rel * from.max_feat * 3,
+                           n * 12, nullptr, nullptr, 0, lane, 32);
+        if (lane == 0) atomicAdd(lp.from_fetched, (unsigned long long)n * 12);
+      }
+      __syncwarp();
+      if (lane == 0) st_vol(&s_ptail[w], next + kPullWarps);   // the ring entry may be reused
+    }
+  } else if (warp >= kProdWarp0) {
     // ---- producers: run ahead through the pair sequence, held back only by the operand rings --------------------
     const int p = tid - kProdWarp0 * 32;
     const uint32_t sB_a = umma::smem_u32(sB), sA_a = umma::smem_u32(sA);
@@ -885,8 +931,22 @@ hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __rest
         s_dropped = 0;
         s_any = 0;
         if (pull) {
-          s_claim[0] = lp.from_kp3d_host && rf < (unsigned)lp.from_n && sepb_claim_row(lp.from_have, fi, 2u);
-          s_claim[1] = lp.to_kp2d_host && rt < (unsigned)lp.to_n && sepb_claim_row(lp.to_have, ti, 1u);
+          // rows this CTA is first to want: hand them to the pullers; s_claim keeps what the ring could not take
+          bool cf = lp.from_kp3d_host && rf < (unsigned)lp.from_n && sepb_claim_row(lp.from_have, fi, 2u);
+          bool ct = lp.to_kp2d_host && rt < (unsigned)lp.to_n && sepb_claim_row(lp.to_have, ti, 1u);
+          int head = s_phead;
+          auto post = [&](int x, int n) {
+            // entry head % kPullQ last held request head - kPullQ, which puller head % kPullWarps consumes
+            if (ld_vol(&s_ptail[head % kPullWarps]) <= head - kPullQ) return false;   // ring full: copy inline
+            s_pq[head % kPullQ] = make_int2(x, n);
+            __threadfence_block();
+            st_vol(&s_phead, ++head);
+            return true;
+          };
+          if (cf && post(fi, nf)) cf = false;
+          if (ct && post(ti | (int)0x80000000, nt)) ct = false;
+          s_claim[0] = cf;
+          s_claim[1] = ct;
         }
       }
       bar_sync(1, kEpiThreads);   // also: s_scan / s_any / s_dropped are free again
@@ -903,6 +963,10 @@ hamming_mma_persist_kernel(FramesView from, FramesView to, const int32_t* __rest
         }
         bar_sync(1, kEpiThreads);   // s_claim is read before the next pair's tail may rewrite it
       }
+    }
+    if (tid == 0) {
+      __threadfence_block();
+      st_vol(&s_pdone, 1);   // the pullers finish the requests still in the ring, then join the barrier below
     }
   }
   umma::tc_fence_before();
@@ -967,11 +1031,11 @@ int sepb_launch_hamming_mma(sepb_ctx* ctx, FramesView from, FramesView to, const
     }
     const int ctas = n_pairs < ctx->sm_count ? n_pairs : ctx->sm_count;
     if (wide)
-      hamming_mma_persist_kernel<256><<<ctas, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
+      hamming_mma_persist_kernel<256><<<ctas, kThreadsP, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
                                                                                d_knn_dist, d_n_matches, d_match_from, d_match_to,
                                                                                d_n_unique_to, lp);
     else
-      hamming_mma_persist_kernel<128><<<ctas, kThreadsT, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
+      hamming_mma_persist_kernel<128><<<ctas, kThreadsP, smem, ctx->stream>>>(from, to, d_pairs, n_pairs, nndr, strict, d_knn_idx,
                                                                                d_knn_dist, d_n_matches, d_match_from, d_match_to,
                                                                                d_n_unique_to, lp);
     ctx->launches++;
