@@ -294,24 +294,26 @@ __device__ bool cholesky6(const double* S /*21, upper by rows*/, double lam, con
     double d = L[7 * j];
     for (int p = 0; p < j; ++p) d -= L[6 * j + p] * L[6 * j + p];
     if (!(d > 0)) return false;
-    d = sqrt(d);
-    L[7 * j] = d;
+    // one reciprocal per column instead of a division per entry: this solve is serial work of one thread while the CTA
+    // waits (ncu: `barrier` is the kernel's top stall), and an FP64 division is a ~40-instruction dependent chain
+    const double inv = 1.0 / sqrt(d);
+    L[7 * j] = inv;   // the diagonal holds 1 / L_jj
     for (int i = j + 1; i < 6; ++i) {
       double v = L[6 * i + j];
       for (int p = 0; p < j; ++p) v -= L[6 * i + p] * L[6 * j + p];
-      L[6 * i + j] = v / d;
+      L[6 * i + j] = v * inv;
     }
   }
   double y[6];
   for (int i = 0; i < 6; ++i) {
     double v = rhs[i];
     for (int p = 0; p < i; ++p) v -= L[6 * i + p] * y[p];
-    y[i] = v / L[7 * i];
+    y[i] = v * L[7 * i];
   }
   for (int i = 5; i >= 0; --i) {
     double v = y[i];
     for (int p = i + 1; p < 6; ++p) v -= L[6 * p + i] * x[p];
-    x[i] = v / L[7 * i];
+    x[i] = v * L[7 * i];
   }
   return true;
 }
@@ -324,7 +326,7 @@ struct Ctl {
   double Al[21], bcl[6], chil; // the link edge's share of the camera block at c2
   double bc[6];                // raw camera gradient of the trial (points + link)
   double xp[6];
-  double lam, ni, cur_chi, rho, chi2;
+  double lam, ni, cur_chi, rho, chi2, lchi_n;   // lchi_n: the link edge's chi2 at the trial pose cn
   int qmax, ok, again, stop, cur, fail, iters;
 };
 
@@ -574,6 +576,8 @@ bundle_adjust_kernel(FramesView from, FramesView to, const int32_t* __restrict__
         }
         first = false;
         double part[2] = {0, 0};   // dx . (lambda dx + b) over the points, robust chi2 at the trial estimate
+        // the link edge at the trial pose: by one thread of another warp, under the pass below, not by thread 0 after it
+        if (ctl.ok && tid == kThreadsB - 1) ctl.lchi_n = link_chi(ctl, ctl.cn.p);
         if (ctl.ok) {
           double xp[6];
           for (int k = 0; k < 6; ++k) xp[k] = ctl.xp[k];
@@ -612,7 +616,7 @@ bundle_adjust_kernel(FramesView from, FramesView to, const int32_t* __restrict__
         if (tid == 0) {
           double tmp_chi = kHuge, scale = 0;
           if (ctl.ok) {
-            tmp_chi = part[1] + link_chi(ctl, ctl.cn.p);
+            tmp_chi = part[1] + ctl.lchi_n;
             scale = part[0];
             for (int k = 0; k < 6; ++k) scale += ctl.xp[k] * (lam * ctl.xp[k] + ctl.bc[k]);
           }
