@@ -430,7 +430,7 @@ def run_ours(args):
         # DRAM traffic per launch from the committed ncu --set full captures (only valid for the workload they were taken on)
         traffic = {}
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
             w = tj["workload"]
             if (w["keyframes_per_robot"], w["features_per_frame"], w["netvlad_dim"], w["top_k"]) == \
                     (args.frames, args.feat, args.dim, args.topk):
@@ -443,7 +443,7 @@ def run_ours(args):
         k2_tops = P * 2.0 * 256 * args.feat * args.feat / (ms_k2 * 1e-3) / 1e12  # 256-term dot product per distance
         rooflines = {}
         if match_kernel == "tensor":
-            rooflines["K2"] = {"kernel": "hamming_mma_kernel (K2T, tcgen05 kind::i8)", "bound": "tensor", "achieved": k2_tops,
+            rooflines["K2"] = {"kernel": "hamming_mma_persist_kernel (K2T, tcgen05 kind::i8)", "bound": "tensor", "achieved": k2_tops,
                                "peak": 2 * bf16_burst, "unit": "TOP/s", "frac": k2_tops / (2 * bf16_burst), "traffic": traffic.get("K2"),
                                "algorithmic_bytes": k2_bytes,
                                "peak_source": peak_src + ": 2 x measured bf16 burst (int8 dense issues at twice the bf16 rate; "
@@ -480,7 +480,7 @@ def run_ours(args):
         c_solve = 1.1e5 if args.pnp_flags == 0 else 2.5e3          # f64 ops of one 5-point EPnP / one 4-point P3P solve
         k3_ops = n_ransac * iters_mean * (c_solve + 30.0 * m_mean)   # H_eff * (C_solve + 30*M)
         ransac_pairs_per_s = world * n_ransac / max(ms_k3 * 1e-3, 1e-12)
-        rooflines["K3"] = {"kernel": "pnp_ransac_kernel (K3)", "bound": "fp64 issue", "achieved": k3_ops / max(ms_k3, 1e-9) / 1e-3,
+        rooflines["K3"] = {"kernel": "pnp_persist_kernel (K3)", "bound": "fp64 issue", "achieved": k3_ops / max(ms_k3, 1e-9) / 1e-3,
                            "peak": dfma_peak, "unit": "f64 op/s", "frac": k3_ops / max(ms_k3, 1e-9) / 1e-3 / dfma_peak,
                            "peak_source": "sepb_measure_peak FP64 FMA microbenchmark, same run", "traffic": traffic.get("K3"),
                            "launches_per_step": 2, "note": "latency-bound by construction: OpenCV's serial f64 operation order is "
