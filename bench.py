@@ -371,20 +371,34 @@ def run_ours(args):
     barrier()
     t0 = time.perf_counter()
     ph = np.zeros(3)
+    done = [torch.cuda.Event(), torch.cuda.Event()]
+    deep = args.e2e_pipeline == "deep"
+    if deep:
+        # verify(s+1) is enqueued BEHIND verify(s) before the host waits for step s's results: the device goes from one
+        # step's K3 straight into the next step's K2 (no host round trip between them)
+        verify(slots[0], 0)
+        done[0].record(eng.stream)
     for s_ in range(e2e_steps):
         c, n_ = s_ & 1, (s_ + 1) & 1
         p0 = time.perf_counter()
-        verify(slots[c], c)            # step s
+        if not deep:
+            verify(slots[c], c)        # step s
         p1 = time.perf_counter()
         keyframes(slots[n_])           # step s+1's keyframes travel while step s is verified
         p2 = time.perf_counter()
         if s_ + 1 < e2e_steps:
             descriptors(slots[n_])     # step s+1: peer descriptors and candidate search
             search(slots[n_], n_)
-        eng.ctx.sync()                 # step s's results are in the caller's buffers
+            if deep:
+                verify(slots[n_], n_)
+                done[n_].record(eng.stream)
+        if deep:
+            done[c].synchronize()      # step s's results are in the caller's buffers
+        else:
+            eng.ctx.sync()
         p3 = time.perf_counter()
         ph += (p1 - p0, p2 - p1, p3 - p2)
-        r_e2e = outs[c]
+        r_e2e = {k: v.copy() for k, v in outs[c].items()} if deep and s_ == e2e_steps - 1 else outs[c]
     slots[n_].local.wait()             # the last submitted upload completes inside the timed region
     slots[n_].peer.wait()
     torch.cuda.synchronize()
@@ -493,7 +507,9 @@ def run_ours(args):
                 "data": "synthetic", "config": workload_config(args), "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
                         "steps": e2e_steps, "host_phases_ms": e2e_phases_ms,
-                        "pipeline": "double-buffered keyframe stores: step s+1 uploads while step s is verified; its candidate search runs "
+                        "pipeline": ("the next step's verification is enqueued behind this one before the host waits for results; "
+                                     if args.e2e_pipeline == "deep" else "") +
+                                    "double-buffered keyframe stores: step s+1 uploads while step s is verified; its candidate search runs "
                                     + ("on a high-priority second stream, concurrently" if args.e2e_search == "overlap" else "behind it on the same stream"),
                         "upload": ("lazy key points: descriptors + counts of every frame are copied, kp2d / kp3d rows are pulled by the "
                                    "device from pinned host memory for the frames whose pairs reach PnP (sepb_frames_bind_host_async)")
@@ -872,6 +888,9 @@ def main():
                     help="Hamming matcher kernel: tcgen05 int8 GEMM (tensor), POPC pipe (popc); identical results")
     ap.add_argument("--e2e-upload", default="lazy", choices=["lazy", "full"],
                     help="end-to-end leg: how keyframes reach the device (identical results)")
+    ap.add_argument("--e2e-pipeline", default="simple", choices=["deep", "simple"],
+                    help="end-to-end leg: deep = the next step's verification is enqueued before the host waits for this "
+                         "step's results; simple = enqueue, wait, enqueue")
     ap.add_argument("--e2e-search", default="overlap", choices=["overlap", "serial"],
                     help="end-to-end leg: the next step's candidate search on a high-priority second context (overlap) or "
                          "queued behind the verification on the same stream (serial)")
