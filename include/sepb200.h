@@ -338,7 +338,8 @@ SEPB_API int sepb_estimate_transformations_dev(sepb_ctx* ctx, const sepb_frames*
  * whose chi2 exceeds the kernel's delta after each stage drop their inlier; the refined pose replaces the transform,
  * fewer than min_inliers remaining inliers (SEPB_PNP_FEW_INLIERS) or a diverged optimisation (SEPB_PNP_BA_FAILED) null
  * it.  g2o and RTAB-Map are not vendored by the reference: the algorithm is restated from their published sources
- * (oracle/ba.py), parity against the reference's binaries is unpinned.  cvsba (type 2) is not built. */
+ * (oracle/ba.py), parity against the reference's binaries is unpinned.  cvsba (type 2) is not built.  Stores with
+ * max_feat > 2048 are refused (SEPB_E_SHAPE). */
 typedef struct sepb_ba_params {
   int32_t type;                /* Vis/BundleAdjustment: 0 = off, 1 = g2o-style (the only one built) */
   int32_t iterations;          /* Optimizer/Iterations of the second stage, 20 */

@@ -224,3 +224,43 @@ def test_inside_verify_pairs_and_the_two_call_driver(ctx):
     finally:
         ctx.set_bundle_adjustment(None)
         fr.close(); to.close()
+
+
+def test_host_bound_stores_and_other_solver_options(ctx):
+    """The adjustment needs the From pixels and the To 3-D points too: with host-bound stores (sepb_frames_bind_host_async)
+    they are fetched before it runs -- same results as with whole uploads; and it composes with the P3P flags and the
+    refine loop (it starts from whatever PnP produced)."""
+    import torch
+    A, B = synth.make_robots(2, 36, n_feat=1000, dim=8, seed=321, overlap=0.5)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()  # noqa: E731
+    hA = {k: pin(getattr(A, k)) for k in ("desc", "kp2d", "kp3d", "count", "octave")}
+    hB = {k: pin(getattr(B, k)) for k in ("desc", "kp2d", "kp3d", "count", "octave")}
+    pairs = [[o, l] for l in range(36) for o in range(36) if A.place[o] == B.place[l]][:20] + [[1, 0], [2, 5]]
+    fa, fb = capi.frames_from_robot(ctx, A), capi.frames_from_robot(ctx, B)
+    la, lb = capi.Frames(ctx, 36, 1000), capi.Frames(ctx, 36, 1000)
+    b = capi.ba_params(synth.BASELINE * synth.FY / synth.FX)
+    gp = capi.guess_params(synth.WIDTH, synth.HEIGHT)
+    try:
+        ctx.set_bundle_adjustment(b)
+        for kw in (dict(), dict(flags=capi.PNP_P3P), dict(refine_iterations=2)):
+            prm = capi.pnp_params(synth.FX, synth.FY, synth.CX, synth.CY, **kw)
+            want = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+            want2 = capi.estimate_transformations(ctx, fa, fb, pairs, prm, gp)
+            assert (want["status"] == 1).sum() >= 10
+            la.upload(0, hA["desc"], hA["kp2d"], hA["kp3d"], hA["count"], hA["octave"], lazy=True)
+            lb.upload(0, hB["desc"], hB["kp2d"], hB["kp3d"], hB["count"], hB["octave"], lazy=True)
+            got = capi.verify_pairs(ctx, la, lb, pairs, prm)
+            got2 = capi.estimate_transformations(ctx, la, lb, pairs, prm, gp)
+            for g, w in ((got, want), (got2, want2)):
+                for k in ("status", "n_matches", "n_inliers", "transform", "pose", "inlier_mask", "covariance"):
+                    assert np.array_equal(g[k], w[k], equal_nan=True), (kw, k)
+        # the adjustment really ran on top of each option: different from the same call without it
+        ctx.set_bundle_adjustment(None)
+        plain = capi.verify_pairs(ctx, fa, fb, pairs, prm)
+        ok = (plain["status"] == 1) & (want["status"] == 1)
+        assert ok.sum() >= 10 and (np.abs(plain["transform"][ok] - want["transform"][ok]).max(1) > 0).all()
+    finally:
+        ctx.set_bundle_adjustment(None)
+        ctx.sync()
+        for f in (fa, fb, la, lb):
+            f.close()
