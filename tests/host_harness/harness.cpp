@@ -4,6 +4,7 @@
 #include "../../multi_robot_slam_separators_b200/csrc/epnp.cuh"
 #include "../../multi_robot_slam_separators_b200/csrc/pnp_geom.cuh"
 #include "../../multi_robot_slam_separators_b200/csrc/p3p.cuh"
+#include "../../multi_robot_slam_separators_b200/csrc/ba_math.cuh"
 
 extern "C" {
 
@@ -60,4 +61,50 @@ void hh_epnp_n(const double* obj, const double* img, int n, const double* K4, do
 }
 
 int hh_update_iters(double p, double ep, int mp, int mx) { return cvm::ransac_update_num_iters(p, ep, mp, mx); }
+
+// ---- 2-view bundle adjustment arithmetic (ba_math.cuh) against oracle/ba.py ------------------------------------------
+static ba::BaKernelParams ba_params(const double* K4, double baseline, double var, double delta) {
+  ba::BaKernelParams P{};
+  P.fx = K4[0]; P.fy = K4[1]; P.cx = K4[2]; P.cy = K4[3];
+  P.baseline = baseline; P.var = var; P.delta = delta;
+  return P;
+}
+static ba::Cam ba_cam(const double* q4, const double* t3) {
+  ba::Cam c;
+  for (int i = 0; i < 4; ++i) c.p.q[i] = q4[i];
+  for (int i = 0; i < 3; ++i) c.p.t[i] = t3[i];
+  ba::cam_finish(c);
+  return c;
+}
+// one point's block of the normal equations: V (6, symmetric), bl (3), W (18), camera block A (21) and bc (6), chi2
+double hh_ba_point_system(const double* K4, double baseline, double var, double delta, const double* q1, const double* t1,
+                          const double* q2, const double* t2, const double* X, const float* meas6, unsigned flags, double* V,
+                          double* bl, double* W, double* A, double* bc) {
+  const ba::BaKernelParams P = ba_params(K4, baseline, var, delta);
+  const ba::Cam c1 = ba_cam(q1, t1), c2 = ba_cam(q2, t2);
+  ba::PtSys s;
+  for (int i = 0; i < 21; ++i) A[i] = 0;
+  for (int i = 0; i < 6; ++i) bc[i] = 0;
+  const double chi = ba::point_system(P, c1, c2, X, meas6, flags, s, A, bc);
+  for (int i = 0; i < 6; ++i) V[i] = s.V[i];
+  for (int i = 0; i < 3; ++i) bl[i] = s.bl[i];
+  for (int i = 0; i < 18; ++i) W[i] = s.W[i];
+  return chi;
+}
+void hh_ba_se3(const double* qa, const double* ta, const double* qb, const double* tb, const double* upd6, double* mul7,
+               double* inv7, double* upd7, double* link6) {
+  ba::Se3 a, b;
+  for (int i = 0; i < 4; ++i) { a.q[i] = qa[i]; b.q[i] = qb[i]; }
+  for (int i = 0; i < 3; ++i) { a.t[i] = ta[i]; b.t[i] = tb[i]; }
+  const ba::Se3 m = ba::se3_mul(a, b), iv = ba::se3_inv(a), u = ba::se3_update(a, upd6);
+  for (int i = 0; i < 4; ++i) { mul7[i] = m.q[i]; inv7[i] = iv.q[i]; upd7[i] = u.q[i]; }
+  for (int i = 0; i < 3; ++i) { mul7[4 + i] = m.t[i]; inv7[4 + i] = iv.t[i]; upd7[4 + i] = u.t[i]; }
+  ba::link_error(iv, iv, b, link6);   // measurement^-1 = cam1^-1 = a^-1: any fixed pair exercises the composition
+}
+int hh_ba_cholesky6(const double* S21, double lam, const double* rhs, double* x) { return ba::cholesky6(S21, lam, rhs, x) ? 1 : 0; }
+void hh_ba_quat(const double* R9, double* q4, double* R9_back) {
+  ba::quat_from_matrix(R9, q4);
+  ba::quat_normalize_rotation(q4);
+  ba::quat_to_matrix(q4, R9_back);
+}
 }

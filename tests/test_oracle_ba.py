@@ -111,3 +111,80 @@ def test_fixture(golden):
         assert ok == bool(g[f"ok_{i}"]) and np.array_equal(kept, g[f"kept_{i}"])
         assert np.abs(T - g[f"T_{i}"]).max() <= 1e-6
         assert abs(res["chi2"] - float(g[f"chi2_{i}"])) <= 1e-6 * float(g[f"chi2_{i}"])
+
+
+# ---- the product's arithmetic (csrc/ba_math.cuh, host build) against this oracle ---------------------------------------
+
+def _harness():
+    import ctypes as C
+    from tests import host_harness
+    H = host_harness.load()
+    dp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    H.hh_ba_point_system.restype = C.c_double
+    H.hh_ba_point_system.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double] + [C.c_void_p] * 6 + [C.c_uint] + [C.c_void_p] * 5
+    H.hh_ba_cholesky6.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]
+    return H, dp
+
+
+def test_header_point_block_matches_the_oracles_linearisation():
+    """ba_math.cuh:point_system (what the kernel accumulates per inlier) == oracle _linearize restricted to that point,
+    stereo and mono edges, edges that left (level 1), Huber on and off."""
+    H, dp = _harness()
+    pr, pb = problem(21, 40, n_out=5, nan_frac=0.3)
+    K4 = np.array(K, np.float64)
+    cam2 = ba.cam_update(pb["cam2"], np.array([0.01, -0.02, 0.015, 1e-3, -2e-3, 1e-3]))
+    pts = pb["pts"] + 0.01
+    pb["level"][0, 3] = 1
+    pb["level"][1, 7] = 1
+    for delta in (8.0, 0.0):
+        Vs, bls, Ws, A_or, bc_or, chi_or = ba._linearize(dict(pb, info=np.zeros((6, 6))), cam2, pts, 1.5, delta)
+        A_sum, bc_sum, chi_sum = np.zeros(21), np.zeros(6), 0.0
+        for i in range(40):
+            meas = np.concatenate([pb["meas"][0, i], pb["meas"][1, i]]).astype(np.float32)
+            flags = int(pb["level"][0, i]) | int(pb["level"][1, i]) << 1 | int(pb["stereo"][0, i]) << 2 | int(pb["stereo"][1, i]) << 3
+            V, bl, W, A, bc = np.zeros(6), np.zeros(3), np.zeros(18), np.zeros(21), np.zeros(6)
+            X = np.ascontiguousarray(pts[i])
+            chi_sum += H.hh_ba_point_system(dp(K4), bp.BASELINE, 1.5, delta, dp(pb["cam1"][0]), dp(pb["cam1"][1]),
+                                            dp(np.ascontiguousarray(cam2[0])), dp(np.ascontiguousarray(cam2[1])), dp(X),
+                                            dp(meas), flags, dp(V), dp(bl), dp(W), dp(A), dp(bc))
+            Vf = np.array([[V[0], V[1], V[2]], [V[1], V[3], V[4]], [V[2], V[4], V[5]]])
+            scale = max(1.0, np.abs(Vs[i]).max())
+            assert np.abs(Vf - Vs[i]).max() <= 1e-9 * scale and np.abs(bl - bls[i]).max() <= 1e-9 * scale
+            assert np.abs(W.reshape(6, 3) - Ws[i]).max() <= 1e-9 * max(1.0, np.abs(Ws[i]).max())
+            A_sum += A
+            bc_sum += bc
+        iu = np.triu_indices(6)
+        # the oracle's camera block also holds the link edge: its information was zeroed above, so only its chi2 (0) remains
+        assert np.abs(A_sum - A_or[iu]).max() <= 1e-9 * np.abs(A_or).max() and np.abs(bc_sum - bc_or).max() <= 1e-9 * np.abs(bc_or).max()
+        assert abs(chi_sum - chi_or) <= 1e-9 * chi_or
+
+
+def test_header_pose_algebra_and_small_solves():
+    import ctypes as C
+    H, dp = _harness()
+    rng = np.random.default_rng(5)
+    for _ in range(20):
+        qa = ba.quat_normalize_rotation(rng.normal(size=4))
+        qb = ba.quat_normalize_rotation(rng.normal(size=4))
+        ta, tb = rng.normal(size=3), rng.normal(size=3)
+        upd = rng.normal(0, 0.05, 6)
+        mul7, inv7, upd7, link6 = np.zeros(7), np.zeros(7), np.zeros(7), np.zeros(6)
+        H.hh_ba_se3(dp(qa), dp(ta), dp(qb), dp(tb), dp(upd), dp(mul7), dp(inv7), dp(upd7), dp(link6))
+        m, iv, u = ba.se3_mul((qa, ta), (qb, tb)), ba.se3_inv((qa, ta)), ba.cam_update((qa, ta), upd)
+        for got, want in ((mul7, m), (inv7, iv), (upd7, u)):
+            assert np.abs(got[:4] - want[0]).max() < 1e-14 and np.abs(got[4:] - want[1]).max() < 1e-13
+        d = ba.se3_mul(iv, ba.se3_mul(iv, (qb, tb)))
+        assert np.abs(link6 - np.concatenate([d[1], d[0][:3]])).max() < 1e-13
+        # rotation matrix <-> quaternion, both branches of Eigen's conversion (trace > 0 and each dominant diagonal)
+        R = ba.quat_to_matrix(qa)
+        q4, Rb = np.zeros(4), np.zeros(9)
+        H.hh_ba_quat(dp(np.ascontiguousarray(R.ravel())), dp(q4), dp(Rb))
+        assert np.abs(q4 - ba.quat_normalize_rotation(ba.quat_from_matrix(R))).max() < 1e-14 and np.abs(Rb.reshape(3, 3) - R).max() < 1e-14
+        # 6 x 6 Cholesky (one reciprocal per column) against numpy
+        M = rng.normal(size=(6, 6))
+        S = M @ M.T + 0.1 * np.eye(6)
+        rhs, x = rng.normal(size=6), np.zeros(6)
+        assert H.hh_ba_cholesky6(dp(np.ascontiguousarray(S[np.triu_indices(6)])), 0.3, dp(rhs), dp(x)) == 1
+        assert np.abs(x - np.linalg.solve(S + 0.3 * np.eye(6), rhs)).max() < 1e-10
+    S = -np.eye(6)
+    assert H.hh_ba_cholesky6(dp(np.ascontiguousarray(S[np.triu_indices(6)])), 0.0, dp(np.ones(6)), dp(np.zeros(6))) == 0
