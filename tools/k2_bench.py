@@ -6,6 +6,8 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from multi_robot_slam_separators_b200 import capi, synth
 
+if os.environ.get("SEPB_LIB"):          # developer: time another build of the library on the same data
+    capi.LIB_PATH = os.path.abspath(os.environ["SEPB_LIB"])
 ctx = capi.Context(0)
 print("popc/s %.3e  dfma/s %.3e" % (ctx.measure_peak("popc"), ctx.measure_peak("dfma")))
 nF = int(sys.argv[1]) if len(sys.argv) > 1 else 256
