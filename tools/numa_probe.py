@@ -4,6 +4,7 @@ import glob
 import os
 import subprocess
 import sys
+import time
 
 import torch
 
@@ -56,6 +57,25 @@ def main():
         print("node %d -> gpu0: %.1f GB/s" % (node, 5 * (1 << 30) / e0.elapsed_time(e1) / 1e6))
         del src
     os.sched_setaffinity(0, allowed)
+    # aggregate host -> device bandwidth with 1, 2, 4, 8 GPUs copying at once (what bounds the end-to-end leg at N = 8)
+    ng = torch.cuda.device_count()
+    size = 1 << 29
+    srcs = [torch.empty(size, dtype=torch.uint8).pin_memory() for _ in range(ng)]
+    dsts = [torch.empty(size, dtype=torch.uint8, device="cuda:%d" % d) for d in range(ng)]
+    for k in sorted({1, 2, 4, 8, ng}):
+        if k > ng:
+            continue
+        for rep in range(2):
+            for d in range(k):
+                torch.cuda.synchronize(d)
+            t0 = time.perf_counter()
+            for _ in range(4):
+                for d in range(k):
+                    dsts[d].copy_(srcs[d], non_blocking=True)
+            for d in range(k):
+                torch.cuda.synchronize(d)
+            dt = time.perf_counter() - t0
+        print("%d GPUs copying at once: %.1f GB/s in aggregate (%.1f per GPU)" % (k, 4 * k * size / dt / 1e9, 4 * size / dt / 1e9))
 
 
 if __name__ == "__main__":
