@@ -1,5 +1,7 @@
+"""RANSAC statistics of the two calls of estimate_transformation on a synthetic world: matches, inliers, iterations run
+(why the second call's K3 costs as much as the first: the window matcher's lists have a lower inlier ratio)."""
 import sys, os, numpy as np, torch
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from multi_robot_slam_separators_b200 import capi, synth
 from multi_robot_slam_separators_b200.engine import Camera, SeparatorEngine
 n = 4000
